@@ -1,0 +1,148 @@
+"""Host-side mirror of cvpce/models/classification.py for the hot path (same names, arguments and results).
+
+The conv trunks stay torch modules (not rebuilt); pooling + concat + L2 (classification.py:46-51, 79-85)
+and the nearest-neighbour search (classification.py:87-95) run in libcvpce_b200.so.
+"""
+import torch
+from torch import nn
+from torchvision.models import resnet, vgg
+
+from . import ops
+
+# MACVGG.forward normalisation constants (classification.py:41-44): ImageNet statistics re-expressed for [-1,1] input
+NORM_MEAN = [0.485 * 2 - 1, 0.456 * 2 - 1, 0.406 * 2 - 1]
+NORM_STD = [0.229 * 2, 0.224 * 2, 0.225 * 2]
+
+
+def tanh_normalize_affine():
+    """Per-channel (a,b) with a*x+b == normalize(scale_to_tanh(x)) for x in [0,1]: folds utils.py:280-281 and
+    classification.py:41-44 into the crop kernel's affine."""
+    out = []
+    for m, s in zip(NORM_MEAN, NORM_STD):
+        out += [2.0 / s, (-1.0 - m) / s]
+    return out
+
+
+class MACVGG(nn.Module):
+    """classification.py:20-51. VGG16 split after relu4_3 / relu5_3; MAC descriptor of both, concatenated, L2-normalised."""
+
+    embedding_size = 512 * 2
+
+    def __init__(self, config='D', convs_per_block=(2, 2, 3, 3, 3), batch_norm=True, vgg_state_dict=None):
+        super().__init__()
+        source = vgg.VGG(vgg.make_layers(vgg.cfgs[config], batch_norm=batch_norm), init_weights=vgg_state_dict is None)
+        if vgg_state_dict is not None:
+            source.load_state_dict(vgg_state_dict)
+        per_conv = 3 if batch_norm else 2
+        block_lengths = [n * per_conv + 1 for n in convs_per_block]  # + max pool
+        split_1 = sum(block_lengths[:-1]) - 1  # through the last ReLU of block 4
+        split_2 = sum(block_lengths) - 1       # through the last ReLU of block 5 (no pool5)
+        self.block1 = source.features[:split_1]
+        self.block2 = source.features[split_1:split_2]
+        self.register_buffer('_mean', torch.tensor(NORM_MEAN).view(1, 3, 1, 1), persistent=False)
+        self.register_buffer('_std', torch.tensor(NORM_STD).view(1, 3, 1, 1), persistent=False)
+        self.regions_levels = 0  # 0: MAC (reference); L>0: R-MAC extension with L scales
+
+    def features(self, x, normalized=False):
+        if not normalized:
+            x = (x - self._mean.to(x.dtype)) / self._std.to(x.dtype)
+        f4 = self.block1(x)
+        f5 = self.block2(f4)
+        return f4, f5
+
+    def forward(self, x, eps=1e-8, normalized=False):
+        f4, f5 = self.features(x, normalized)
+        if f4.dtype not in (torch.float32, torch.bfloat16):
+            f4, f5 = f4.float(), f5.float()
+        if self.regions_levels > 0:
+            regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.regions_levels) for f in (f4, f5)]
+            return ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=True, final_l2=True, eps=eps)
+        return ops.region_pool_embed([f4, f5], eps=eps)
+
+
+class MACResNet(nn.Module):
+    """classification.py:53-85."""
+    layer_output_sizes = [64, 256, 512, 1024, 2048]
+
+    def __init__(self, source_resnet, descriptor_layers=(2, 3)):
+        super().__init__()
+        stages = [nn.Sequential(source_resnet.conv1, source_resnet.bn1, source_resnet.relu, source_resnet.maxpool),
+                  source_resnet.layer1, source_resnet.layer2, source_resnet.layer3, source_resnet.layer4]
+        self.blocks = nn.ModuleList()
+        start = 0
+        for l in descriptor_layers:
+            self.blocks.append(nn.Sequential(*stages[start:l + 1]))
+            start = l + 1
+        self.embedding_size = sum(self.layer_output_sizes[l] for l in descriptor_layers)
+
+    def forward(self, x, eps=1e-8):
+        feats = []
+        for b in self.blocks:
+            x = b(x)
+            feats.append(x)
+        return ops.region_pool_embed(feats, eps=eps)
+
+
+# below this many similarity entries the launch-bound fp32 kernel is used; above it the tcgen05 kernel
+_TENSOR_CORE_MIN_WORK = 1 << 16
+
+
+def nearest_neighbors(anchors, queries, k=1, exact=True):
+    """classification.py:90-95: indices int64[Q,k] of the k anchors with the smallest cosine distance to each query,
+    ascending distance; ties by ascending anchor index (the reference's argsort leaves ties unspecified)."""
+    return similarity_topk(anchors, queries, k, exact)[1]
+
+
+def similarity_topk(anchors, queries, k=1, exact=True, prepared=None):
+    """(cosine similarity f32[Q,k], indices i64[Q,k]). `prepared` = PreparedGallery for a gallery searched repeatedly."""
+    Q, D = queries.shape
+    G = anchors.shape[0] if prepared is None else prepared.G
+    k_eff = min(k, G) if G > 0 else 0
+    if Q == 0 or k_eff == 0:
+        return (torch.empty((Q, k_eff), dtype=torch.float32, device=queries.device),
+                torch.empty((Q, k_eff), dtype=torch.int64, device=queries.device))
+    use_tc = (D % 64 == 0 and 64 <= D <= 4096 and k_eff <= 32 and Q * G >= _TENSOR_CORE_MIN_WORK)
+    if not use_tc:
+        g = anchors if prepared is None else prepared.f32
+        return ops.sim_topk_f32(queries, g, k_eff, normalize=True)
+    if prepared is None:
+        prepared = PreparedGallery(anchors)
+    q32 = queries.contiguous().float()
+    qb, qinv = ops.rows_prepare(q32, normalize=True)
+    return ops.sim_topk(qb, prepared.bf16, k_eff, 0, q32 if exact else None, prepared.f32 if exact else None,
+                        qinv if exact else None, prepared.inv_norm if exact else None)
+
+
+class PreparedGallery:
+    """One-time operand preparation of a gallery (Classifier.build_index time): fp32 rows, inverse norms, bf16 unit rows."""
+
+    def __init__(self, embedding, idx_base=0):
+        self.f32 = embedding.contiguous().float()
+        self.G, self.D = self.f32.shape
+        self.idx_base = idx_base
+        if self.G > 0 and self.D % 64 == 0:
+            self.bf16, self.inv_norm = ops.rows_prepare(self.f32, normalize=True)
+        else:
+            self.bf16, self.inv_norm = None, None
+
+
+def macvgg_embedder(model='vgg16_bn', pretrained=True, progress=True):
+    """classification.py:97-109."""
+    configs = {'vgg16': ('D', False), 'vgg16_bn': ('D', True)}
+    if model not in configs:
+        raise NotImplementedError(f'MACVGG not implemented for {model}')
+    state = None
+    if pretrained:
+        weights = {'vgg16': vgg.VGG16_Weights.IMAGENET1K_V1, 'vgg16_bn': vgg.VGG16_BN_Weights.IMAGENET1K_V1}[model]
+        state = weights.get_state_dict(progress=progress)
+    config, bn = configs[model]
+    return MACVGG(config, vgg_state_dict=state, batch_norm=bn)
+
+
+def macresnet_encoder(model='resnet50', pretrained=True, progress=True, batch_norm=True, desc_layers=(2, 3)):
+    """classification.py:111-121 (rebuilt on the current torchvision constructor; the reference's call is broken there)."""
+    if model != 'resnet50':
+        raise NotImplementedError(f'MACResNet not implemented for {model}')
+    norm_layer = nn.BatchNorm2d if batch_norm else nn.Identity
+    weights = resnet.ResNet50_Weights.IMAGENET1K_V1 if pretrained else None
+    return MACResNet(resnet.resnet50(weights=weights, progress=progress, norm_layer=norm_layer), desc_layers)

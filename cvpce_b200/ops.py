@@ -1,0 +1,260 @@
+"""Tensor-in / tensor-out wrappers over the C ABI (include/cvpce_b200.h).
+
+torch is plumbing here: it owns device memory and the current stream; all arithmetic happens in libcvpce_b200.so.
+CPU tensors are rejected -- there is no CPU fallback.
+"""
+import ctypes
+import math
+import struct
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32, NCHW, NHWC  # noqa: F401
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _need_cuda(name, *tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("%s: expected CUDA tensors (cvpce_b200 has no CPU fallback), got device %s" % (name, t.device))
+
+
+def threshold_as_cpu_op(iou_threshold):
+    """torchvision's CPU nms compares the fp32 IoU with a DOUBLE threshold; `ovr > thr_double` is equivalent to
+    `ovr > f` with f the largest fp32 <= thr_double. (Equal to float(thr) for 0.5, the only value cvpce uses.)"""
+    f = struct.unpack("f", struct.pack("f", iou_threshold))[0]
+    if f > iou_threshold:  # rounded up: step one ulp down
+        bits = struct.unpack("I", struct.pack("f", f))[0]
+        bits = bits - 1 if f > 0 else bits + 1
+        f = struct.unpack("f", struct.pack("I", bits))[0]
+    return f
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# NMS  (tv:ops/boxes.py:20-48, tv:models/detection/retinanet.py:559-561, cvpce/production.py:13-15)
+# ---------------------------------------------------------------------------------------------------------------------
+def nms_batched(boxes, scores, seg_offsets, max_n, iou_threshold=0.5, min_score=None, max_keep=0, box_scale=None,
+                want_boxes=False, want_scores=False):
+    """Greedy NMS over a CSR batch of images in one launch.
+
+    boxes f32[total,4], scores f32[total], seg_offsets i32[n_images+1] (device), max_n = host upper bound of candidates per image.
+    Returns (keep i64[total] local indices laid out per segment, keep_counts i32[n_images], kept_boxes|None, kept_scores|None).
+    No host synchronisation."""
+    _need_cuda("nms_batched", boxes, scores, seg_offsets, box_scale)
+    boxes = boxes.contiguous().float()
+    scores = scores.contiguous().float()
+    seg_offsets = seg_offsets.contiguous().to(torch.int32)
+    n_images = seg_offsets.numel() - 1
+    total = boxes.shape[0]
+    keep = torch.empty(total, dtype=torch.int64, device=boxes.device)
+    counts = torch.empty(n_images, dtype=torch.int32, device=boxes.device)
+    kept_boxes = torch.empty((total, 4), dtype=torch.float32, device=boxes.device) if want_boxes else None
+    kept_scores = torch.empty(total, dtype=torch.float32, device=boxes.device) if want_scores else None
+    if box_scale is not None:
+        box_scale = box_scale.contiguous().float()
+    lib = _lib.load()
+    rc = lib.cvpce_nms_batched(_ptr(boxes), _ptr(scores), _ptr(seg_offsets), n_images, int(max_n),
+                               threshold_as_cpu_op(float(iou_threshold)),
+                               float("-inf") if min_score is None else float(min_score), int(max_keep),
+                               _ptr(keep), _ptr(counts), _ptr(box_scale), _ptr(kept_boxes), _ptr(kept_scores), _stream())
+    _lib.check(rc, "cvpce_nms_batched")
+    return keep, counts, kept_boxes, kept_scores
+
+
+def nms(boxes, scores, iou_threshold):
+    """Drop-in for torchvision.ops.nms(boxes, scores, iou_threshold) -> int64[K] (one D2H read of the count)."""
+    _need_cuda("nms", boxes, scores)
+    n = boxes.shape[0]
+    if n == 0:
+        return torch.empty(0, dtype=torch.int64, device=boxes.device)
+    seg = torch.tensor([0, n], dtype=torch.int32, device=boxes.device)
+    keep, counts, _, _ = nms_batched(boxes, scores, seg, n, iou_threshold)
+    return keep[: int(counts.item())]
+
+
+def batched_nms(boxes, scores, idxs, iou_threshold):
+    """Drop-in for torchvision.ops.batched_nms (tv:ops/boxes.py:51-103): per-class NMS through the coordinate-offset
+    trick torchvision itself uses on CUDA (single-class GLN input: the offset is 0)."""
+    _need_cuda("batched_nms", boxes, scores, idxs)
+    if boxes.numel() == 0:
+        return torch.empty((0,), dtype=torch.int64, device=boxes.device)
+    max_coordinate = boxes.max()
+    offsets = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
+    return nms(boxes + offsets[:, None], scores, iou_threshold)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# crop + pad + resize  (cvpce/production.py:20, cvpce/datautils.py:234-239, utils.py:280-281, classification.py:41-44)
+# ---------------------------------------------------------------------------------------------------------------------
+def make_image_table(images):
+    """images: list of CUDA f32 [3,H,W] tensors (pixel stride 1) or one [n,3,H,W] tensor -> i64[n,5] device table.
+    The caller must keep `images` alive while the table is used."""
+    if isinstance(images, torch.Tensor):
+        images = [images] if images.dim() == 3 else list(images.unbind(0))
+    rows = []
+    for im in images:
+        _need_cuda("make_image_table", im)
+        if im.dtype != torch.float32 or im.dim() != 3 or im.shape[0] != 3 or im.stride(2) != 1:
+            raise RuntimeError("make_image_table: images must be float32 [3,H,W] with unit pixel stride")
+        rows.append([im.data_ptr(), im.shape[1], im.shape[2], im.stride(0), im.stride(1)])
+    return torch.tensor(rows, dtype=torch.int64).to(images[0].device, non_blocking=True)
+
+
+def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, antialias=True, pad_value=0.5, affine=None,
+                out_dtype=torch.float32, channels_last=False, return_valid=False):
+    """All crops of a batch in one launch. boxes f32[K,4] (device) -> [K,3,S,S] (or a channels_last view of [K,S,S,3])."""
+    _need_cuda("crop_resize", image_table, boxes, box_image_idx)
+    boxes = boxes.contiguous().float()
+    K = boxes.shape[0]
+    S = int(size)
+    dt = F32 if out_dtype == torch.float32 else BF16
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise RuntimeError("crop_resize: out_dtype must be float32 or bfloat16")
+    if channels_last:
+        out = torch.empty((K, S, S, 3), dtype=out_dtype, device=boxes.device)
+    else:
+        out = torch.empty((K, 3, S, S), dtype=out_dtype, device=boxes.device)
+    valid = torch.empty(K, dtype=torch.int32, device=boxes.device) if return_valid else None
+    if box_image_idx is not None:
+        box_image_idx = box_image_idx.contiguous().to(torch.int32)
+    aff = None
+    if affine is not None:
+        aff = (ctypes.c_float * 6)(*[float(v) for v in affine])
+    if K > 0:
+        rc = _lib.load().cvpce_crop_resize(_ptr(image_table), int(n_images), _ptr(boxes), _ptr(box_image_idx), K, S,
+                                           1 if antialias else 0, float(pad_value),
+                                           ctypes.cast(aff, ctypes.c_void_p) if aff is not None else None, dt,
+                                           NHWC if channels_last else NCHW, _ptr(out), _ptr(valid), _stream())
+        _lib.check(rc, "cvpce_crop_resize")
+    if channels_last:
+        out = out.permute(0, 3, 1, 2)  # logical NCHW, physical NHWC (torch.channels_last)
+    return (out, valid) if return_valid else out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# region max-pool embedding  (cvpce/models/classification.py:46-51, :79-85)
+# ---------------------------------------------------------------------------------------------------------------------
+def rmac_regions(H, W, levels):
+    buf = (ctypes.c_int32 * (4 * 64))()
+    n = _lib.load().cvpce_rmac_regions(int(H), int(W), int(levels), ctypes.cast(buf, ctypes.c_void_p), 64)
+    return [tuple(buf[4 * i: 4 * i + 4]) for i in range(min(n, 64))]
+
+
+def region_pool_embed(feats, regions=None, per_region_l2=False, final_l2=True, eps=1e-8, out=None):
+    """feats: list of CUDA [B,C,H,W] maps (f32 or bf16, any strides) -> f32[B, sum C].
+    regions: None (MAC: whole map) or a list (per map) of lists of (y0,x0,y1,x1)."""
+    _need_cuda("region_pool_embed", *feats)
+    B = feats[0].shape[0]
+    dtype = feats[0].dtype
+    if dtype not in (torch.float32, torch.bfloat16) or any(f.dtype != dtype or f.shape[0] != B or f.dim() != 4 for f in feats):
+        raise RuntimeError("region_pool_embed: maps must be 4-d, share batch size and dtype (float32 or bfloat16)")
+    D = sum(f.shape[1] for f in feats)
+    if out is None:
+        out = torch.empty((B, D), dtype=torch.float32, device=feats[0].device)
+    maps = (_lib.FeatureMap * len(feats))()
+    for i, f in enumerate(feats):
+        maps[i] = _lib.FeatureMap(f.data_ptr(), f.shape[1], f.shape[2], f.shape[3], f.stride(0), f.stride(1), f.stride(2), f.stride(3))
+    rg = nr = None
+    if regions is not None:
+        flat = [int(v) for per_map in regions for r in per_map for v in r]
+        rg = (ctypes.c_int32 * len(flat))(*flat)
+        nr = (ctypes.c_int32 * len(regions))(*[len(r) for r in regions])
+    rc = _lib.load().cvpce_region_pool_embed(maps, len(feats), F32 if dtype == torch.float32 else BF16, B,
+                                             ctypes.cast(rg, ctypes.c_void_p) if rg is not None else None,
+                                             ctypes.cast(nr, ctypes.c_void_p) if nr is not None else None,
+                                             1 if per_region_l2 else 0, 1 if final_l2 else 0, float(eps), _ptr(out),
+                                             out.stride(0), _stream())
+    _lib.check(rc, "cvpce_region_pool_embed")
+    return out
+
+
+def l2norm_rows_(x, eps=1e-8):
+    _need_cuda("l2norm_rows_", x)
+    if x.dtype != torch.float32 or x.dim() != 2 or x.stride(1) != 1:
+        raise RuntimeError("l2norm_rows_: expected float32 [B,D] with unit column stride")
+    rc = _lib.load().cvpce_l2norm_rows(_ptr(x), x.shape[0], x.shape[1], x.stride(0), float(eps), _stream())
+    _lib.check(rc, "cvpce_l2norm_rows")
+    return x
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# cosine similarity + top-k  (cvpce/models/classification.py:87-95)
+# ---------------------------------------------------------------------------------------------------------------------
+def rows_prepare(x, normalize=True, eps=1e-8, want_bf16=True):
+    """f32[R,D] -> (bf16[R,D] of x/max(||x||,eps) (or a plain cast), inv_norm f32[R])."""
+    _need_cuda("rows_prepare", x)
+    x = x.contiguous().float()
+    R, D = x.shape
+    xb = torch.empty((R, D), dtype=torch.bfloat16, device=x.device) if want_bf16 else None
+    inv = torch.empty(R, dtype=torch.float32, device=x.device)
+    rc = _lib.load().cvpce_rows_prepare(_ptr(x), R, D, 1 if normalize else 0, float(eps), _ptr(xb), _ptr(inv), _stream())
+    _lib.check(rc, "cvpce_rows_prepare")
+    return xb, inv
+
+
+def sim_topk_f32(queries, gallery, k=1, idx_base=0, normalize=True, eps=1e-8):
+    """Exact-fp32 CUDA-core path: (similarity f32[Q,k], index i64[Q,k])."""
+    _need_cuda("sim_topk_f32", queries, gallery)
+    q = queries.contiguous().float()
+    g = gallery.contiguous().float()
+    Q, D = q.shape
+    G = g.shape[0]
+    s = torch.empty((Q, k), dtype=torch.float32, device=q.device)
+    i = torch.empty((Q, k), dtype=torch.int64, device=q.device)
+    rc = _lib.load().cvpce_sim_topk_f32(_ptr(q), _ptr(g), Q, G, D, int(k), int(idx_base), 1 if normalize else 0, float(eps),
+                                        _ptr(s), _ptr(i), _stream())
+    _lib.check(rc, "cvpce_sim_topk_f32")
+    return s, i
+
+
+def sim_topk_workspace_bytes(Q, G, D, k):
+    return int(_lib.load().cvpce_sim_topk_workspace_bytes(int(Q), int(G), int(D), int(k)))
+
+
+def sim_topk(q_bf16, g_bf16, k=1, idx_base=0, q_f32=None, g_f32=None, q_inv_norm=None, g_inv_norm=None, workspace=None):
+    """tcgen05 path: bf16 operands [Q,D], [G,D]; with q_f32/g_f32 the candidates are re-scored in exact fp32 (parity mode).
+    Returns (similarity f32[Q,k], index i64[Q,k])."""
+    _need_cuda("sim_topk", q_bf16, g_bf16, q_f32, g_f32, q_inv_norm, g_inv_norm, workspace)
+    if q_bf16.dtype != torch.bfloat16 or g_bf16.dtype != torch.bfloat16 or not q_bf16.is_contiguous() or not g_bf16.is_contiguous():
+        raise RuntimeError("sim_topk: operands must be contiguous bfloat16 [rows, D]")
+    Q, D = q_bf16.shape
+    G = g_bf16.shape[0]
+    need = sim_topk_workspace_bytes(Q, G, D, k)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty(max(need, 16), dtype=torch.uint8, device=q_bf16.device)
+    s = torch.empty((Q, k), dtype=torch.float32, device=q_bf16.device)
+    i = torch.empty((Q, k), dtype=torch.int64, device=q_bf16.device)
+    for t in (q_f32, g_f32):
+        if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
+            raise RuntimeError("sim_topk: q_f32 / g_f32 must be contiguous float32")
+    rc = _lib.load().cvpce_sim_topk(_ptr(q_bf16), _ptr(g_bf16), Q, G, D, int(k), int(idx_base), _ptr(q_f32), _ptr(g_f32),
+                                    _ptr(q_inv_norm), _ptr(g_inv_norm), _ptr(s), _ptr(i), _ptr(workspace),
+                                    workspace.numel() * workspace.element_size(), _stream())
+    _lib.check(rc, "cvpce_sim_topk")
+    return s, i
+
+
+def topk_merge(scores, idx):
+    """scores f32[W,Q,k], idx i64[W,Q,k] (global indices) -> merged (f32[Q,k], i64[Q,k])."""
+    _need_cuda("topk_merge", scores, idx)
+    scores = scores.contiguous().float()
+    idx = idx.contiguous().to(torch.int64)
+    W, Q, k = scores.shape
+    s = torch.empty((Q, k), dtype=torch.float32, device=scores.device)
+    i = torch.empty((Q, k), dtype=torch.int64, device=scores.device)
+    rc = _lib.load().cvpce_topk_merge(_ptr(scores), _ptr(idx), W, Q, k, _ptr(s), _ptr(i), _stream())
+    _lib.check(rc, "cvpce_topk_merge")
+    return s, i
+
+
+def gpu_kernel_launch_count():
+    """Not tracked by the library; bench.py counts launches from the calls it makes."""
+    return math.nan

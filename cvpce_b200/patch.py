@@ -1,0 +1,89 @@
+"""Drop-in patchers: swap the hot-path call sites of an imported, unmodified reference (and of torchvision's RetinaNet
+post-processing) for the sm_100a implementations.  Nothing in /root/reference is edited; see INTEGRATION.md.
+
+    import cvpce, cvpce_b200.patch
+    cvpce_b200.patch.apply(cvpce)      # idempotent; cvpce_b200.patch.revert() undoes it
+"""
+import sys
+
+import torch
+
+from . import classification, datautils, ops, production
+
+_saved = []
+
+
+def _swap(obj, name, new):
+    _saved.append((obj, name, getattr(obj, name)))
+    setattr(obj, name, new)
+
+
+def _batched_nms(boxes, scores, idxs, iou_threshold):
+    if boxes.is_cuda:
+        return ops.batched_nms(boxes, scores, idxs, iou_threshold)
+    raise RuntimeError("cvpce_b200.patch: batched_nms called with CPU tensors; the B200 path has no CPU fallback")
+
+
+def _macvgg_forward(self, x, eps=1e-8):
+    from torchvision.transforms import functional as ttf
+    x = ttf.normalize(x, classification.NORM_MEAN, classification.NORM_STD)
+    f4 = self.block1(x)
+    f5 = self.block2(f4)
+    return ops.region_pool_embed([f4, f5], eps=eps)
+
+
+def _macresnet_forward(self, x, eps=1e-8):
+    feats = []
+    for b in self.blocks:
+        x = b(x)
+        feats.append(x)
+    return ops.region_pool_embed(feats, eps=eps)
+
+
+def _generate_proposals_and_images(self, image):
+    boxes = self.generate_proposals(image)
+    S = datautils.CLASSIFICATION_IMAGE_SIZE
+    if not len(boxes):
+        return boxes, torch.empty((0, 3, S, S))
+    return boxes, datautils.crops_for_classification(image.to(boxes.device), boxes)
+
+
+def _resize_for_classification(img):
+    if not img.is_cuda:
+        raise RuntimeError("cvpce_b200.patch: resize_for_classification needs a CUDA image; no CPU fallback")
+    return datautils.resize_for_classification(img)
+
+
+def _classify(self, images, return_embedding=False):
+    return production.Classifier.classify(self, images, return_embedding)
+
+
+def apply(ref=None):
+    """Patch the reference package `ref` (default: sys.modules['cvpce']) and torchvision's RetinaNet NMS call site."""
+    if _saved:
+        return
+    ref = ref or sys.modules.get("cvpce")
+    from torchvision.models.detection import retinanet
+    _swap(retinanet.box_ops, "batched_nms", _batched_nms)                       # tv:retinanet.py:560
+    if ref is None:
+        return
+    rc, rp, rd = ref.models.classification, ref.production, ref.datautils
+    _swap(rc, "nearest_neighbors", classification.nearest_neighbors)            # classification.py:90
+    _swap(rp, "nearest_neighbors", classification.nearest_neighbors)            # production.py:6 (from-import alias)
+    if hasattr(ref, "utils") and hasattr(ref.utils, "nearest_neighbors"):
+        _swap(ref.utils, "nearest_neighbors", classification.nearest_neighbors) # utils.py:20
+    _swap(rc.MACVGG, "forward", _macvgg_forward)                                # classification.py:38-51
+    _swap(rc.MACResNet, "forward", _macresnet_forward)                          # classification.py:78-85
+    _swap(rd, "resize_for_classification", _resize_for_classification)          # datautils.py:234
+    _swap(rp.ProposalGenerator, "generate_proposals_and_images", _generate_proposals_and_images)  # production.py:16
+    # Classifier.classify keeps its signature; the patched version embeds all crops, searches once, syncs once
+    rp.Classifier.embed = production.Classifier.embed
+    rp.Classifier.prepared_gallery = production.Classifier.prepared_gallery
+    rp.Classifier._prepared = None
+    _swap(rp.Classifier, "classify", _classify)                                 # production.py:57
+
+
+def revert():
+    while _saved:
+        obj, name, old = _saved.pop()
+        setattr(obj, name, old)

@@ -1,0 +1,173 @@
+/*
+ * cvpce_b200.h -- C ABI of the B200-native (sm_100a) proposal -> product classification hot path.
+ *
+ * This is the drop-in boundary: every entry point replaces one Python/torch call site of the reference
+ * (laitalaj/cvpce, paths relative to the reference root; "tv:" = torchvision, a third-party dependency of it).
+ * Plain pointers and sizes only; no torch types.  All pointers are DEVICE pointers unless marked [host].
+ * Every call is stream-ordered on `stream` (a cudaStream_t passed as void*), never synchronises the device,
+ * never allocates or frees caller-visible memory and never falls back to the CPU.
+ *
+ * Return value: 0 (CVPCE_OK) or a cvpce_status code; cvpce_last_error() gives a thread-local message.
+ * Empty inputs (0 boxes / crops / queries) are valid and return CVPCE_OK without launching.
+ */
+#ifndef CVPCE_B200_H
+#define CVPCE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CVPCE_B200_VERSION 100
+
+#if defined(__GNUC__)
+#define CVPCE_API __attribute__((visibility("default")))
+#else
+#define CVPCE_API
+#endif
+
+typedef enum cvpce_status {
+  CVPCE_OK = 0,
+  CVPCE_ERR_INVALID_ARG = 1,   /* null pointer, negative size, misaligned pointer, unsupported enum value */
+  CVPCE_ERR_UNSUPPORTED = 2,   /* shape outside what the kernels implement (message says which limit) */
+  CVPCE_ERR_CUDA = 3,          /* a CUDA runtime / driver call failed (message carries cudaGetErrorString) */
+  CVPCE_ERR_NO_DEVICE = 4,     /* no sm_100 device is current: there is NO CPU fallback */
+  CVPCE_ERR_WORKSPACE = 5      /* workspace pointer null or smaller than *_workspace_bytes() */
+} cvpce_status;
+
+typedef enum cvpce_dtype { CVPCE_F32 = 0, CVPCE_BF16 = 1 } cvpce_dtype;
+typedef enum cvpce_layout { CVPCE_NCHW = 0, CVPCE_NHWC = 1 } cvpce_layout;
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+CVPCE_API const char* cvpce_last_error(void);
+/* CVPCE_B200_VERSION the library was built from. */
+CVPCE_API int cvpce_version(void);
+/* CVPCE_OK iff the current CUDA device is compute capability 10.x (B200); else CVPCE_ERR_NO_DEVICE. */
+CVPCE_API int cvpce_device_check(void);
+/* Frees lazily created module state (TMA descriptor cache). Safe to call more than once. */
+CVPCE_API int cvpce_shutdown(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * a1 + a2  Batched greedy IoU-NMS.
+ * Replaces: tv:models/detection/retinanet.py:559-561  box_ops.batched_nms(boxes, scores, labels, nms_thresh)
+ *           followed by keep[:detections_per_img]  (reached from cvpce/models/proposals.py:176-177), i.e.
+ *           tv:ops/boxes.py:20-48 torch.ops.torchvision.nms for the single-class GLN detector; and, optionally,
+ *           the confidence filter res['boxes'][res['scores'] > thr] of cvpce/production.py:13-15.
+ *
+ * Semantics (bit-exact with the torchvision CPU op): candidates of one image are visited in (score descending,
+ * index ascending) order (stable sort; NaN scores first); candidate j is suppressed iff an earlier KEPT candidate
+ * i has  inter / (area_i + area_j - inter) > iou_threshold  evaluated in IEEE fp32 without contraction, with
+ * area = (x2-x1)*(y2-y1) (no +1) and inter = max(0,.)*max(0,.); 0/0 is NaN and does not suppress.
+ * `iou_threshold` is compared as fp32; pass the double threshold rounded toward -inf to reproduce the CPU op's
+ * float-vs-double comparison (identical for 0.5, the only value cvpce uses).
+ * `min_score`: candidates with score <= min_score are dropped (pass -INFINITY to disable); because kept boxes are
+ * in descending score order this equals the reference's post-NMS filter.  `max_keep` <= 0 means unlimited.
+ *
+ * boxes   f32 [total,4] xyxy, 16-byte aligned; scores f32 [total]; seg_offsets i32 [n_images+1] (CSR, device).
+ * max_n   [host] upper bound of candidates per image (<= CVPCE_NMS_MAX_N); an image exceeding it gets
+ *         keep_counts[b] = -1.
+ * keep    i64 [total]: for image b the kept LOCAL indices (0-based within the segment, score-descending) are
+ *         written at keep[seg_offsets[b] ...]; keep_counts i32 [n_images].
+ * kept_boxes  (nullable) f32 [total,4]: the kept boxes in the same positions, multiplied by box_scale
+ *         (nullable f32 [n_images,2] = (x ratio, y ratio), the fp32 multiply of tv:models/detection/transform.py:306-319).
+ * kept_scores (nullable) f32 [total].
+ */
+#define CVPCE_NMS_MAX_N 8192
+CVPCE_API int cvpce_nms_batched(const float* boxes, const float* scores, const int32_t* seg_offsets, int n_images, int max_n,
+                      float iou_threshold, float min_score, int max_keep,
+                      int64_t* keep, int32_t* keep_counts,
+                      const float* box_scale, float* kept_boxes, float* kept_scores, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * a3 + a4 (+ a5, a6)  Batched ROI crop -> pad-to-square -> (antialiased) bilinear resize.
+ * Replaces: the per-box python loop  image[:, y1:y2, x1:x2]  over boxes.to(long) at cvpce/production.py:20
+ *           (same expression: classification_eval.py:24, detection_eval.py:29, production.py:111) and
+ *           cvpce/datautils.py:234-239 resize_for_classification (canvas filled with 0.5, crop at top-left,
+ *           ttf.resize to S x S); optionally fuses utils.scale_to_tanh (cvpce/utils.py:280-281, called at
+ *           production.py:63) and the MACVGG input normalisation (cvpce/models/classification.py:41-44) as a
+ *           per-channel affine y = x*a_c + b_c.
+ *
+ * image_table i64 [n_images,5] (device): {data pointer (f32, CHW, pixel stride 1), H, W, channel stride, row stride}
+ *             strides in elements.
+ * boxes f32 [K,4] xyxy in image pixels; coordinates are truncated toward zero (Tensor.to(long)) and then clamped to
+ *             the image like a python slice end; box_image_idx i32 [K] (nullable: all boxes belong to image 0).
+ * antialias   1: ATen _upsample_bilinear2d_aa (installed torchvision >= 0.17 default), 0: plain bilinear,
+ *             align_corners=False (torchvision 0.9, the version the reference pins).
+ * affine      [host] nullable f32[6] = {a_0,b_0,a_1,b_1,a_2,b_2}.
+ * out         [K,3,S,S] (NCHW) or [K,S,S,3] (NHWC) of out_dtype.
+ * valid       (nullable) i32 [K]: 1, or 0 for an empty crop (x2<=x1 or y2<=y1 after truncation, where the reference
+ *             raises); an empty crop's output is pad_value passed through the affine.
+ */
+CVPCE_API int cvpce_crop_resize(const int64_t* image_table, int n_images, const float* boxes, const int32_t* box_image_idx,
+                      int K, int S, int antialias, float pad_value, const float* affine,
+                      int out_dtype, int out_layout, void* out, int32_t* valid, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * a8 + a9  Region max-pool embedding: MAC (reference) or R-MAC (extension) + L2 normalisation.
+ * Replaces: x.amax(dim=(-2,-1)) x2, torch.cat, desc / norm(desc).clamp(min=eps) of
+ *           cvpce/models/classification.py:46-51 (MACVGG) and :79-85 (MACResNet).
+ *
+ * maps [host] n_maps (<= 4) feature maps of the same batch, each [B,C,H,W] with arbitrary element strides
+ *      (NCHW-contiguous and channels-last are the fast cases), dtype f32 or bf16.
+ * regions [host] i32 [sum_m n_regions[m], 4] = (y0,x0,y1,x1), end exclusive, in feature-map cells;
+ *      n_regions [host] i32 [n_maps]; both null => one whole-map region per map (MAC, the reference's mode).
+ * per_region_l2 0: region maxima of a map are summed as they are (with one region: the plain MAC descriptor);
+ *               1: each region vector is divided by max(||v||_2, eps) before the sum (R-MAC, Tolias et al. 2016).
+ * final_l2      1: out row = desc / max(||desc||_2, eps) over the concatenation of all maps (classification.py:51).
+ * out f32 [B, sum_m C_m] with row stride out_stride (elements).
+ */
+typedef struct cvpce_feature_map {
+  const void* data;
+  int32_t C, H, W;
+  int64_t stride_n, stride_c, stride_h, stride_w;
+} cvpce_feature_map;
+#define CVPCE_POOL_MAX_MAPS 4
+#define CVPCE_POOL_MAX_REGIONS 32
+CVPCE_API int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                            const int32_t* regions, const int32_t* n_regions,
+                            int per_region_l2, int final_l2, float eps,
+                            float* out, int64_t out_stride, void* stream);
+/* [host] R-MAC region grid of Tolias et al. for an H x W map and `levels` scales; returns the region count and
+ * writes up to max_regions (y0,x0,y1,x1) quadruples. */
+CVPCE_API int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, int max_regions);
+/* In-place row L2 normalisation x / max(||x||_2, eps); x f32 [B,D] with row stride `stride`. */
+CVPCE_API int cvpce_l2norm_rows(float* x, int B, int D, int64_t stride, float eps, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * a10 + a11  Cosine similarity + per-row top-k.
+ * Replaces: cvpce/models/classification.py:87-95  distance() = 1 - cosine_similarity and nearest_neighbors()
+ *           (gather [Q,G,D] x2, reduce, full argsort, [:, :k]).
+ * Result order: (cosine similarity descending == distance ascending, gallery index ascending on equal scores).
+ *
+ * cvpce_rows_prepare: one-time operand preparation (gallery at build_index time, queries per batch):
+ *   x f32 [R,D] -> x_bf16 [R,D] = bf16(x * inv_norm) and inv_norm f32 [R] = 1/max(||x||_2, eps) (normalize=1),
+ *   or a plain cast with inv_norm = 1 (normalize=0; rows already unit-norm, as MACVGG outputs are).
+ */
+CVPCE_API int cvpce_rows_prepare(const float* x, int64_t R, int D, int normalize, float eps,
+                       void* x_bf16, float* inv_norm, void* stream);
+/* tcgen05 path.  q_bf16 [Q,D], g_bf16 [G,D] bf16 row-major, 16-byte aligned, D % 64 == 0, 64 <= D <= 4096, 1 <= k <= 32.
+ * The kernel computes S = Q x G^T tile by tile on the tensor cores (TMA-fed, fp32 accumulators in TMEM) and keeps a
+ * per-row candidate list in registers; S never reaches HBM.  When q_f32/g_f32 are given (parity mode), the k' >= k + 8
+ * candidates of each row are re-scored in exact fp32 (score = dot(q,g) * q_inv_norm * g_inv_norm; inv norms nullable = 1)
+ * before the final selection, so indices match an fp32 reference; otherwise the bf16-operand scores are returned.
+ * idx_base is added to the gallery row index (gallery shards).  out_scores f32 [Q,k], out_idx i64 [Q,k].
+ * Rows with fewer than k gallery entries are padded with score -INFINITY and index -1. */
+CVPCE_API size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k);
+CVPCE_API int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                   const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                   float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream);
+/* CUDA-core fp32 path (any D >= 1, k <= 64): exact fp32 dot products, same ordering contract; used for tiny shapes and
+ * as the on-device cross-check of the tensor-core path.  normalize=1 divides by max(norm,eps) of both rows (distance()). */
+CVPCE_API int cvpce_sim_topk_f32(const float* q, const float* g, int Q, int G, int D, int k, int64_t idx_base,
+                       int normalize, float eps, float* out_scores, int64_t* out_idx, void* stream);
+/* Merge W per-shard results [W,Q,k] (scores f32, global idx i64) into the overall top-k per row with the same
+ * ordering contract (used after the NCCL all-gather of the gallery-sharded search). */
+CVPCE_API int cvpce_topk_merge(const float* scores, const int64_t* idx, int W, int Q, int k,
+                     float* out_scores, int64_t* out_idx, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CVPCE_B200_H */

@@ -1,0 +1,145 @@
+"""Writes tests/golden/*.npz by running the UNMODIFIED reference (through oracle/shim.py) and the compiled third-party ops
+it calls (torchvision.ops.nms / batched_nms, F.interpolate) on seeded synthetic inputs.
+
+Run in the authoring container only (needs /root/reference):   python -m oracle.make_golden
+Inputs are regenerated from numpy RandomState seeds by oracle/synth.py, so only the small outputs are stored.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+import torchvision
+
+from . import shim, synth
+
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def golden_nms():
+    cases = {}
+    for name, (boxes, scores, thr, per_img) in synth.nms_cases().items():
+        b, s = torch.from_numpy(boxes), torch.from_numpy(scores)
+        keep = torchvision.ops.nms(b, s, thr)
+        # the RetinaNet call site: batched_nms with a single class, then [:detections_per_img]  (tv:retinanet.py:559-561)
+        keep_b = torchvision.ops.batched_nms(b, s, torch.zeros(len(s), dtype=torch.int64), thr)[:per_img]
+        cases[name + "/keep"] = keep.numpy()
+        if torch.equal(keep[:per_img], keep_b):
+            cases[name + "/keep_postprocess"] = keep_b.numpy()
+        else:
+            # batched_nms' "vanilla" branch (CPU, numel > 4000) re-sorts the kept indices by score with an UNSTABLE sort:
+            # same set, same score sequence, but equal scores may come in another index order. Not stored as golden.
+            assert name == "random2000_ties" and torch.equal(s[keep[:per_img]], s[keep_b])
+    np.savez_compressed(os.path.join(OUT, "nms.npz"), **cases)
+    print("nms:", {k: v.shape for k, v in cases.items()})
+
+
+def golden_crops(ref):
+    out = {}
+    img = torch.from_numpy(synth.shelf_image(synth.CROP_IMAGE_SEED, *synth.CROP_IMAGE_HW))
+    boxes = torch.from_numpy(synth.crop_boxes())
+    for S in (256, 224):
+        ref.datautils.CLASSIFICATION_IMAGE_SIZE = S
+        pix = synth.sample_pixels(S)
+        vals = []
+        for x1, y1, x2, y2 in boxes.to(dtype=torch.long):  # production.py:20
+            r = ref.datautils.resize_for_classification(img[:, y1:y2, x1:x2])
+            vals.append(r.reshape(-1)[pix].numpy())
+        out["aa_S%d" % S] = np.stack(vals)
+    ref.datautils.CLASSIFICATION_IMAGE_SIZE = 256
+    # thesis-era semantics (torchvision 0.9: no antialias): same canvas, F.interpolate(antialias=False)
+    pix = synth.sample_pixels(256)
+    vals = []
+    for x1, y1, x2, y2 in boxes.to(dtype=torch.long):
+        c = img[:, y1:y2, x1:x2]
+        _, h, w = c.shape
+        L = max(h, w)
+        canvas = torch.full((3, L, L), 0.5)
+        canvas[:, :h, :w] = c
+        r = torch.nn.functional.interpolate(canvas[None], size=(256, 256), mode="bilinear", align_corners=False, antialias=False)[0]
+        vals.append(r.reshape(-1)[pix].numpy())
+    out["noaa_S256"] = np.stack(vals)
+    np.savez_compressed(os.path.join(OUT, "crops.npz"), **out)
+    print("crops:", {k: v.shape for k, v in out.items()})
+
+
+def golden_mac(ref):
+    out = {}
+    # (1) pooling + concat + L2 of MACVGG.forward on given feature maps: the trunk blocks are swapped for stand-ins that
+    # return seeded maps, so the reference's own forward (classification.py:46-51) does the pooling.
+    f4, f5 = synth.feature_maps()
+    enc = ref.models.classification.MACVGG(batch_norm=False)
+
+    class Give(torch.nn.Module):
+        def __init__(self, t):
+            super().__init__()
+            self.t = t
+
+        def forward(self, x):
+            return self.t
+
+    enc.block1, enc.block2 = Give(torch.from_numpy(f4)), Give(torch.from_numpy(f5))
+    out["mac_given_maps"] = enc(torch.zeros(f4.shape[0], 3, 8, 8)).numpy()
+    # (2) the whole encoder with seeded random-init VGG16 weights (no BN, as production uses): embeddings of seeded inputs
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = ref.models.classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    x = torch.from_numpy(synth.encoder_inputs())
+    with torch.no_grad():
+        out["macvgg_embeddings"] = enc(x).numpy()
+    w0 = enc.block1[0].weight.detach().reshape(-1)
+    out["macvgg_weight_probe"] = torch.cat([w0[:8], enc.block2[-2].weight.detach().reshape(-1)[:8]]).numpy()
+    np.savez_compressed(os.path.join(OUT, "mac.npz"), **out)
+    print("mac:", {k: v.shape for k, v in out.items()})
+
+
+def golden_nn(ref):
+    out = {}
+    nn = ref.models.classification.nearest_neighbors
+    a, q, expected = synth.nn_kat()
+    got = nn(torch.from_numpy(a), torch.from_numpy(q))[:, 0].numpy()
+    assert np.array_equal(got, expected), (got, expected)  # reference test/models/classification_test.py:7-28
+    out["kat_top1"] = got
+    for name, (Q, G, D, k, seed) in synth.NN_CASES.items():
+        g, qq = synth.nn_case(Q, G, D, seed)
+        out[name] = nn(torch.from_numpy(g), torch.from_numpy(qq), k).numpy()
+    np.savez_compressed(os.path.join(OUT, "nn.npz"), **out)
+    print("nn:", {k: v.shape for k, v in out.items()})
+
+
+def golden_classify(ref):
+    """Classifier.build_index + classify (production.py:36-74) on a seeded toy gallery, CPU devices."""
+    out = {}
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = ref.models.classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    gallery, queries = synth.classify_case()
+    cpu = torch.device("cpu")
+    clf = ref.production.Classifier(enc, synth.GalleryDataset(gallery), device=cpu, emb_device=cpu, batch_size=4,
+                                    num_workers=0, k=3)
+    res, emb = clf.classify(torch.from_numpy(queries), return_embedding=True)
+    out["gallery_embedding"] = clf.embedding.numpy()
+    out["query_embedding"] = emb.numpy()
+    out["labels"] = np.array([[int(a[1:]) for a in row] for row in res], dtype=np.int64)  # annotations are "g<i>"
+    np.savez_compressed(os.path.join(OUT, "classify.npz"), **out)
+    print("classify:", {k: v.shape for k, v in out.items()}, out["labels"].tolist())
+
+
+def main():
+    if not shim.available():
+        sys.exit("reference tree not present; golden vectors can only be regenerated in the authoring container")
+    os.makedirs(OUT, exist_ok=True)
+    warnings.simplefilter("ignore")
+    ref = shim.load()
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    golden_nms()
+    golden_crops(ref)
+    golden_mac(ref)
+    golden_nn(ref)
+    golden_classify(ref)
+    with open(os.path.join(OUT, "VERSIONS.txt"), "w") as f:
+        f.write("torch %s\ntorchvision %s\nnumpy %s\nreference commit 7509e7d (laitalaj/cvpce)\n" %
+                (torch.__version__, torchvision.__version__, np.__version__))
+
+
+if __name__ == "__main__":
+    main()

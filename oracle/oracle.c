@@ -1,0 +1,357 @@
+/*
+ * oracle.c -- CPU restatement of the reference's proposal -> product classification path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this; the product
+ * (cvpce_b200/) never does.  Plain C, fp32 arithmetic where the reference computes in fp32, compiled WITHOUT
+ * -ffast-math and with -ffp-contract=off so that the NMS decisions are the x86 IEEE ones.
+ *
+ * Each function cites the reference lines it follows (paths relative to the laitalaj/cvpce root; "tv:" = torchvision
+ * 0.26, "aten:" = PyTorch 2.11 ATen -- third-party dependencies whose compiled ops the reference calls; their source
+ * is not in the reference tree, so their published algorithms are restated here and PINNED against the compiled
+ * ops themselves by oracle/make_golden.py -> tests/golden/ and tests/test_oracle_golden.py).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define API __attribute__((visibility("default")))
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * NMS.  tv:ops/boxes.py:20-48 -> torch.ops.torchvision.nms (CPU kernel nms_kernel_impl): stable descending sort of
+ * the scores, areas = (x2-x1)*(y2-y1), greedy loop; j suppressed iff ovr = inter/(iarea + area_j - inter) > thr,
+ * with ovr in fp32 and thr a double.  Reached from tv:models/detection/retinanet.py:559-561 (batched_nms + [:N]).
+ * Returns the number of kept indices written to keep (score-descending order).
+ * --------------------------------------------------------------------------------------------------------------- */
+typedef struct { float s; int32_t i; } sortkey;
+
+static int cmp_desc_stable(const void* a, const void* b) {
+  const sortkey* x = (const sortkey*)a;
+  const sortkey* y = (const sortkey*)b;
+  const int xn = x->s != x->s, yn = y->s != y->s; /* NaN sorts first in torch's descending sort */
+  if (xn != yn) return xn ? -1 : 1;
+  if (!xn) {
+    if (x->s > y->s) return -1;
+    if (x->s < y->s) return 1;
+  }
+  return (x->i > y->i) - (x->i < y->i);
+}
+
+API int64_t oracle_nms(const float* boxes, const float* scores, int64_t n, double iou_threshold, int64_t* keep) {
+  if (n <= 0) return 0;
+  sortkey* order = (sortkey*)malloc(sizeof(sortkey) * (size_t)n);
+  float* areas = (float*)malloc(sizeof(float) * (size_t)n);
+  unsigned char* suppressed = (unsigned char*)calloc((size_t)n, 1);
+  for (int64_t i = 0; i < n; ++i) {
+    order[i].s = scores[i];
+    order[i].i = (int32_t)i;
+    areas[i] = (boxes[4 * i + 2] - boxes[4 * i + 0]) * (boxes[4 * i + 3] - boxes[4 * i + 1]);
+  }
+  qsort(order, (size_t)n, sizeof(sortkey), cmp_desc_stable);
+  int64_t nk = 0;
+  for (int64_t _i = 0; _i < n; ++_i) {
+    const int64_t i = order[_i].i;
+    if (suppressed[i]) continue;
+    keep[nk++] = i;
+    const float ix1 = boxes[4 * i], iy1 = boxes[4 * i + 1], ix2 = boxes[4 * i + 2], iy2 = boxes[4 * i + 3];
+    const float iarea = areas[i];
+    for (int64_t _j = _i + 1; _j < n; ++_j) {
+      const int64_t j = order[_j].i;
+      if (suppressed[j]) continue;
+      const float xx1 = ix1 > boxes[4 * j] ? ix1 : boxes[4 * j];
+      const float yy1 = iy1 > boxes[4 * j + 1] ? iy1 : boxes[4 * j + 1];
+      const float xx2 = ix2 < boxes[4 * j + 2] ? ix2 : boxes[4 * j + 2];
+      const float yy2 = iy2 < boxes[4 * j + 3] ? iy2 : boxes[4 * j + 3];
+      const float dw = xx2 - xx1, dh = yy2 - yy1;
+      const float w = dw > 0.f ? dw : 0.f;
+      const float h = dh > 0.f ? dh : 0.f;
+      const float inter = w * h;
+      const float uni = iarea + areas[j] - inter;
+      const float ovr = inter / uni;
+      if ((double)ovr > iou_threshold) suppressed[j] = 1;
+    }
+  }
+  free(order);
+  free(areas);
+  free(suppressed);
+  return nk;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Crop + pad + resize.  cvpce/production.py:20 (boxes.to(long); python slice image[:, y1:y2, x1:x2]) and
+ * cvpce/datautils.py:234-239 resize_for_classification: canvas [3,L,L] = 0.5, canvas[:, :h, :w] = crop,
+ * ttf.resize(canvas, (S,S)) -> F.interpolate(bilinear, align_corners=False, antialias) (tv:transforms/_functional_tensor.py:445-467).
+ * antialias=1: aten:native/cpu/UpSampleKernel.cpp separable_upsample_generic_Nd_kernel_impl with
+ *   HelperInterpBase::_compute_indices_min_size_weights_aa (bilinear filter): horizontal pass, then vertical pass.
+ * antialias=0: aten upsample_bilinear2d (area_pixel_compute_source_index, two taps per axis).
+ * Returns 0, or 1 when the crop is empty in both dimensions (the reference raises there); out is then filled with pad.
+ * --------------------------------------------------------------------------------------------------------------- */
+static int64_t slice_index(int64_t i, int64_t n) {
+  if (i < 0) { i += n; if (i < 0) i = 0; }
+  return i > n ? n : i;
+}
+
+static float aa_filter(float x) {
+  if (x < 0.f) x = -x;
+  return x < 1.f ? 1.f - x : 0.f;
+}
+
+/* weights for one output index; returns xsize, sets *xmin */
+static int aa_weights(int64_t i, int64_t input_size, float scale, float support, float* w, int max_size, int64_t* xmin_out) {
+  const float center = (float)((double)scale * ((double)i + 0.5));
+  const float invscale = (scale >= 1.0f) ? 1.0f / scale : 1.0f;
+  int64_t xmin = (int64_t)((double)(center - support) + 0.5);
+  if (xmin < 0) xmin = 0;
+  int64_t hi = (int64_t)((double)(center + support) + 0.5);
+  if (hi > input_size) hi = input_size;
+  int64_t xsize = hi - xmin;
+  if (xsize < 0) xsize = 0;
+  if (xsize > max_size) xsize = max_size;
+  float total = 0.f;
+  for (int64_t j = 0; j < xsize; ++j) {
+    const float x = (float)(((double)((float)(j + xmin) - center) + 0.5) * (double)invscale);
+    w[j] = aa_filter(x);
+    total += w[j];
+  }
+  const float norm = total != 0.f ? 1.0f / total : 0.f;
+  for (int64_t j = 0; j < xsize; ++j) w[j] *= norm;
+  *xmin_out = xmin;
+  return (int)xsize;
+}
+
+API int oracle_crop_resize(const float* image, int64_t H, int64_t W, int64_t stride_c, int64_t stride_h, const float* box,
+                           int S, int antialias, float pad, float* out /* [3,S,S] */) {
+  int64_t b[4];
+  for (int t = 0; t < 4; ++t) b[t] = (int64_t)box[t]; /* Tensor.to(torch.long) truncates toward zero */
+  const int64_t xs = slice_index(b[0], W), xe = slice_index(b[2], W);
+  const int64_t ys = slice_index(b[1], H), ye = slice_index(b[3], H);
+  const int64_t w = xe > xs ? xe - xs : 0, h = ye > ys ? ye - ys : 0;
+  const int64_t L = h > w ? h : w;
+  if (L == 0) {
+    for (int64_t i = 0; i < 3 * (int64_t)S * S; ++i) out[i] = pad;
+    return 1;
+  }
+  float* canvas = (float*)malloc(sizeof(float) * 3 * (size_t)L * (size_t)L);
+  for (int64_t i = 0; i < 3 * L * L; ++i) canvas[i] = pad;
+  for (int c = 0; c < 3; ++c)
+    for (int64_t y = 0; y < h; ++y)
+      memcpy(canvas + (c * L + y) * L, image + c * stride_c + (ys + y) * stride_h + xs, sizeof(float) * (size_t)w);
+  const float scale = (float)L / (float)S;
+  if (antialias) {
+    const float support = scale >= 1.0f ? scale : 1.0f;
+    const int max_size = (int)ceilf(support) * 2 + 1;
+    float* wts = (float*)malloc(sizeof(float) * (size_t)S * (size_t)max_size);
+    int64_t* mins = (int64_t*)malloc(sizeof(int64_t) * (size_t)S);
+    int* sizes = (int*)malloc(sizeof(int) * (size_t)S);
+    for (int o = 0; o < S; ++o) sizes[o] = aa_weights(o, L, scale, support, wts + (size_t)o * max_size, max_size, &mins[o]);
+    float* tmp = (float*)malloc(sizeof(float) * 3 * (size_t)L * (size_t)S); /* [3,L,S] after the horizontal pass */
+    for (int64_t cy = 0; cy < 3 * L; ++cy)
+      for (int o = 0; o < S; ++o) {
+        const float* src = canvas + cy * L + mins[o];
+        const float* wv = wts + (size_t)o * max_size;
+        float t = 0.f;
+        for (int j = 0; j < sizes[o]; ++j) t += src[j] * wv[j];
+        tmp[cy * S + o] = t;
+      }
+    for (int c = 0; c < 3; ++c)
+      for (int oy = 0; oy < S; ++oy) {
+        const float* wv = wts + (size_t)oy * max_size;
+        for (int ox = 0; ox < S; ++ox) {
+          float t = 0.f;
+          for (int i = 0; i < sizes[oy]; ++i) t += tmp[((int64_t)c * L + mins[oy] + i) * S + ox] * wv[i];
+          out[((int64_t)c * S + oy) * S + ox] = t;
+        }
+      }
+    free(tmp); free(sizes); free(mins); free(wts);
+  } else {
+    for (int oy = 0; oy < S; ++oy) {
+      float sy = scale * ((float)oy + 0.5f) - 0.5f;
+      if (sy < 0.f) sy = 0.f;
+      int64_t y0 = (int64_t)sy;
+      if (y0 > L - 1) y0 = L - 1;
+      const int64_t y1 = y0 + (y0 < L - 1 ? 1 : 0);
+      const float ly1 = sy - (float)y0, ly0 = 1.f - ly1;
+      for (int ox = 0; ox < S; ++ox) {
+        float sx = scale * ((float)ox + 0.5f) - 0.5f;
+        if (sx < 0.f) sx = 0.f;
+        int64_t x0 = (int64_t)sx;
+        if (x0 > L - 1) x0 = L - 1;
+        const int64_t x1 = x0 + (x0 < L - 1 ? 1 : 0);
+        const float lx1 = sx - (float)x0, lx0 = 1.f - lx1;
+        for (int c = 0; c < 3; ++c) {
+          const float* p = canvas + (int64_t)c * L * L;
+          out[((int64_t)c * S + oy) * S + ox] =
+              ly0 * (lx0 * p[y0 * L + x0] + lx1 * p[y0 * L + x1]) + ly1 * (lx0 * p[y1 * L + x0] + lx1 * p[y1 * L + x1]);
+        }
+      }
+    }
+  }
+  free(canvas);
+  return 0;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Region max-pool embedding.  cvpce/models/classification.py:46-51 (MACVGG: x.amax(dim=(-2,-1)) of two maps, cat,
+ * desc / norm(desc).clamp(min=eps)) and :79-85 (MACResNet).  With regions + per_region_l2 it is R-MAC
+ * (Tolias, Sicre, Jegou 2016: per region channel-wise max -> L2 -> sum -> L2), the north-star extension
+ * ("parity unpinned" by the reference: it has no R-MAC).
+ * feat: NCHW-contiguous fp32 maps.  regions: (y0,x0,y1,x1) per map, concatenated; n_regions NULL = whole map.
+ * --------------------------------------------------------------------------------------------------------------- */
+API void oracle_region_pool_embed(const float* const* feats, const int32_t* Cs, const int32_t* Hs, const int32_t* Ws, int n_maps,
+                                  int64_t B, const int32_t* regions, const int32_t* n_regions, int per_region_l2, int final_l2,
+                                  float eps, float* out /* [B, sum C] */) {
+  int64_t D = 0;
+  for (int m = 0; m < n_maps; ++m) D += Cs[m];
+  for (int64_t n = 0; n < B; ++n) {
+    float* orow = out + n * D;
+    int64_t col = 0;
+    const int32_t* rg = regions;
+    for (int m = 0; m < n_maps; ++m) {
+      const int C = Cs[m], H = Hs[m], W = Ws[m];
+      const int R = n_regions ? n_regions[m] : 1;
+      float* v = (float*)malloc(sizeof(float) * (size_t)C);
+      for (int c = 0; c < C; ++c) orow[col + c] = 0.f;
+      for (int r = 0; r < R; ++r) {
+        const int y0 = n_regions ? rg[4 * r] : 0, x0 = n_regions ? rg[4 * r + 1] : 0;
+        const int y1 = n_regions ? rg[4 * r + 2] : H, x1 = n_regions ? rg[4 * r + 3] : W;
+        double ss = 0.0;
+        for (int c = 0; c < C; ++c) {
+          const float* plane = feats[m] + ((n * C + c) * (int64_t)H) * W;
+          float mx = -INFINITY;
+          for (int y = y0; y < y1; ++y)
+            for (int x = x0; x < x1; ++x)
+              if (plane[y * W + x] > mx) mx = plane[y * W + x];
+          v[c] = mx;
+          ss += (double)mx * (double)mx;
+        }
+        float dn = 1.f;
+        if (per_region_l2) {
+          dn = (float)sqrt(ss);
+          if (dn < eps) dn = eps;
+        }
+        for (int c = 0; c < C; ++c) {
+          const float t = per_region_l2 ? v[c] / dn : v[c];
+          orow[col + c] = (r == 0) ? t : orow[col + c] + t;
+        }
+      }
+      free(v);
+      if (n_regions) rg += 4 * R;
+      col += C;
+    }
+    if (final_l2) {
+      double ss = 0.0;
+      for (int64_t c = 0; c < D; ++c) ss += (double)orow[c] * (double)orow[c];
+      float dn = (float)sqrt(ss);
+      if (dn < eps) dn = eps;
+      for (int64_t c = 0; c < D; ++c) orow[c] = orow[c] / dn;
+    }
+  }
+}
+
+/* R-MAC region grid (Tolias et al. 2016): scale l = 1..levels, region side floor(2*min(H,W)/(l+1)), regions spread
+ * uniformly along each axis.  Mirrors the host helper the library exports so both can be compared. */
+API int oracle_rmac_regions(int H, int W, int levels, int32_t* regions, int max_regions) {
+  int count = 0;
+  const int w = H < W ? H : W;
+  for (int l = 1; l <= levels; ++l) {
+    int side = (2 * w) / (l + 1);
+    if (side < 1) side = 1;
+    const int ny = (H == w) ? l : l + (int)((double)(H - w) / (double)w * (l + 1) / 2.0 + 0.5);
+    const int nx = (W == w) ? l : l + (int)((double)(W - w) / (double)w * (l + 1) / 2.0 + 0.5);
+    for (int iy = 0; iy < ny; ++iy) {
+      const int y0 = ny > 1 ? (int)((double)(H - side) * iy / (ny - 1)) : (H - side) / 2;
+      for (int ix = 0; ix < nx; ++ix) {
+        const int x0 = nx > 1 ? (int)((double)(W - side) * ix / (nx - 1)) : (W - side) / 2;
+        if (count < max_regions && regions) {
+          regions[4 * count] = y0; regions[4 * count + 1] = x0;
+          regions[4 * count + 2] = y0 + side; regions[4 * count + 3] = x0 + side;
+        }
+        ++count;
+      }
+    }
+  }
+  return count;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Cosine similarity + top-k.  cvpce/models/classification.py:87-95: distance = 1 - cosine_similarity(a, b),
+ * nearest_neighbors = distances.argsort(-1)[:, :k].  cosine_similarity (aten:native/Distance.cpp) =
+ * sum(a*b) / (max(||a||,eps) * max(||b||,eps)), eps = 1e-8.  Dot products are accumulated in DOUBLE here so the
+ * ranking is the mathematically exact one; the reference's argsort is not stable, so ties are resolved
+ * (similarity descending, gallery index ascending) -- the contract the CUDA path states.  normalize=0 skips the norms
+ * (rows already unit length, as MACVGG outputs are).  out_sim holds cosine similarities (= 1 - distance).
+ * --------------------------------------------------------------------------------------------------------------- */
+API void oracle_sim_topk(const float* q, const float* g, int64_t Q, int64_t G, int64_t D, int k, int normalize, double eps,
+                         double* out_sim /* [Q,k] */, int64_t* out_idx /* [Q,k] */) {
+  double* gn = (double*)malloc(sizeof(double) * (size_t)(G > 0 ? G : 1));
+  for (int64_t j = 0; j < G; ++j) {
+    double s = 0.0;
+    if (normalize) {
+      for (int64_t d = 0; d < D; ++d) s += (double)g[j * D + d] * (double)g[j * D + d];
+      s = sqrt(s);
+      if (s < eps) s = eps;
+    } else {
+      s = 1.0;
+    }
+    gn[j] = s;
+  }
+  for (int64_t i = 0; i < Q; ++i) {
+    double* ts = out_sim + i * k;
+    int64_t* ti = out_idx + i * k;
+    for (int t = 0; t < k; ++t) { ts[t] = -INFINITY; ti[t] = -1; }
+    double qn = 1.0;
+    if (normalize) {
+      double s = 0.0;
+      for (int64_t d = 0; d < D; ++d) s += (double)q[i * D + d] * (double)q[i * D + d];
+      qn = sqrt(s);
+      if (qn < eps) qn = eps;
+    }
+    const float* qi = q + i * D;
+    for (int64_t j = 0; j < G; ++j) {
+      const float* gj = g + j * D;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      int64_t d = 0;
+      for (; d + 3 < D; d += 4) {
+        a0 += (double)qi[d] * (double)gj[d];
+        a1 += (double)qi[d + 1] * (double)gj[d + 1];
+        a2 += (double)qi[d + 2] * (double)gj[d + 2];
+        a3 += (double)qi[d + 3] * (double)gj[d + 3];
+      }
+      for (; d < D; ++d) a0 += (double)qi[d] * (double)gj[d];
+      const double s = ((a0 + a1) + (a2 + a3)) / (qn * gn[j]);
+      if (ti[k - 1] < 0 || s > ts[k - 1]) {
+        int pos = k - 1;
+        while (pos > 0 && (ti[pos - 1] < 0 || ts[pos - 1] < s)) { ts[pos] = ts[pos - 1]; ti[pos] = ti[pos - 1]; --pos; }
+        ts[pos] = s;
+        ti[pos] = j;
+      }
+    }
+  }
+  free(gn);
+}
+
+/* fp32 variant used only as a timed CPU baseline (reference arithmetic type): Q x G^T in fp32 + top-k. */
+API void oracle_sim_topk_f32(const float* q, const float* g, int64_t Q, int64_t G, int64_t D, int k, float* out_sim,
+                             int64_t* out_idx) {
+  for (int64_t i = 0; i < Q; ++i) {
+    float* ts = out_sim + i * k;
+    int64_t* ti = out_idx + i * k;
+    for (int t = 0; t < k; ++t) { ts[t] = -INFINITY; ti[t] = -1; }
+    const float* qi = q + i * D;
+    for (int64_t j = 0; j < G; ++j) {
+      const float* gj = g + j * D;
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      int64_t d = 0;
+      for (; d + 7 < D; d += 8)
+        for (int u = 0; u < 8; ++u) acc[u] += qi[d + u] * gj[d + u];
+      for (; d < D; ++d) acc[0] += qi[d] * gj[d];
+      const float s = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+      if (ti[k - 1] < 0 || s > ts[k - 1]) {
+        int pos = k - 1;
+        while (pos > 0 && (ti[pos - 1] < 0 || ts[pos - 1] < s)) { ts[pos] = ts[pos - 1]; ti[pos] = ti[pos - 1]; --pos; }
+        ts[pos] = s;
+        ti[pos] = j;
+      }
+    }
+  }
+}

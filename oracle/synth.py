@@ -1,0 +1,185 @@
+"""Seeded synthetic inputs shared by the golden generator, the tests and bench.py.
+
+numpy RandomState only, so the same seed gives the same bytes in the authoring container and on the GPU box.
+"""
+from math import sqrt
+
+import numpy as np
+
+WEIGHT_SEED = 0            # torch.manual_seed before building the random-init VGG16 encoder
+CROP_IMAGE_SEED = 7
+CROP_IMAGE_HW = (384, 512)
+SHELF_HW = (1536, 2048)    # BASELINE.json configs 2-4: 2048x1536 shelves
+
+
+def shelf_image(seed, H, W):
+    return np.random.RandomState(seed).rand(3, H, W).astype(np.float32)
+
+
+def shelf_candidates(seed, H=SHELF_HW[0], W=SHELF_HW[1], n_products=200, duplicates=4):
+    """Scored candidate boxes as a GLN would hand them to NMS: n_products true boxes on a jittered shelf grid
+    (w in [60,400], h in [90,400] px), each with one primary candidate (jitter sigma 2 px, score U(0.6,1)) and
+    `duplicates` worse ones (sigma 6 px, score U(0.05,0.6)). Scores are distinct fp32. Returns (boxes f32[N,4], scores f32[N])."""
+    rs = np.random.RandomState(seed)
+    cols = int(np.ceil(np.sqrt(n_products * W / H)))
+    rows = int(np.ceil(n_products / cols))
+    cw, ch = W / cols, H / rows
+    boxes, scores = [], []
+    for i in range(n_products):
+        r, c = divmod(i, cols)
+        w = min(rs.uniform(60, 400), cw * 1.15)
+        h = min(rs.uniform(90, 400), ch * 1.15)
+        cx = (c + 0.5) * cw + rs.uniform(-0.1, 0.1) * cw
+        cy = (r + 0.5) * ch + rs.uniform(-0.1, 0.1) * ch
+        base = np.array([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2])
+        boxes.append(base + rs.normal(0, 2, 4))
+        scores.append(rs.uniform(0.6, 1.0))
+        for _ in range(duplicates):
+            boxes.append(base + rs.normal(0, 6, 4))
+            scores.append(rs.uniform(0.05, 0.6))
+    boxes = np.asarray(boxes, dtype=np.float32)
+    boxes[:, 0::2] = np.clip(boxes[:, 0::2], 0, W)
+    boxes[:, 1::2] = np.clip(boxes[:, 1::2], 0, H)
+    scores = np.asarray(scores, dtype=np.float32)
+    # make scores distinct in fp32 (re-draw collisions)
+    while len(np.unique(scores)) != len(scores):
+        _, first = np.unique(scores, return_index=True)
+        dup = np.setdiff1d(np.arange(len(scores)), first)
+        scores[dup] = rs.uniform(0.05, 0.6, len(dup)).astype(np.float32)
+    perm = rs.permutation(len(scores))
+    return boxes[perm], scores[perm]
+
+
+def random_boxes(seed, n, extent=1000.0, wh=(20.0, 140.0), tie_every=0):
+    rs = np.random.RandomState(seed)
+    xy = rs.uniform(0, extent, (n, 2))
+    sz = rs.uniform(wh[0], wh[1], (n, 2))
+    boxes = np.concatenate([xy, xy + sz], 1).astype(np.float32)
+    scores = rs.uniform(0, 1, n).astype(np.float32)
+    if tie_every:
+        scores[::tie_every] = scores[0]
+    return boxes, scores
+
+
+def nms_cases():
+    """name -> (boxes, scores, iou_threshold, detections_per_img)"""
+    cases = {}
+    cases["ties"] = (np.array([[0, 0, 10, 10]] * 3 + [[20, 20, 30, 30]] * 2, dtype=np.float32),
+                     np.array([.5, .5, .5, .7, .7], dtype=np.float32), 0.5, 1000)
+    cases["zero_area"] = (np.array([[5, 5, 5, 5], [5, 5, 5, 5], [0, 0, 10, 10], [1, 1, 1, 9]], dtype=np.float32),
+                          np.array([.9, .8, .7, .6], dtype=np.float32), 0.5, 1000)
+    cases["single"] = (np.array([[1, 2, 3, 4]], dtype=np.float32), np.array([.3], dtype=np.float32), 0.5, 1000)
+    # hand-made IoU values 0.81 / 0.64 / 1/1.44 in the spirit of reference test/metrics_test.py:5-21
+    cases["hand_iou"] = (np.array([[0, 0, 10, 10], [0, 0, 9, 9], [0, 0, 8, 8], [0, 0, 12, 12], [100, 100, 110, 110]], dtype=np.float32),
+                         np.array([.9, .8, .7, .6, .5], dtype=np.float32), 0.65, 1000)
+    b, s = random_boxes(11, 2000, tie_every=7)
+    cases["random2000_ties"] = (b, s, 0.5, 1000)
+    b, s = random_boxes(12, 5000)
+    cases["random5000"] = (b, s, 0.5, 1000)
+    b, s = random_boxes(13, 700, extent=300.0)
+    cases["dense700_thr03"] = (b, s, 0.3, 200)
+    b, s = shelf_candidates(100)
+    cases["shelf200"] = (b, s, 0.5, 200)
+    b, s = shelf_candidates(101, n_products=150)
+    cases["shelf150"] = (b, s, 0.5, 1000)
+    return cases
+
+
+def crop_boxes():
+    """Boxes on the CROP_IMAGE_HW image: up-sampling, down-sampling, 1-px strips, borders, whole image, fractional coords."""
+    H, W = CROP_IMAGE_HW
+    return np.array([
+        [100.7, 200.2, 200.9, 350.5],   # survey KAT: ints (100,200,200,350)
+        [0, 0, W, H],                   # whole image (down-sampling, L=512)
+        [10, 10, 11, 300],              # 1-px wide
+        [30, 50, 330, 51],              # 1-px tall
+        [300.5, 100.5, 500.2, 380.9],   # down/up mix, L=280
+        [50, 60, 90, 75],               # strong up-sampling
+        [W - 1, H - 1, W, H],           # single pixel at the corner
+        [5, 5, 405, 305],               # L=400 -> 256 down-sampling
+        [0, 0, 256, 256],               # identity scale
+        [17, 33, 274, 290],             # L=257
+        [200, 0, 520, 384],             # x2 beyond the image: python slice clamps
+        [123.9, 45.1, 223.2, 300.7],
+    ], dtype=np.float32)
+
+
+def sample_pixels(S, n=3072):
+    return np.random.RandomState(S).choice(3 * S * S, n, replace=False)
+
+
+def feature_maps():
+    rs = np.random.RandomState(21)
+    f4 = np.abs(rs.randn(5, 40, 12, 12)).astype(np.float32)
+    f5 = np.abs(rs.randn(5, 24, 6, 6)).astype(np.float32)
+    return f4, f5
+
+
+def encoder_inputs(n=4, S=64, seed=31):
+    return (np.random.RandomState(seed).rand(n, 3, S, S) * 2 - 1).astype(np.float32)
+
+
+def nn_kat():
+    """reference test/models/classification_test.py:8-25 (6 unit anchors in R^3, 7 queries, expected top-1)."""
+    a = np.array([[1, 0, 0], [1 / sqrt(3)] * 3, [-1 / sqrt(3)] * 3, [-1, 0, 0], [1 / sqrt(2), 0, 1 / sqrt(2)],
+                  [-1 / sqrt(2), 0, -1 / sqrt(2)]], dtype=np.float32)
+    q = np.array([[1 / sqrt(1.01), 0.1 / sqrt(1.01), 0], [0.9 / sqrt(2.02), 0, 1.1 / sqrt(2.02)], [-1, 0, 0], [1, 0, 0],
+                  [1 / sqrt(3)] * 3, [-1.1 / sqrt(2.02), 0, -0.9 / sqrt(2.02)], [-1, 0, 0]], dtype=np.float32)
+    return a, q, np.array([0, 4, 3, 0, 1, 5, 3], dtype=np.int64)
+
+
+# name -> (Q, G, D, k, seed)
+NN_CASES = {
+    "c1_like": (64, 180, 1024, 5, 41),      # BASELINE config 1/2 shape
+    "d512": (48, 1000, 512, 5, 42),
+    "small_odd": (7, 33, 100, 3, 43),       # D not a multiple of 64 -> fp32 path
+    "k_gt_1_wide": (16, 300, 256, 10, 44),
+}
+
+
+def unit_rows(rs, n, d, nonneg=True):
+    x = rs.randn(n, d)
+    if nonneg:
+        x = np.abs(x)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    return x.astype(np.float32)
+
+
+def nn_case(Q, G, D, seed):
+    rs = np.random.RandomState(seed)
+    return unit_rows(rs, G, D), unit_rows(rs, Q, D)
+
+
+def planted_queries(rs, gallery, Q, frac=0.1, noise=0.05):
+    """C5-style queries: `frac` of them are noisy copies of random gallery rows (planted neighbours), the rest random."""
+    G, D = gallery.shape
+    q = rs.randn(Q, D).astype(np.float32)
+    n_plant = int(Q * frac)
+    planted = rs.randint(0, G, n_plant)
+    q[:n_plant] = gallery[planted] + noise * rs.randn(n_plant, D).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return q.astype(np.float32), planted
+
+
+def classify_case():
+    rs = np.random.RandomState(51)
+    gallery = (rs.rand(10, 3, 64, 64) * 2 - 1).astype(np.float32)
+    queries = rs.rand(6, 3, 64, 64).astype(np.float32)
+    # make three queries near-copies of gallery items so the expected labels are meaningful
+    for qi, gi in ((0, 3), (2, 7), (5, 1)):
+        queries[qi] = np.clip((gallery[gi] + 1) / 2 + 0.01 * rs.randn(3, 64, 64), 0, 1)
+    return gallery, queries
+
+
+class GalleryDataset:
+    """Yields the (img[-1,1], raw img, categories, annotation) tuples Classifier.build_index expects (datautils.py:397-415)."""
+
+    def __init__(self, images):
+        import torch
+        self.images = [torch.from_numpy(im) for im in images]
+
+    def __len__(self):
+        return len(self.images)
+
+    def __getitem__(self, i):
+        return self.images[i], self.images[i], [], "g%d" % i
