@@ -1,0 +1,416 @@
+#!/usr/bin/env python
+"""bench.py -- proposal crops classified / second through the B200-native hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c5]
+
+A "step" is one pass of the whole hot path over one batch of synthetic shelf images:
+scored candidate boxes -> NMS -> crop/pad/resize -> VGG16 trunk (torch, not rebuilt: SURVEY §8 a7) -> MAC pool + L2 ->
+cosine top-k against the gallery.  Default workload = BASELINE.json configs[2] ("c3": 32 shelves of 2048x1536 with ~200
+products each per GPU, gallery 8192 x 1024): the largest single-GPU configuration; with N GPUs every rank processes its
+own 32 shelves (images are independent: weak scaling, no collective in the data path; configs[3] at N=8 -> 256 shelves).
+`value` is measured with inputs resident in HBM; `e2e` through the same public call with pinned HOST buffers (H2D of the
+shelf images and candidates, D2H of the result indices inside the timed region).
+
+--impl reference : the reference's own CPU implementation of the path (oracle/torch_port.py: the same torch/torchvision CPU
+ops in the same order; /root/reference itself cannot travel to the GPU box), all host threads, each step a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "proposal crops classified/sec"
+UNIT = "crops/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c5"])
+    ap.add_argument("--shelves", type=int, default=None, help="shelf images per GPU per step (c3: 32, c2: 1)")
+    ap.add_argument("--products", type=int, default=200)
+    ap.add_argument("--gallery", type=int, default=None)
+    ap.add_argument("--k", type=int, default=5)
+    ap.add_argument("--trunk", default="f32", choices=["f32", "bf16"], help="dtype of the torch VGG16 trunk")
+    ap.add_argument("--channels-last", action="store_true")
+    ap.add_argument("--trunk-batch", type=int, default=128)
+    ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
+    ap.add_argument("--queries", type=int, default=100000, help="c5 only")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-crops", type=int, default=32)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------------------ helpers
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.proc = None
+        self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+                power.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"hbm": float(p["hbm_gbs"]), "tensor_burst": float(p["bf16_tflops"]), "tensor_sustained": float(p["bf16_tflops_sustained"]),
+                "source": "MEASURED_PEAKS.json"}
+    except Exception:
+        return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    elif torch.cuda.is_available():
+        torch.cuda.set_device(0)
+    return world, rank, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms, world):
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+def sum_over_ranks(v, world):
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+    return v
+
+
+# ----------------------------------------------------------------------------------------------------- workload (c2/c3)
+def build_shelves(args, rank, n_shelves, device):
+    from cvpce_b200 import synth
+    H, W = synth.SHELF_HW
+    images, boxes, scores, sizes = [], [], [], []
+    for i in range(n_shelves):
+        gi = rank * n_shelves + i
+        gen = torch.Generator(device=device).manual_seed(100 + gi)
+        images.append(torch.rand((3, H, W), generator=gen, device=device))
+        b, s = synth.shelf_candidates(100 + gi, H, W, args.products)
+        boxes.append(b)
+        scores.append(s)
+        sizes.append(len(s))
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    return images, np.concatenate(boxes), np.concatenate(scores), seg, max(sizes)
+
+
+def build_encoder(args, device):
+    from cvpce_b200 import classification, synth
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).to(device)
+    if args.trunk == "bf16":
+        enc = enc.to(torch.bfloat16)
+    if args.channels_last:
+        enc = enc.to(memory_format=torch.channels_last)
+    return enc
+
+
+def build_gallery(G, D, device, seed=3):
+    gen = torch.Generator(device=device).manual_seed(seed)
+    g = torch.randn((G, D), generator=gen, device=device).abs_()
+    return g / g.norm(dim=1, keepdim=True)
+
+
+def run_ours_shelves(args, world, rank, local):
+    from cvpce_b200 import _lib, pipeline, classification
+    device = torch.device("cuda", local)
+    _lib.load()
+    peaks = measured_peaks()
+    n_shelves = args.shelves or (32 if args.workload == "c3" else 1)
+    G = args.gallery or (8192 if args.workload == "c3" else 180)
+    enc = build_encoder(args, device)
+    gallery = build_gallery(G, enc.embedding_size, device)
+    images, boxes_h, scores_h, seg_h, max_n = build_shelves(args, rank, n_shelves, device)
+    hp = pipeline.HotPath(enc, gallery, k=args.k, trunk_batch=args.trunk_batch,
+                          trunk_dtype=torch.float32 if args.trunk == "f32" else torch.bfloat16, channels_last=args.channels_last)
+    if args.sim == "f32":  # CUDA-core similarity instead of the tcgen05 kernel (debug / cross-check)
+        from cvpce_b200 import ops
+        ops_sim = ops.sim_topk
+
+        def sim_f32(qb, gb, k, base, q32, g32, qi, gi, workspace=None):
+            return ops.sim_topk_f32(q32, g32, k, base, normalize=True)
+        ops.sim_topk = sim_f32
+    boxes_d = torch.from_numpy(boxes_h).to(device)
+    scores_d = torch.from_numpy(scores_h).to(device)
+    seg_d = torch.from_numpy(seg_h).to(device)
+
+    # -------- device-resident timing ("value")
+    for _ in range(args.warmup):
+        out = hp.step(images, boxes_d, scores_d, seg_d, max_n)
+    K_crops = int(out["counts"].sum())
+    hp.launches = 0
+    hp.timer = pipeline.StageTimer()
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = hp.step(images, boxes_d, scores_d, seg_d, max_n)
+    e1.record()
+    barrier(world)
+    ms_total = max_over_ranks(e0.elapsed_time(e1), world)
+    clocks = sampler.stop() if sampler else None
+    launches = hp.launches
+    stages = hp.timer.summary()
+    hp.timer = pipeline._NoTimer()
+    total_crops = sum_over_ranks(float(K_crops), world)
+    value = total_crops * args.steps / (ms_total / 1e3)
+
+    # -------- end-to-end timing: pinned host inputs, H2D + D2H inside the timed region
+    images_h = [im.cpu().pin_memory() for im in images]
+    boxes_p, scores_p, seg_p = torch.from_numpy(boxes_h).pin_memory(), torch.from_numpy(scores_h).pin_memory(), torch.from_numpy(seg_h).pin_memory()
+    h2d = sum(im.numel() * 4 for im in images_h) + boxes_p.numel() * 4 + scores_p.numel() * 4 + seg_p.numel() * 4
+    del images
+
+    def e2e_step():
+        imgs = [im.to(device, non_blocking=True) for im in images_h]
+        o = hp.step(imgs, boxes_p.to(device, non_blocking=True), scores_p.to(device, non_blocking=True),
+                    seg_p.to(device, non_blocking=True), max_n)
+        idx = o["topk_idx"].cpu()
+        bx = o["boxes"].cpu()
+        return idx, bx
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        idx_h, bx_h = e2e_step()
+    d2h = idx_h.numel() * 8 + bx_h.numel() * 4 + n_shelves * 4
+    barrier(world)
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier(world)
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
+    e2e_value = total_crops * args.steps / (ms_e2e / 1e3)
+
+    # -------- per-kernel rooflines from the events recorded inside the timed region
+    kernels = {}
+    for name, d in stages.items():
+        ms = d["ms"] / d["launches"]
+        ent = {"launches_per_step": d["launches"] / args.steps, "avg_ms": round(ms, 4)}
+        if name == "sim_topk":
+            tf = d["flops"] / d["launches"] / (ms / 1e3) / 1e12
+            ent.update({"bound": "tensor", "achieved_tflops": round(tf, 2), "frac": round(tf / peaks["tensor_burst"], 4)})
+        else:
+            gbs = d["bytes"] / d["launches"] / (ms / 1e3) / 1e9
+            ent.update({"bound": "hbm", "achieved_gbs": round(gbs, 1), "frac": round(gbs / peaks["hbm"], 4),
+                        "algorithmic_bytes_per_launch": d["bytes"] / d["launches"]})
+        ent["share_of_step"] = round(d["ms"] / ms_total, 4)
+        kernels[name] = ent
+    ours_ms = sum(d["ms"] for d in stages.values())
+    dom = max((n for n in stages if n != "sim_topk"), key=lambda n: stages[n]["ms"])
+    dd = stages[dom]
+    dom_gbs = dd["bytes"] / dd["launches"] / (dd["ms"] / dd["launches"] / 1e3) / 1e9
+    roofline = {"kernel": dom, "bound": "hbm", "achieved": round(dom_gbs, 1), "peak": peaks["hbm"], "unit": "GB/s",
+                "frac": round(dom_gbs / peaks["hbm"], 4), "traffic": None, "peak_source": peaks["source"] + " (hbm_gbs, burst copy)"}
+
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.trunk == "f32" else "bf16", "data": "synthetic",
+        "config": {"workload": "%s: %d shelves 2048x1536 x ~%d products per GPU -> NMS(0.5, top200) -> 256x256 crops -> VGG16(random init)+MAC"
+                               " -> cosine top-%d vs %d x 1024 gallery" % (args.workload, n_shelves, args.products, args.k, G),
+                   "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16 (%s%s, tf32 convs %s)" % (
+                       args.trunk, ", channels_last" if args.channels_last else "", torch.backends.cudnn.allow_tf32),
+                   "similarity": "tcgen05 bf16 + exact fp32 re-score" if args.sim == "tc" else "cuda-core fp32",
+                   "l2": "inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9),
+                   "parallelism": "dp%d (independent images, no data-path collective)" % world},
+        "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": round(ms_e2e / args.steps, 3)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "kernels": kernels,
+        "own_kernels_share_of_step": round(ours_ms / ms_total, 4),
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_reference_rate(args, G, sample_crops=args.cpu_sample_crops, repeats=1)
+    return line
+
+
+# ------------------------------------------------------------------------------------------- reference / cpu baseline
+def cpu_reference_rate(args, G, sample_crops, repeats, warmup=0):
+    """Times the CPU port of the reference path (oracle/torch_port.py) on a bounded sample: one shelf's NMS, then the first
+    `sample_crops` surviving boxes through crop -> VGG16 -> MAC -> nearest_neighbors, on all host threads."""
+    from oracle import torch_port
+    from cvpce_b200 import synth
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    H, W = synth.SHELF_HW
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = torch_port.MACVGGPort().eval().requires_grad_(False)
+    gen = torch.Generator().manual_seed(3)
+    gallery = torch.randn((G, 1024), generator=gen).abs_()
+    gallery = gallery / gallery.norm(dim=1, keepdim=True)
+    image = torch.rand((3, H, W), generator=torch.Generator().manual_seed(100))
+    b, s = synth.shelf_candidates(100, H, W, args.products)
+    b, s = torch.from_numpy(b), torch.from_numpy(s)
+    nn_chunk = 4 if G > 1024 else None  # the reference form materialises Q*G*D*4 B twice; chunk queries to stay in memory
+    times = []
+    n = 0
+    for it in range(warmup + repeats):
+        t0 = time.perf_counter()
+        boxes, idx = torch_port.hot_path(enc, gallery, image, b, s, k=args.k, detections_per_img=200, max_crops=sample_crops,
+                                         batch_size=32, nn_chunk=nn_chunk)
+        dt = time.perf_counter() - t0
+        n = len(boxes)
+        if it >= warmup:
+            times.append(dt)
+    best = min(times)
+    return {"value": round(n / best, 3), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "1 shelf: NMS of %d candidates, first %d kept boxes -> crop -> VGG16 fp32 -> MAC -> nearest_neighbors vs %d x 1024"
+                      " (torch CPU ops of the reference, best of %d)" % (len(s), n, G, repeats),
+            "seconds_per_step": [round(t, 3) for t in times]}
+
+
+def run_reference(args, world, rank):
+    if rank != 0:
+        return None
+    G = args.gallery or (8192 if args.workload == "c3" else 180)
+    base = cpu_reference_rate(args, G, sample_crops=args.cpu_sample_crops, repeats=args.steps, warmup=args.warmup)
+    secs = base.pop("seconds_per_step")
+    n = args.cpu_sample_crops
+    value = n * len(secs) / sum(secs)
+    base["value"] = round(value, 3)
+    return {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(1e3 * sum(secs) / len(secs), 2), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "%s (bounded sample per step: %s)" % (args.workload, base["sample"])},
+            "cpu_baseline": base,
+            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# ----------------------------------------------------------------------------------------------------- workload c5
+def run_ours_c5(args, world, rank, local):
+    """BASELINE.json configs[4]: 1M x 512 gallery sharded over the ranks, 100k queries, cosine top-5, all-gather + merge.
+    Strong scaling: the gallery is fixed, each rank searches G/world rows for ALL queries."""
+    from cvpce_b200 import dist as cdist
+    device = torch.device("cuda", local)
+    peaks = measured_peaks()
+    G = args.gallery or 1_000_000
+    Q, D, k = args.queries, 512, args.k
+    searcher = cdist.ShardedGallery.synthetic(G, D, world, rank, device, seed=5)
+    q = cdist.synthetic_queries(Q, D, device, seed=6)
+    for _ in range(args.warmup):
+        sim, idx = searcher.search(q, k)
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        sim, idx = searcher.search(q, k)
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    clocks = sampler.stop() if sampler else None
+    flops = 2.0 * Q * G * D * args.steps
+    tf = flops / (ms / 1e3) / 1e12 / world
+    return {"metric": "gallery queries matched/sec (cosine top-%d)" % k, "value": round(Q * args.steps / (ms / 1e3), 1), "unit": "queries/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 operands, f32 accumulate + exact f32 re-score",
+            "data": "synthetic", "config": {"workload": "c5: %d x %d gallery sharded over %d GPU(s), %d queries, top-%d, all-gather merge" % (G, D, world, Q, k)},
+            "roofline": {"kernel": "sim_topk", "bound": "tensor", "achieved": round(tf, 1), "peak": peaks["tensor_sustained"], "unit": "TFLOP/s",
+                         "frac": round(tf / peaks["tensor_sustained"], 4), "traffic": None,
+                         "peak_source": peaks["source"] + " (bf16_tflops_sustained); includes prepare + re-score + merge time"},
+            "gpu_launches": searcher.launches, "clocks": clocks}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        rank = int(os.environ.get("RANK", "0"))
+        line = run_reference(args, world, rank)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    if not torch.cuda.is_available():
+        sys.exit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    world, rank, local = dist_setup(args)
+    if args.workload == "c5":
+        line = run_ours_c5(args, world, rank, local)
+    else:
+        line = run_ours_shelves(args, world, rank, local)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,8 +1,653 @@
-// placeholder until the tcgen05 kernel lands (replaced in the next commit)
+// Cosine similarity + fused per-row top-k on the sm_100a tensor cores (tcgen05 + TMEM + TMA).
+//
+// Replaces cvpce/models/classification.py:87-95 (distance / nearest_neighbors: gather two [Q,G,D] tensors, reduce, full
+// argsort) with S = Q x G^T computed tile by tile and reduced on the fly; S never reaches HBM.
+//
+// Kernel 1  sim_topk_tc_kernel   (one CTA per SM, 256 threads, warp-specialised)
+//   warp 0      TMA producer: 128B-swizzled K-major bf16 tiles of Q (128 x 64) and G (256 x 64) into a shared-memory ring
+//               (for D <= 512 the whole 128 x D query block is loaded once and stays resident; only G streams)
+//   warp 1      one elected thread issues tcgen05.mma (M=128, N=256, K=16, bf16 x bf16 -> f32) into TMEM; the 512 TMEM
+//               columns hold TWO 128x256 accumulators so the MMAs of tile n+1 overlap the epilogue of tile n
+//   warp 2      TMEM allocator
+//   warps 4-7   epilogue: tcgen05.ld gives every thread one complete query row of the tile (lane == row), so each thread
+//               keeps its row's running top-k' (sorted, in registers) with NO cross-thread traffic; a value is compared
+//               against the current k'-th score first, so the common case costs one compare per similarity
+//   grid = (query blocks of 128) x (gallery splits); each CTA writes its k' candidates per row to a small workspace.
+// Kernel 2  sim_select_kernel    (one warp per query row)
+//   merges the splits' candidates, re-scores the surviving k' in exact fp32 from the fp32 operands (parity mode) and
+//   writes the final top-k ordered by (similarity desc, gallery index asc).
 #include "common.cuh"
-namespace cvpce { void tma_cache_clear() {} }
-extern "C" size_t cvpce_sim_topk_workspace_bytes(int, int, int, int) { return 0; }
-extern "C" int cvpce_sim_topk(const void*, const void*, int, int, int, int, int64_t, const float*, const float*, const float*,
-                              const float*, float*, int64_t*, void*, size_t, void*) {
-  return cvpce::set_err(CVPCE_ERR_UNSUPPORTED, "sim_topk: tcgen05 path not built");
+#include <cuda.h>
+#include <math.h>
+#include <mutex>
+#include <unordered_map>
+
+namespace cvpce {
+
+// ------------------------------------------------------------------------------------------------------------------------
+// tile configuration
+// ------------------------------------------------------------------------------------------------------------------------
+constexpr int BM = 128;            // query rows per CTA (UMMA M)
+constexpr int BN = 256;            // gallery rows per tile (UMMA N)
+constexpr int BK = 64;             // bf16 elements per k-block = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int A_TILE_BYTES = BM * BK * 2;   // 16 KB
+constexpr int B_TILE_BYTES = BN * BK * 2;   // 32 KB
+constexpr int kStagesStream = 4;   // ring depth when A and B both stream (48 KB per stage)
+constexpr int kStagesResident = 3; // ring depth when A is resident (32 KB per stage)
+constexpr int kMaxResidentKB = 8;  // D <= 512
+constexpr int kTcThreads = 256;
+constexpr int kEpilogueWarp0 = 4;
+constexpr uint32_t kTmemCols = 512;
+
+// ------------------------------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, f32 accumulate, single CTA
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp receives row (lane base + t), columns [col, col+32)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows at a 128-byte pitch, 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);  // start address
+  d |= (uint64_t)0 << 16;                        // leading byte offset: unused for a single swizzle atom along K
+  d |= (uint64_t)(1024u >> 4) << 32;             // stride byte offset between 8-row groups
+  d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                        // layout type: SWIZZLE_128B
+  return d;
+}
+// Instruction descriptor for kind::f16: D=f32, A=B=bf16, both K-major, N=256, M=128.
+constexpr uint32_t kInstrDesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+// r[j] for a run-time j without spilling the register array to local memory: a 5-level select tree (31 SELs)
+__device__ __forceinline__ uint32_t pick32(const uint32_t (&r)[32], int j) {
+  uint32_t a[16], b[8], c[4], d[2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (j & 1) ? r[2 * i + 1] : r[2 * i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[2 * i + 1] : b[2 * i];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) d[i] = (j & 8) ? c[2 * i + 1] : c[2 * i];
+  return (j & 16) ? d[1] : d[0];
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// per-thread running top-KP, sorted descending, in registers.  Equal scores keep arrival order (= ascending index).
+// ------------------------------------------------------------------------------------------------------------------------
+template <int KP>
+struct TopList {
+  float s[KP];
+  int i[KP];
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int j = 0; j < KP; ++j) {
+      s[j] = -INFINITY;
+      i[j] = -1;
+    }
+  }
+  __device__ __forceinline__ float threshold() const { return s[KP - 1]; }
+  __device__ __forceinline__ void insert(float v, int idx) {  // requires v > s[KP-1]
+    s[KP - 1] = v;
+    i[KP - 1] = idx;
+#pragma unroll
+    for (int j = KP - 1; j > 0; --j) {
+      const bool sw = s[j] > s[j - 1];
+      const float ts = s[j], tp = s[j - 1];
+      const int ti = i[j], tq = i[j - 1];
+      s[j - 1] = sw ? ts : tp;
+      s[j] = sw ? tp : ts;
+      i[j - 1] = sw ? ti : tq;
+      i[j] = sw ? tq : ti;
+    }
+  }
+};
+
+struct TcParams {
+  int Q, G, D;
+  int n_tiles;          // ceil(G / BN)
+  int m_blocks;         // ceil(Q / BM)
+  int n_split;          // gallery splits (gridDim.x = m_blocks * n_split, m fastest)
+  int tiles_per_split;  // ceil(n_tiles / n_split)
+  float* cand_s;        // [Q, n_split, KP]
+  int* cand_i;
+};
+
+template <bool RESIDENT_A, int KP>
+__global__ void __launch_bounds__(kTcThreads, 1)
+sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_g, const TcParams p) {
+  constexpr int kStages = RESIDENT_A ? kStagesResident : kStagesStream;
+  constexpr int kStageBytes = RESIDENT_A ? B_TILE_BYTES : (A_TILE_BYTES + B_TILE_BYTES);
+  extern __shared__ __align__(1024) uint8_t smem_dyn[];
+  // 1024-byte alignment is required by the 128B swizzle atoms
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+  uint8_t* a_res = smem;                                                   // RESIDENT_A: [KB][128x64] tiles
+  uint8_t* ring = smem + (RESIDENT_A ? kMaxResidentKB * A_TILE_BYTES : 0);  // [kStages][kStageBytes]
+
+  __shared__ __align__(8) uint64_t full_bar[kStagesStream];
+  __shared__ __align__(8) uint64_t empty_bar[kStagesStream];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ __align__(8) uint64_t a_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_blk = blockIdx.x % p.m_blocks;
+  const int split = blockIdx.x / p.m_blocks;
+  const int t0 = split * p.tiles_per_split;
+  const int t1 = min(p.n_tiles, t0 + p.tiles_per_split);
+  const int KB = p.D / BK;
+  const int m0 = m_blk * BM;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_g);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], 4);  // one arrival per epilogue warp
+    }
+    mbar_init(&a_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(&tmem_base_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer =====================================================
+    if (lane == 0) {
+      if (RESIDENT_A) {
+        mbar_expect_tx(&a_full_bar, (uint32_t)(KB * A_TILE_BYTES));
+        for (int kb = 0; kb < KB; ++kb) tma_load_2d(a_res + kb * A_TILE_BYTES, &tmap_q, &a_full_bar, kb * BK, m0);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t0; t < t1; ++t) {
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], (uint32_t)kStageBytes);
+          uint8_t* st = ring + stage * kStageBytes;
+          if (!RESIDENT_A) {
+            tma_load_2d(st, &tmap_q, &full_bar[stage], kb * BK, m0);
+            tma_load_2d(st + A_TILE_BYTES, &tmap_g, &full_bar[stage], kb * BK, t * BN);
+          } else {
+            tma_load_2d(st, &tmap_g, &full_bar[stage], kb * BK, t * BN);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ====================================================== MMA issuer ======================================================
+    if (lane == 0) {
+      if (RESIDENT_A) {
+        mbar_wait(&a_full_bar, 0);
+        tc_fence_after();
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t acc_phase = 0;  // bit a = phase of accumulator a
+      for (int t = t0; t < t1; ++t) {
+        const int acc = (t - t0) & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((acc_phase >> acc) & 1u) ^ 1u);  // epilogue has drained this accumulator
+        acc_phase ^= 1u << acc;
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint8_t* st = ring + stage * kStageBytes;
+          const uint32_t a_addr = RESIDENT_A ? smem_u32(a_res + kb * A_TILE_BYTES) : smem_u32(st);
+          const uint32_t b_addr = RESIDENT_A ? smem_u32(st) : smem_u32(st + A_TILE_BYTES);
+          const uint64_t a_desc = make_smem_desc(a_addr);
+          const uint64_t b_desc = make_smem_desc(b_addr);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (address >> 4) field
+            umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), kInstrDesc, (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= kEpilogueWarp0) {
+    // ======================================================= epilogue =======================================================
+    const int ew = warp - kEpilogueWarp0;      // == warp % 4: the TMEM lane quadrant this warp may read
+    const int row = m0 + ew * 32 + lane;       // query row owned by this thread
+    TopList<KP> top;
+    top.init();
+    uint32_t acc_phase = 0;
+    for (int t = t0; t < t1; ++t) {
+      const int acc = (t - t0) & 1;
+      mbar_wait(&tmem_full_bar[acc], (acc_phase >> acc) & 1u);
+      acc_phase ^= 1u << acc;
+      tc_fence_after();
+      const int n0 = t * BN;
+      const int valid = min(BN, p.G - n0);  // columns beyond the gallery are TMA zero-fill: must not become candidates
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (c0 >= valid) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + (uint32_t)c0, r);
+        tmem_ld_wait();
+        // common case: one compare per similarity against the row's current k'-th score; the (rare) survivors are
+        // collected in a bitmask and inserted below in ascending column order, so equal scores keep the lower index
+        const float thr = top.threshold();
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) m |= (__uint_as_float(r[j]) > thr) ? (1u << j) : 0u;
+        if (c0 + 32 > valid) m &= (1u << (valid - c0)) - 1u;  // tail tile: drop the zero-filled columns
+        while (m) {
+          const int j = __ffs(m) - 1;
+          m &= m - 1;
+          const float v = __uint_as_float(pick32(r, j));
+          if (v > top.threshold()) top.insert(v, n0 + c0 + j);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+    }
+    if (row < p.Q) {
+      float* cs = p.cand_s + ((size_t)row * p.n_split + split) * KP;
+      int* ci = p.cand_i + ((size_t)row * p.n_split + split) * KP;
+#pragma unroll
+      for (int j = 0; j < KP; j += 4) {
+        *reinterpret_cast<float4*>(cs + j) = make_float4(top.s[j], top.s[j + 1], top.s[j + 2], top.s[j + 3]);
+        *reinterpret_cast<int4*>(ci + j) = make_int4(top.i[j], top.i[j + 1], top.i[j + 2], top.i[j + 3]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// select: merge split candidates, exact fp32 re-score, final ordering.  One warp per query row.
+// ------------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool before(float sa, int ia, float sb, int ib) {
+  // strict total order (score desc, index asc); invalid (idx < 0) entries last
+  if ((ia < 0) || (ib < 0)) return (ib < 0) && (ia >= 0);
+  return sa > sb || (sa == sb && ia < ib);
+}
+
+template <int KP>
+__global__ void __launch_bounds__(128) sim_select_kernel(const float* __restrict__ cand_s, const int* __restrict__ cand_i, int Q,
+                                                         int n_split, int k, long long idx_base, int D,
+                                                         const float* __restrict__ q32, const float* __restrict__ g32,
+                                                         const float* __restrict__ q_inv, const float* __restrict__ g_inv,
+                                                         float* __restrict__ out_s, long long* __restrict__ out_i) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= Q) return;
+  const int C = n_split * KP;
+  const float* cs = cand_s + (size_t)row * C;
+  const int* ci = cand_i + (size_t)row * C;
+  // ---- stage 1: the KP best candidates by kernel-1 score; lane j ends up holding the j-th
+  float my_s = -INFINITY;
+  int my_i = -1;
+  if (n_split == 1) {
+    if (lane < KP) {
+      my_s = cs[lane];
+      my_i = ci[lane];
+    }
+  } else {
+    float last_s = INFINITY;
+    int last_i = -1;
+    bool first = true;
+    for (int r = 0; r < KP; ++r) {
+      float bs = -INFINITY;
+      int bi = -1;
+      for (int c = lane; c < C; c += 32) {
+        const float s = cs[c];
+        const int i = ci[c];
+        if (i < 0) continue;
+        const bool after_last = first || before(last_s, last_i, s, i);
+        if (after_last && before(s, i, bs, bi)) {
+          bs = s;
+          bi = i;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (before(os, oi, bs, bi)) {
+          bs = os;
+          bi = oi;
+        }
+      }
+      if (lane == r) {
+        my_s = bs;
+        my_i = bi;
+      }
+      last_s = bs;
+      last_i = bi;
+      first = false;
+      if (bi < 0) break;  // warp-uniform: candidates exhausted
+    }
+  }
+  // ---- stage 2: exact fp32 re-score of the KP survivors
+  if (q32 != nullptr) {
+    const float* qr = q32 + (size_t)row * D;
+    const float qi = q_inv ? q_inv[row] : 1.f;
+    for (int c = 0; c < KP; ++c) {
+      const int gi = __shfl_sync(0xffffffffu, my_i, c);
+      if (gi < 0) continue;  // warp-uniform
+      const float* gr = g32 + (size_t)gi * D;
+      float acc = 0.f;
+      if ((D & 3) == 0) {
+        for (int d = lane * 4; d < D; d += 128) {
+          const float4 a = *reinterpret_cast<const float4*>(qr + d);
+          const float4 b = __ldg(reinterpret_cast<const float4*>(gr + d));
+          acc = fmaf(a.x, b.x, acc);
+          acc = fmaf(a.y, b.y, acc);
+          acc = fmaf(a.z, b.z, acc);
+          acc = fmaf(a.w, b.w, acc);
+        }
+      } else {
+        for (int d = lane; d < D; d += 32) acc = fmaf(qr[d], __ldg(gr + d), acc);
+      }
+      acc = warp_sum(acc);
+      const float sc = acc * qi * (g_inv ? g_inv[gi] : 1.f);
+      if (lane == c) my_s = sc;
+    }
+  }
+  // ---- stage 3: final rank among the KP survivors by (score desc, index asc)
+  int rank = 0;
+  for (int c = 0; c < KP; ++c) {
+    const float os = __shfl_sync(0xffffffffu, my_s, c);
+    const int oi = __shfl_sync(0xffffffffu, my_i, c);
+    if (c != lane && before(os, oi, my_s, my_i)) ++rank;
+  }
+  if (lane < KP && my_i >= 0 && rank < k) {
+    out_s[(size_t)row * k + rank] = my_s;
+    out_i[(size_t)row * k + rank] = idx_base + my_i;
+  }
+  // rows with fewer than k valid candidates: pad
+  const int n_valid = __popc(__ballot_sync(0xffffffffu, lane < KP && my_i >= 0));
+  for (int j = n_valid + lane; j < k; j += 32) {
+    out_s[(size_t)row * k + j] = -INFINITY;
+    out_i[(size_t)row * k + j] = -1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// host side: TMA descriptors (driver entry point fetched through the runtime, no -lcuda), launch plan
+// ------------------------------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+struct TmaKey {
+  const void* ptr;
+  long long rows;
+  int D, box_rows;
+  bool operator==(const TmaKey& o) const { return ptr == o.ptr && rows == o.rows && D == o.D && box_rows == o.box_rows; }
+};
+struct TmaKeyHash {
+  size_t operator()(const TmaKey& k) const {
+    return std::hash<const void*>()(k.ptr) ^ (std::hash<long long>()(k.rows) * 1315423911u) ^ (size_t)(k.D * 2654435761u) ^
+           (size_t)k.box_rows;
+  }
+};
+static std::mutex g_tma_mutex;
+static std::unordered_map<TmaKey, CUtensorMap, TmaKeyHash> g_tma_cache;
+
+void tma_cache_clear() {
+  std::lock_guard<std::mutex> lock(g_tma_mutex);
+  g_tma_cache.clear();
+}
+
+// 2-D bf16 tensor [rows, D] row-major; box = [box_rows, 64] with 128-byte swizzle; out-of-bounds rows read as zero.
+static int make_tmap(const void* ptr, long long rows, int D, int box_rows, CUtensorMap* out) {
+  TmaKey key{ptr, rows, D, box_rows};
+  {
+    std::lock_guard<std::mutex> lock(g_tma_mutex);
+    auto it = g_tma_cache.find(key);
+    if (it != g_tma_cache.end()) {
+      *out = it->second;
+      return CVPCE_OK;
+    }
+  }
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return set_err(CVPCE_ERR_CUDA, "sim_topk: cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)D * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_err(CVPCE_ERR_CUDA, "sim_topk: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  std::lock_guard<std::mutex> lock(g_tma_mutex);
+  if (g_tma_cache.size() > 256) g_tma_cache.clear();
+  g_tma_cache[key] = *out;
+  return CVPCE_OK;
+}
+
+static int kp_for(int k, bool rescore) {
+  const int want = rescore ? k + 8 : k;
+  return want <= 16 ? 16 : 32;
+}
+
+struct TcPlan {
+  int m_blocks, n_tiles, n_split, tiles_per_split, kp;
+};
+
+static TcPlan make_plan(int Q, int G, int D, int k, bool rescore) {
+  TcPlan pl;
+  pl.m_blocks = (Q + BM - 1) / BM;
+  pl.n_tiles = (G + BN - 1) / BN;
+  pl.kp = kp_for(k, rescore);
+  const int sms = sm_count();
+  // gallery splits: (a) keep every SM busy when there are few query blocks, (b) keep the gallery range one wave of CTAs
+  // streams within ~64 MB so that it stays L2-resident while all query blocks of the wave pass over it, (c) avoid a
+  // ragged last wave.
+  int best = 1;
+  double best_cost = 1e30;
+  const int max_split = pl.n_tiles < 64 ? pl.n_tiles : 64;
+  for (int s = 1; s <= max_split; ++s) {
+    const int tps = (pl.n_tiles + s - 1) / s;
+    const int used = (pl.n_tiles + tps - 1) / tps;  // splits that actually get tiles
+    if (used != s) continue;
+    const long long ctas = (long long)pl.m_blocks * s;
+    const long long waves = (ctas + sms - 1) / sms;
+    double cost = (double)waves * tps;                                // time in tile units
+    const double range_mb = (double)tps * BN * D * 2 / (1024.0 * 1024.0);
+    if (range_mb > 64.0 && pl.m_blocks > 1) cost *= 1.0 + 0.25 * (range_mb / 64.0 - 1.0) / 8.0;  // mild L2 penalty
+    cost *= 1.0 + 0.002 * s;                                          // merge / prologue overhead per split
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = s;
+    }
+  }
+  pl.n_split = best;
+  pl.tiles_per_split = (pl.n_tiles + best - 1) / best;
+  return pl;
+}
+
+template <bool RES, int KP>
+static int launch_tc(const CUtensorMap& tq, const CUtensorMap& tg, const TcParams& p, cudaStream_t st) {
+  constexpr int stages = RES ? kStagesResident : kStagesStream;
+  constexpr int stage_bytes = RES ? B_TILE_BYTES : (A_TILE_BYTES + B_TILE_BYTES);
+  const size_t smem = 1024 + (RES ? (size_t)kMaxResidentKB * A_TILE_BYTES : 0) + (size_t)stages * stage_bytes;
+  static bool configured = false;
+  if (!configured) {
+    CVPCE_CUDA_OK(cudaFuncSetAttribute(sim_topk_tc_kernel<RES, KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  sim_topk_tc_kernel<RES, KP><<<(unsigned)(p.m_blocks * p.n_split), kTcThreads, smem, st>>>(tq, tg, p);
+  CVPCE_LAUNCH_OK("sim_topk_tc_kernel");
+  return CVPCE_OK;
+}
+
+}  // namespace cvpce
+
+extern "C" size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k) {
+  using namespace cvpce;
+  if (Q <= 0 || G <= 0 || D <= 0 || k <= 0 || k > 32) return 0;
+  const TcPlan pl = make_plan(Q, G, D, k, true);
+  return (size_t)Q * pl.n_split * 32 * 8 + 256;  // sized for KP = 32 so that both modes fit
+}
+
+extern "C" int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                              const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                              float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(Q >= 0 && G >= 0, CVPCE_ERR_INVALID_ARG, "sim_topk: negative size Q=%d G=%d", Q, G);
+  CVPCE_REQUIRE(D >= 64 && D <= 4096 && D % 64 == 0, CVPCE_ERR_UNSUPPORTED, "sim_topk: D=%d must be a multiple of 64 in [64,4096] (use cvpce_sim_topk_f32)", D);
+  CVPCE_REQUIRE(k >= 1 && k <= 32, CVPCE_ERR_UNSUPPORTED, "sim_topk: k=%d outside [1,32] (use cvpce_sim_topk_f32)", k);
+  if (Q == 0) return CVPCE_OK;
+  CVPCE_REQUIRE(q_bf16 && out_scores && out_idx && (g_bf16 || G == 0), CVPCE_ERR_INVALID_ARG, "sim_topk: null pointer");
+  CVPCE_REQUIRE(aligned16(q_bf16) && aligned16(g_bf16), CVPCE_ERR_INVALID_ARG, "sim_topk: operands must be 16-byte aligned (TMA)");
+  CVPCE_REQUIRE((q_f32 == nullptr) == (g_f32 == nullptr), CVPCE_ERR_INVALID_ARG, "sim_topk: q_f32 and g_f32 must be given together");
+  CVPCE_REQUIRE(!q_f32 || (aligned16(q_f32) && aligned16(g_f32)), CVPCE_ERR_INVALID_ARG, "sim_topk: fp32 operands must be 16-byte aligned");
+  if (int rc = require_sm100()) return rc;
+  const bool rescore = q_f32 != nullptr;
+  cudaStream_t st = (cudaStream_t)stream;
+  const TcPlan pl = make_plan(Q, G > 0 ? G : 1, D, k, rescore);
+  const size_t need = (size_t)Q * pl.n_split * pl.kp * 8 + 256;
+  CVPCE_REQUIRE(workspace && workspace_bytes >= need, CVPCE_ERR_WORKSPACE, "sim_topk: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  uintptr_t ws = (reinterpret_cast<uintptr_t>(workspace) + 127) & ~(uintptr_t)127;
+  float* cand_s = reinterpret_cast<float*>(ws);
+  int* cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.n_split * pl.kp * 4);
+
+  TcParams p;
+  p.Q = Q; p.G = G; p.D = D;
+  p.n_tiles = G > 0 ? pl.n_tiles : 0;
+  p.m_blocks = pl.m_blocks;
+  p.n_split = pl.n_split;
+  p.tiles_per_split = pl.tiles_per_split;
+  p.cand_s = cand_s;
+  p.cand_i = cand_i;
+  CUtensorMap tq, tg;
+  if (int rc = make_tmap(q_bf16, Q, D, BM, &tq)) return rc;
+  if (int rc = make_tmap(G > 0 ? g_bf16 : q_bf16, G > 0 ? G : Q, D, BN, &tg)) return rc;
+  const bool resident = D <= kMaxResidentKB * BK;
+  int rc;
+  if (pl.kp == 16) rc = resident ? launch_tc<true, 16>(tq, tg, p, st) : launch_tc<false, 16>(tq, tg, p, st);
+  else             rc = resident ? launch_tc<true, 32>(tq, tg, p, st) : launch_tc<false, 32>(tq, tg, p, st);
+  if (rc) return rc;
+  const int warps = 4;
+  const int grid = (Q + warps - 1) / warps;
+  if (pl.kp == 16)
+    sim_select_kernel<16><<<grid, warps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm,
+                                                       g_inv_norm, out_scores, reinterpret_cast<long long*>(out_idx));
+  else
+    sim_select_kernel<32><<<grid, warps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm,
+                                                       g_inv_norm, out_scores, reinterpret_cast<long long*>(out_idx));
+  CVPCE_LAUNCH_OK("sim_select_kernel");
+  return CVPCE_OK;
 }

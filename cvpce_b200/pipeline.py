@@ -1,0 +1,122 @@
+"""The batched hot path as one object: scored candidate boxes of a batch of shelf images -> NMS -> crops -> encoder
+(torch conv trunk + MAC/R-MAC kernel) -> cosine top-k against a prepared gallery.
+
+This is what bench.py times and what a production caller uses when it has more than one image in flight; it performs ONE
+host synchronisation per step (the kept-box counts, needed to size the crop tensor) instead of the reference's four per
+box (cvpce/production.py:20) plus one per result element (:70).
+"""
+import torch
+
+from . import classification, ops
+
+
+class StageTimer:
+    """Records CUDA events around each library call so that bench.py can report per-kernel durations measured inside
+    the timed region (events are recorded on the current stream, where the kernels are launched)."""
+
+    def __init__(self):
+        self.records = []  # (name, start_event, end_event, algorithmic bytes, flops)
+
+    def span(self, name, nbytes=0.0, flops=0.0):
+        timer = self
+
+        class _Span:
+            def __enter__(self):
+                self.s = torch.cuda.Event(enable_timing=True)
+                self.e = torch.cuda.Event(enable_timing=True)
+                self.s.record()
+
+            def __exit__(self, *exc):
+                self.e.record()
+                timer.records.append((name, self.s, self.e, float(nbytes), float(flops)))
+
+        return _Span()
+
+    def summary(self):
+        out = {}
+        for name, s, e, nbytes, flops in self.records:
+            d = out.setdefault(name, {"launches": 0, "ms": 0.0, "bytes": 0.0, "flops": 0.0})
+            d["launches"] += 1
+            d["ms"] += s.elapsed_time(e)
+            d["bytes"] += nbytes
+            d["flops"] += flops
+        return out
+
+
+class _NoTimer:
+    def span(self, *a, **k):
+        import contextlib
+        return contextlib.nullcontext()
+
+
+class HotPath:
+    def __init__(self, encoder, gallery_embedding, k=1, size=256, antialias=True, iou_threshold=0.5, detections_per_img=200,
+                 min_score=None, trunk_batch=128, trunk_dtype=torch.float32, channels_last=False, exact=True, rmac_levels=0):
+        self.encoder = encoder
+        self.gallery = classification.PreparedGallery(gallery_embedding)
+        self.k = k
+        self.size = size
+        self.antialias = antialias
+        self.iou_threshold = iou_threshold
+        self.detections_per_img = detections_per_img
+        self.min_score = min_score
+        self.trunk_batch = trunk_batch
+        self.trunk_dtype = trunk_dtype
+        self.channels_last = channels_last
+        self.exact = exact
+        self.rmac_levels = rmac_levels
+        self.affine = classification.tanh_normalize_affine()  # scale_to_tanh + MACVGG normalisation folded into the crop kernel
+        self.launches = 0  # launches of OUR kernels (library calls), counted per call site
+        self.timer = _NoTimer()
+
+    @torch.no_grad()
+    def step(self, images, cand_boxes, cand_scores, seg_offsets, max_n):
+        """images: list of CUDA f32 [3,H,W]; cand_boxes f32[total,4] / cand_scores f32[total] / seg_offsets i32[B+1] on the
+        device (original-image pixels); max_n: host upper bound of candidates per image.
+        Returns dict(boxes f32[K,4], image_idx i32[K], counts i32[B] (host), topk_idx i64[K,k], topk_sim f32[K,k], embedding)."""
+        B = len(images)
+        total = cand_boxes.shape[0]
+        with self.timer.span("nms", 20.0 * total):
+            keep, counts, kept_boxes, _ = ops.nms_batched(cand_boxes, cand_scores, seg_offsets, max_n, self.iou_threshold,
+                                                          self.min_score, self.detections_per_img, want_boxes=True)
+        self.launches += 1
+        counts_h = counts.cpu()  # the one host synchronisation of the step
+        K = int(counts_h.sum())
+        dev = cand_boxes.device
+        counts64 = counts.to(torch.int64)
+        image_idx = torch.repeat_interleave(torch.arange(B, device=dev), counts64, output_size=K)
+        first = torch.cumsum(counts64, 0) - counts64
+        pos = seg_offsets[:-1].to(torch.int64)[image_idx] + (torch.arange(K, device=dev) - first[image_idx])
+        boxes = kept_boxes[pos]
+        table = ops.make_image_table(images)
+        S = self.size
+        crop_bytes = 12.0 * S * S * K + 12.0 * float(((boxes[:, 2].long() - boxes[:, 0].long()).clamp(min=0) *
+                                                      (boxes[:, 3].long() - boxes[:, 1].long()).clamp(min=0)).sum()) \
+            if not isinstance(self.timer, _NoTimer) else 0.0
+        with self.timer.span("crop_resize", crop_bytes):
+            crops = ops.crop_resize(table, B, boxes, image_idx.to(torch.int32), S, self.antialias, 0.5, self.affine,
+                                    self.trunk_dtype, self.channels_last)
+        self.launches += 1
+        D = self.encoder.embedding_size
+        emb = torch.empty((K, D), dtype=torch.float32, device=dev)
+        regions = None
+        for i in range(0, K, self.trunk_batch):
+            f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True)
+            if self.rmac_levels and regions is None:
+                regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.rmac_levels) for f in (f4, f5)]
+            esz = f4.element_size()
+            nb = float(f4.numel() + f5.numel()) * esz + 4.0 * D * f4.shape[0]
+            with self.timer.span("region_pool_embed", nb):
+                ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=bool(self.rmac_levels), out=emb[i:i + self.trunk_batch])
+            self.launches += 1
+        G = self.gallery.G
+        k = min(self.k, G)
+        with self.timer.span("rows_prepare", 6.0 * K * D):
+            qb, qinv = ops.rows_prepare(emb, normalize=True)
+        self.launches += 1
+        with self.timer.span("sim_topk", 2.0 * (K + G) * D + 8.0 * K * k, 2.0 * K * G * D):
+            sim, idx = ops.sim_topk(qb, self.gallery.bf16, k, 0, emb if self.exact else None,
+                                    self.gallery.f32 if self.exact else None, qinv if self.exact else None,
+                                    self.gallery.inv_norm if self.exact else None)
+        self.launches += 2 if self.exact else 1
+        return {"boxes": boxes, "image_idx": image_idx, "counts": counts_h, "topk_idx": idx, "topk_sim": sim, "embedding": emb}

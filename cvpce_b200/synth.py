@@ -1,4 +1,4 @@
-"""Seeded synthetic inputs shared by the golden generator, the tests and bench.py.
+"""Seeded synthetic workloads shared by bench.py, the tests and the golden generator (host side, numpy only).
 
 numpy RandomState only, so the same seed gives the same bytes in the authoring container and on the GPU box.
 """

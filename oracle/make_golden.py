@@ -12,7 +12,8 @@ import numpy as np
 import torch
 import torchvision
 
-from . import shim, synth
+from . import shim
+from cvpce_b200 import synth
 
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
 

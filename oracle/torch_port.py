@@ -1,0 +1,98 @@
+"""Torch-CPU restatement of the reference's own call sequence for the hot path.  TEST INFRASTRUCTURE / CPU BASELINE ONLY.
+
+This is what `bench.py --impl reference` and bench.py's `cpu_baseline` time on the box's host cores (kind "port"): the
+same torch / torchvision CPU ops the reference executes, in the same order, so the number is the reference's CPU cost
+rather than the cost of oracle.c's scalar loops.  /root/reference cannot travel to the GPU box; tests/test_reference_pin.py
+checks this port against the real reference where it is available.  Never imported by cvpce_b200/.
+"""
+import torch
+import torchvision
+from torch import nn
+from torchvision.models import vgg
+from torchvision.transforms import functional as ttf
+
+CLASSIFICATION_IMAGE_SIZE = 256  # cvpce/datautils.py:232
+
+
+def postprocess_nms(boxes, scores, nms_thresh=0.5, detections_per_img=200):
+    """tv:models/detection/retinanet.py:559-561 for the single-class GLN."""
+    labels = torch.zeros(len(scores), dtype=torch.int64)
+    return torchvision.ops.batched_nms(boxes, scores, labels, nms_thresh)[:detections_per_img]
+
+
+def resize_for_classification(img, size=CLASSIFICATION_IMAGE_SIZE):
+    """cvpce/datautils.py:234-239"""
+    h, w = img.shape[1:]
+    side = max(h, w)
+    canvas = torch.full((3, side, side), 0.5)
+    canvas[:, :h, :w] = img
+    return ttf.resize(canvas, (size, size))
+
+
+def crops_for_boxes(image, boxes, size=CLASSIFICATION_IMAGE_SIZE):
+    """cvpce/production.py:16-20 (the per-box python loop)."""
+    if not len(boxes):
+        return torch.empty((0, 3, size, size))
+    out = []
+    for x1, y1, x2, y2 in boxes.to(dtype=torch.long):
+        out.append(resize_for_classification(image[:, y1:y2, x1:x2], size))
+    return torch.stack(out)
+
+
+class MACVGGPort(nn.Module):
+    """cvpce/models/classification.py:20-51 with vgg16 (no BN), as the production CLIs build it."""
+    embedding_size = 1024
+
+    def __init__(self):
+        super().__init__()
+        feats = vgg.VGG(vgg.make_layers(vgg.cfgs['D'], batch_norm=False), init_weights=True).features
+        self.block1, self.block2 = feats[:23], feats[23:30]
+
+    def forward(self, x, eps=1e-8):
+        x = ttf.normalize(x, [0.485 * 2 - 1, 0.456 * 2 - 1, 0.406 * 2 - 1], [0.229 * 2, 0.224 * 2, 0.225 * 2])
+        x = self.block1(x)
+        d1 = x.amax(dim=(-2, -1))
+        x = self.block2(x)
+        d2 = x.amax(dim=(-2, -1))
+        d = torch.cat((d1, d2), dim=1)
+        return d / torch.linalg.norm(d, dim=1, keepdim=True).clamp(min=eps)
+
+
+def nearest_neighbors(anchors, queries, k=1):
+    """cvpce/models/classification.py:87-95 in the reference's own form (gathers two [Q,A,D] tensors, full argsort)."""
+    ai = torch.arange(len(anchors))
+    qi = torch.arange(len(queries))
+    qm, am = torch.meshgrid(qi, ai, indexing="ij")
+    dist = 1 - nn.functional.cosine_similarity(anchors[am], queries[qm], dim=-1)
+    return dist.argsort(dim=-1)[:, :k]
+
+
+def nearest_neighbors_chunked(anchors, queries, k=1, chunk=8):
+    """Same result for shapes where the reference form cannot allocate Q*A*D*4 bytes twice: queries in small chunks."""
+    return torch.cat([nearest_neighbors(anchors, queries[i:i + chunk], k) for i in range(0, len(queries), chunk)])
+
+
+@torch.no_grad()
+def classify(encoder, gallery_embedding, images, k=1, batch_size=32, nn_chunk=None):
+    """cvpce/production.py:57-74 (returns indices instead of annotation strings)."""
+    res = []
+    for i in range(0, len(images), batch_size):
+        batch = images[i:i + batch_size] * 2 - 1  # utils.scale_to_tanh
+        emb = encoder(batch)
+        if nn_chunk:
+            res.append(nearest_neighbors_chunked(gallery_embedding, emb, k, nn_chunk))
+        else:
+            res.append(nearest_neighbors(gallery_embedding, emb, k))
+    return torch.cat(res) if res else torch.empty((0, k), dtype=torch.int64)
+
+
+@torch.no_grad()
+def hot_path(encoder, gallery_embedding, image, cand_boxes, cand_scores, k=1, detections_per_img=200, max_crops=None,
+             batch_size=32, nn_chunk=None):
+    """One shelf image through the whole path on the CPU: NMS -> crops -> encoder -> nearest neighbours."""
+    keep = postprocess_nms(cand_boxes, cand_scores, 0.5, detections_per_img)
+    boxes = cand_boxes[keep]
+    if max_crops is not None:
+        boxes = boxes[:max_crops]
+    crops = crops_for_boxes(image, boxes)
+    return boxes, classify(encoder, gallery_embedding, crops, k, batch_size, nn_chunk)

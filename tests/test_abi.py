@@ -1,0 +1,90 @@
+"""CPU: the C-ABI library builds for sm_100a, loads, exports every symbol include/cvpce_b200.h declares, and refuses to
+run without a B200 (no CPU fallback).  No compute calls here."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import ROOT
+from cvpce_b200 import _lib, build, ops
+
+
+@pytest.fixture(scope="module")
+def lib():
+    build.build_library()
+    return _lib.load()
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "cvpce_b200.h")).read()
+    return sorted(set(re.findall(r"CVPCE_API\s+[\w\s\*]+?\b(cvpce_\w+)\s*\(", text)))
+
+
+def test_header_symbols_exported_and_bound(lib):
+    names = declared_symbols()
+    assert len(names) >= 14
+    for n in names:
+        assert hasattr(lib, n), "libcvpce_b200.so does not export %s" % n
+        assert n in _lib.SIGNATURES, "no ctypes signature for %s" % n
+    assert sorted(_lib.SIGNATURES) == names
+
+
+def test_version_and_struct_layout(lib):
+    assert lib.cvpce_version() == 100
+    assert ctypes.sizeof(_lib.FeatureMap) == 56  # void* + 3*int32 (+pad) + 4*int64
+
+
+def test_binary_is_sm100a_only():
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", _lib.SO_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_fails_loudly_without_gpu(lib):
+    assert lib.cvpce_device_check() == 4  # CVPCE_ERR_NO_DEVICE
+    assert b"no CPU fallback" in lib.cvpce_last_error()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.nms(torch.zeros(3, 4), torch.zeros(3), 0.5)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.sim_topk_f32(torch.zeros(2, 8), torch.zeros(4, 8), 1)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.region_pool_embed([torch.zeros(1, 2, 3, 3)])
+
+
+def test_argument_validation_on_host(lib):
+    # validation happens before any device work, so it can be exercised without a GPU
+    assert lib.cvpce_nms_batched(None, None, None, -1, 0, 0.5, 0.0, 0, None, None, None, None, None, None) == 1
+    assert lib.cvpce_nms_batched(None, None, None, 0, 0, 0.5, 0.0, 0, None, None, None, None, None, None) == 0  # empty batch ok
+    assert lib.cvpce_crop_resize(None, 0, None, None, 0, 256, 1, 0.5, None, 0, 0, None, None, None) == 0        # zero crops ok
+    assert lib.cvpce_crop_resize(None, 0, None, None, 4, 0, 1, 0.5, None, 0, 0, None, None, None) == 1
+    assert lib.cvpce_sim_topk_f32(None, None, 0, 10, 8, 1, 0, 1, 1e-8, None, None, None) == 0                  # zero queries ok
+    assert lib.cvpce_sim_topk_f32(None, None, 4, 10, 8, 100, 0, 1, 1e-8, None, None, None) == 2                # k too large
+    assert lib.cvpce_topk_merge(None, None, 0, 4, 1, None, None, None) == 1
+
+
+def test_threshold_rounding_helper():
+    import numpy as np
+    assert ops.threshold_as_cpu_op(0.5) == 0.5
+    f = ops.threshold_as_cpu_op(1 / 3)
+    assert f <= 1 / 3 and float(np.nextafter(np.float32(f), np.float32(1))) > 1 / 3
+    f = ops.threshold_as_cpu_op(0.7)
+    assert f <= 0.7 and float(np.nextafter(np.float32(f), np.float32(1))) > 0.7
+
+
+def test_rmac_regions_host_helper_matches_oracle(lib):
+    import oracle
+    for H, W, L in ((16, 16, 3), (14, 14, 3), (32, 32, 2), (14, 20, 3), (7, 7, 1)):
+        assert ops.rmac_regions(H, W, L) == [tuple(r) for r in oracle.rmac_regions(H, W, L).tolist()]
+
+
+def test_affine_fold_matches_reference_composition():
+    from cvpce_b200 import classification
+    x = torch.rand(2, 3, 5, 5)
+    a = torch.tensor(classification.tanh_normalize_affine()).view(3, 2)
+    got = x * a[:, 0].view(1, 3, 1, 1) + a[:, 1].view(1, 3, 1, 1)
+    want = ((x * 2 - 1) - torch.tensor(classification.NORM_MEAN).view(1, 3, 1, 1)) / torch.tensor(classification.NORM_STD).view(1, 3, 1, 1)
+    assert torch.allclose(got, want, atol=1e-6)

@@ -1,0 +1,353 @@
+"""GPU parity tests proper: the sm_100a kernels, called through the C ABI (cvpce_b200.ops -> libcvpce_b200.so), against
+the CPU oracle (oracle/) and the golden vectors written from the real reference (tests/golden/).
+
+Bars: NMS keep lists and top-k indices bit-exact (ties by the stated order); crops <= 1e-5 abs; pooled maxima exact;
+embeddings / similarities <= 1e-3 relative (observed ~1e-6 in fp32).
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from cvpce_b200 import synth
+from conftest import topk_check
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(cuda):
+    from cvpce_b200 import _lib, ops as _ops
+    lib = _lib.load()  # raises if the .so is missing: no fallback
+    assert lib.cvpce_device_check() == 0, _lib.last_error()
+    return _ops
+
+
+def dev(a, device="cuda"):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device)
+
+
+# ---------------------------------------------------------------------------------------------------------------- NMS
+def test_nms_golden_single(ops, golden):
+    for name, (boxes, scores, thr, per_img) in synth.nms_cases().items():
+        keep = ops.nms(dev(boxes), dev(scores), thr).cpu().numpy()
+        assert np.array_equal(keep, golden["nms"][name + "/keep"]), name
+
+
+def test_nms_batched_csr_matches_golden_and_oracle(ops, golden):
+    cases = synth.nms_cases()
+    names = list(cases)
+    boxes = np.concatenate([cases[n][0] for n in names] + [np.zeros((0, 4), np.float32)])
+    scores = np.concatenate([cases[n][1] for n in names])
+    sizes = [len(cases[n][1]) for n in names]
+    # an empty image in the middle of the batch
+    sizes.insert(3, 0)
+    names.insert(3, None)
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    keep, counts, kboxes, kscores = ops.nms_batched(dev(boxes), dev(scores), dev(seg), max(sizes), 0.5, want_boxes=True, want_scores=True)
+    keep, counts, kboxes, kscores = keep.cpu().numpy(), counts.cpu().numpy(), kboxes.cpu().numpy(), kscores.cpu().numpy()
+    for i, n in enumerate(names):
+        if n is None:
+            assert counts[i] == 0
+            continue
+        b, s, thr, _ = cases[n]
+        want = oracle.nms(b, s, 0.5)
+        got = keep[seg[i]: seg[i] + counts[i]]
+        assert np.array_equal(got, want), n
+        assert np.array_equal(kboxes[seg[i]: seg[i] + counts[i]], b[want]), n
+        assert np.array_equal(kscores[seg[i]: seg[i] + counts[i]], s[want]), n
+        if thr == 0.5:
+            assert np.array_equal(got, golden["nms"][n + "/keep"]), n
+
+
+def test_nms_postprocess_options(ops, golden):
+    b, s, thr, per_img = synth.nms_cases()["random5000"]
+    seg = dev(np.array([0, len(s)], dtype=np.int32))
+    keep, counts, _, _ = ops.nms_batched(dev(b), dev(s), seg, len(s), thr, max_keep=per_img)
+    got = keep[: int(counts.item())].cpu().numpy()
+    assert np.array_equal(got, golden["nms"]["random5000/keep_postprocess"])  # batched_nms(...)[:detections_per_img]
+    # confidence filter of production.py:15 folded in, plus the box rescale of transform.postprocess
+    scale = np.array([[1.5, 0.75]], dtype=np.float32)
+    keep, counts, kb, _ = ops.nms_batched(dev(b), dev(s), seg, len(s), thr, min_score=0.5, max_keep=per_img, box_scale=dev(scale),
+                                          want_boxes=True)
+    want = oracle.postprocess_nms(b, s, thr, per_img, min_score=0.5)
+    n = int(counts.item())
+    assert np.array_equal(keep[:n].cpu().numpy(), want)
+    assert np.array_equal(kb[:n].cpu().numpy(), b[want] * np.array([1.5, 0.75, 1.5, 0.75], dtype=np.float32))
+
+
+def test_nms_random_batch_vs_oracle(ops):
+    rs = np.random.RandomState(5)
+    sizes = [int(v) for v in rs.randint(0, 1500, 48)] + [8192, 1, 64, 65, 63]
+    all_b, all_s = [], []
+    for i, n in enumerate(sizes):
+        b, s = synth.random_boxes(1000 + i, n, extent=float(rs.choice([200, 600, 1500])), tie_every=int(rs.choice([0, 0, 5])))
+        all_b.append(b)
+        all_s.append(s)
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    thr = 0.5
+    keep, counts, _, _ = ops.nms_batched(dev(np.concatenate(all_b)), dev(np.concatenate(all_s)), dev(seg), max(sizes), thr)
+    keep, counts = keep.cpu().numpy(), counts.cpu().numpy()
+    for i, n in enumerate(sizes):
+        want = oracle.nms(all_b[i], all_s[i], thr)
+        assert counts[i] == len(want), (i, n)
+        assert np.array_equal(keep[seg[i]: seg[i] + counts[i]], want), (i, n)
+
+
+def test_nms_threshold_double_semantics(ops):
+    b = dev(np.array([[0, 0, 2, 1], [1, 0, 3, 1]], dtype=np.float32))
+    s = dev(np.array([0.9, 0.8], dtype=np.float32))
+    assert ops.nms(b, s, 1 / 3).tolist() == [0]
+    assert ops.nms(b, s, float(np.float32(1 / 3))).tolist() == [0, 1]
+
+
+def test_nms_limits_and_errors(ops):
+    b, s = synth.random_boxes(3, 100)
+    seg = dev(np.array([0, 100], dtype=np.int32))
+    keep, counts, _, _ = ops.nms_batched(dev(b), dev(s), seg, 50, 0.5)  # max_n too small: flagged, not silently wrong
+    assert int(counts.item()) == -1
+    with pytest.raises(RuntimeError):
+        ops.nms_batched(dev(b), dev(s), seg, 10000, 0.5)
+    with pytest.raises(RuntimeError):
+        ops.nms(torch.from_numpy(b), torch.from_numpy(s), 0.5)  # CPU tensors: no fallback
+    assert ops.nms(dev(np.zeros((0, 4), np.float32)), dev(np.zeros((0,), np.float32)), 0.5).numel() == 0
+
+
+# --------------------------------------------------------------------------------------------------------------- crop
+def test_crops_golden_and_oracle(ops, golden):
+    img = synth.shelf_image(synth.CROP_IMAGE_SEED, *synth.CROP_IMAGE_HW)
+    boxes = synth.crop_boxes()
+    gimg = dev(img)
+    table = ops.make_image_table([gimg])
+    for key, S, aa in (("aa_S256", 256, True), ("aa_S224", 224, True), ("noaa_S256", 256, False)):
+        out, valid = ops.crop_resize(table, 1, dev(boxes), None, S, aa, return_valid=True)
+        out = out.cpu().numpy()
+        assert valid.cpu().numpy().all()
+        got = out.reshape(len(boxes), -1)[:, synth.sample_pixels(S)]
+        np.testing.assert_allclose(got, golden["crops"][key], rtol=0, atol=1e-5)
+        want, _ = oracle.crop_resize(img, boxes, S, aa)
+        np.testing.assert_allclose(out, want, rtol=0, atol=1e-5)
+
+
+def test_crops_multi_image_layouts_affine(ops):
+    from cvpce_b200 import classification
+    imgs = [synth.shelf_image(60 + i, h, w) for i, (h, w) in enumerate([(300, 400), (128, 96), (513, 257)])]
+    gimgs = [dev(im) for im in imgs]
+    rs = np.random.RandomState(9)
+    boxes, idx = [], []
+    for i, im in enumerate(imgs):
+        H, W = im.shape[1:]
+        for _ in range(9):
+            x1, y1 = rs.uniform(0, W - 8), rs.uniform(0, H - 8)
+            boxes.append([x1, y1, x1 + rs.uniform(2, W - x1), y1 + rs.uniform(2, H - y1)])
+            idx.append(i)
+    boxes = np.asarray(boxes, dtype=np.float32)
+    idx = np.asarray(idx, dtype=np.int32)
+    perm = rs.permutation(len(idx))
+    boxes, idx = boxes[perm], idx[perm]
+    S = 96
+    want = np.stack([oracle.crop_resize(imgs[i], boxes[j:j + 1], S, True)[0][0] for j, i in enumerate(idx)])
+    table = ops.make_image_table(gimgs)
+    out = ops.crop_resize(table, 3, dev(boxes), dev(idx), S, True).cpu().numpy()
+    np.testing.assert_allclose(out, want, rtol=0, atol=1e-5)
+    # fused scale_to_tanh + MACVGG normalisation (utils.py:280-281, classification.py:41-44), channels_last, bf16
+    aff = classification.tanh_normalize_affine()
+    mean = np.array(classification.NORM_MEAN, dtype=np.float32).reshape(1, 3, 1, 1)
+    std = np.array(classification.NORM_STD, dtype=np.float32).reshape(1, 3, 1, 1)
+    want_aff = ((want * 2 - 1) - mean) / std
+    out = ops.crop_resize(table, 3, dev(boxes), dev(idx), S, True, affine=aff, channels_last=True)
+    assert out.shape == (len(idx), 3, S, S) and out.is_contiguous(memory_format=torch.channels_last)
+    np.testing.assert_allclose(out.cpu().numpy(), want_aff, rtol=0, atol=2e-5)
+    out = ops.crop_resize(table, 3, dev(boxes), dev(idx), S, True, affine=aff, out_dtype=torch.bfloat16)
+    np.testing.assert_allclose(out.float().cpu().numpy(), want_aff, rtol=1e-2, atol=1e-2)
+
+
+def test_crops_strided_view_empty_and_zero(ops):
+    img = synth.shelf_image(2, 64, 80)
+    big = dev(np.pad(img, ((0, 0), (3, 5), (7, 9))))
+    view = big[:, 3:67, 7:87]  # non-contiguous view with unit pixel stride
+    table = ops.make_image_table([view])
+    boxes = np.array([[3, 4, 50, 60], [10, 10, 10, 10], [20, 5, 20, 40]], dtype=np.float32)
+    out, valid = ops.crop_resize(table, 1, dev(boxes), None, 32, True, return_valid=True)
+    want, wvalid = oracle.crop_resize(img, boxes, 32, True)
+    np.testing.assert_allclose(out.cpu().numpy(), want, rtol=0, atol=1e-5)
+    assert valid.cpu().numpy().astype(bool).tolist() == wvalid.tolist() == [True, False, True]
+    empty = ops.crop_resize(table, 1, dev(np.zeros((0, 4), np.float32)), None, 256, True)
+    assert empty.shape == (0, 3, 256, 256)  # production.py:18-19
+
+
+# --------------------------------------------------------------------------------------------------------------- pool
+def test_mac_golden_and_exact_maxima(ops, golden):
+    f4, f5 = synth.feature_maps()
+    out = ops.region_pool_embed([dev(f4), dev(f5)]).cpu().numpy()
+    np.testing.assert_allclose(out, golden["mac"]["mac_given_maps"], rtol=1e-6, atol=1e-7)
+    raw = ops.region_pool_embed([dev(f4), dev(f5)], final_l2=False).cpu().numpy()
+    assert np.array_equal(raw, oracle.region_pool_embed([f4, f5], final_l2=False))  # max is exact
+
+
+@pytest.mark.parametrize("B", [1, 3, 37])
+def test_mac_vgg_shapes_layouts_dtypes(ops, B):
+    rs = np.random.RandomState(B)
+    f4 = np.maximum(rs.randn(B, 512, 32, 32), 0).astype(np.float32)
+    f5 = np.maximum(rs.randn(B, 512, 16, 16), 0).astype(np.float32)
+    want = oracle.region_pool_embed([f4, f5])
+    g4, g5 = dev(f4), dev(f5)
+    out = ops.region_pool_embed([g4, g5]).cpu().numpy()
+    np.testing.assert_allclose(out, want, rtol=2e-6, atol=1e-7)
+    out_cl = ops.region_pool_embed([g4.contiguous(memory_format=torch.channels_last), g5.contiguous(memory_format=torch.channels_last)])
+    np.testing.assert_allclose(out_cl.cpu().numpy(), want, rtol=2e-6, atol=1e-7)
+    b4, b5 = g4.bfloat16(), g5.bfloat16()
+    want_bf = oracle.region_pool_embed([b4.float().cpu().numpy(), b5.float().cpu().numpy()])
+    np.testing.assert_allclose(ops.region_pool_embed([b4, b5]).cpu().numpy(), want_bf, rtol=2e-6, atol=1e-7)
+    np.testing.assert_allclose(ops.region_pool_embed([b4.contiguous(memory_format=torch.channels_last),
+                                                      b5.contiguous(memory_format=torch.channels_last)]).cpu().numpy(),
+                               want_bf, rtol=2e-6, atol=1e-7)
+
+
+def test_rmac_regions_mode(ops):
+    assert ops.rmac_regions(16, 16, 3) == [tuple(r) for r in oracle.rmac_regions(16, 16, 3).tolist()]
+    assert ops.rmac_regions(14, 20, 3) == [tuple(r) for r in oracle.rmac_regions(14, 20, 3).tolist()]
+    rs = np.random.RandomState(4)
+    feats = [np.maximum(rs.randn(6, 512, 16, 16), 0).astype(np.float32), np.maximum(rs.randn(6, 96, 40, 24), 0).astype(np.float32),
+             np.maximum(rs.randn(6, 30, 7, 7), 0).astype(np.float32)]
+    regions = [oracle.rmac_regions(f.shape[2], f.shape[3], 3).tolist() for f in feats]
+    want = oracle.region_pool_embed(feats, regions, per_region_l2=True)
+    out = ops.region_pool_embed([dev(f) for f in feats], regions=regions, per_region_l2=True).cpu().numpy()
+    np.testing.assert_allclose(out, want, rtol=1e-5, atol=1e-7)
+    want = oracle.region_pool_embed(feats, regions, per_region_l2=False, final_l2=False)
+    out = ops.region_pool_embed([dev(f) for f in feats], regions=regions, per_region_l2=False, final_l2=False).cpu().numpy()
+    np.testing.assert_allclose(out, want, rtol=1e-6, atol=0)
+
+
+def test_l2norm_rows(ops):
+    x = np.random.RandomState(1).randn(77, 1000).astype(np.float32)
+    x[5] = 0
+    out = ops.l2norm_rows_(dev(x)).cpu().numpy()
+    want = x / np.maximum(np.linalg.norm(x.astype(np.float64), axis=1, keepdims=True), 1e-8)
+    np.testing.assert_allclose(out, want, rtol=1e-5, atol=1e-7)
+
+
+# ---------------------------------------------------------------------------------------------------------------- sim
+def test_nearest_neighbors_reference_kat(ops):
+    from cvpce_b200 import classification
+    a, q, expected = synth.nn_kat()
+    got = classification.nearest_neighbors(dev(a), dev(q))[:, 0].cpu().numpy()  # reference test/models/classification_test.py
+    assert np.array_equal(got, expected)
+
+
+def test_sim_topk_f32_vs_oracle_and_golden(ops, golden):
+    for name, (Q, G, D, k, seed) in synth.NN_CASES.items():
+        g, q = synth.nn_case(Q, G, D, seed)
+        sim, idx = ops.sim_topk_f32(dev(q), dev(g), k)
+        osim, oidx = oracle.sim_topk(q, g, k)
+        topk_check(q, g, idx.cpu().numpy(), osim, oidx)
+        assert np.array_equal(idx.cpu().numpy(), golden["nn"][name]), name
+        np.testing.assert_allclose(sim.cpu().numpy(), osim, rtol=1e-3, atol=1e-6)
+
+
+def test_sim_topk_f32_unnormalised_ties_padding(ops):
+    rs = np.random.RandomState(2)
+    g = (rs.randn(500, 96) * rs.uniform(0.1, 5, (500, 1))).astype(np.float32)
+    q = (rs.randn(70, 96) * 3).astype(np.float32)
+    g[7] = 0
+    g[100] = g[50]
+    g[200] = g[50] * 2  # same direction: exact tie after normalisation up to rounding
+    sim, idx = ops.sim_topk_f32(dev(q), dev(g), 8, idx_base=1000)
+    osim, oidx = oracle.sim_topk(q, g, 8)
+    topk_check(q, g, idx.cpu().numpy() - 1000, osim, oidx, tol=1e-5)
+    # fewer gallery rows than k: padded with (-inf, -1)
+    sim, idx = ops.sim_topk_f32(dev(q[:3]), dev(g[:2]), 4)
+    assert (idx[:, 2:] == -1).all() and torch.isinf(sim[:, 2:]).all()
+    # exact duplicates: ascending index
+    gg = np.array([[1, 0], [1, 0], [0, 1], [1, 0]], dtype=np.float32)
+    _, idx = ops.sim_topk_f32(dev(np.array([[1, 0]], dtype=np.float32)), dev(gg), 3)
+    assert idx.tolist() == [[0, 1, 3]]
+
+
+def test_topk_merge(ops):
+    rs = np.random.RandomState(3)
+    W, Q, k = 8, 300, 5
+    scores = rs.randn(W, Q, k).astype(np.float32)
+    scores[:, ::3, :] = np.round(scores[:, ::3, :], 1)  # force ties
+    scores = -np.sort(-scores, axis=2)
+    idx = np.stack([rs.permutation(1000)[:k] + w * 1000 for w in range(W) for _ in range(Q)]).reshape(W, Q, k).astype(np.int64)
+    scores[3, 10, 2:] = -np.inf
+    idx[3, 10, 2:] = -1
+    s, i = ops.topk_merge(dev(scores), dev(idx))
+    for r in range(Q):
+        cand = [(-(scores[w, r, j]), idx[w, r, j]) for w in range(W) for j in range(k) if idx[w, r, j] >= 0]
+        cand.sort()
+        assert i[r].tolist() == [c[1] for c in cand[:k]], r
+        assert s[r].tolist() == [-c[0] for c in cand[:k]], r
+
+
+@pytest.mark.parametrize("Q,G,D,k", [(64, 180, 1024, 1), (300, 5000, 512, 5), (1000, 8192, 1024, 5), (130, 777, 64, 3),
+                                     (257, 40000, 512, 5), (5, 100000, 512, 5)])
+def test_sim_topk_tensor_core_vs_oracle(ops, Q, G, D, k):
+    rs = np.random.RandomState(Q + G)
+    g = synth.unit_rows(rs, G, D, nonneg=(D == 1024))
+    q, _ = synth.planted_queries(rs, g, Q, frac=0.3)
+    gq, gg = dev(q), dev(g)
+    qb, qinv = ops.rows_prepare(gq)
+    gb, ginv = ops.rows_prepare(gg)
+    sim, idx = ops.sim_topk(qb, gb, k, 0, gq, gg, qinv, ginv)
+    osim, oidx = oracle.sim_topk(q, g, k)
+    rate = topk_check(q, g, idx.cpu().numpy(), osim, oidx)
+    assert rate > 0.999, rate
+    np.testing.assert_allclose(sim.cpu().numpy(), osim, rtol=1e-3, atol=1e-6)
+    # cross-check with the exact fp32 CUDA-core kernel on the device
+    sim32, idx32 = ops.sim_topk_f32(gq, gg, k)
+    assert (idx32 == idx).float().mean().item() > 0.999
+    # bf16-operand scores without the re-score: within bf16 rounding of the exact ones, top-1 agreement reported
+    simb, idxb = ops.sim_topk(qb, gb, k)
+    np.testing.assert_allclose(simb[:, 0].cpu().numpy(), osim[:, 0], rtol=0, atol=2e-3)
+
+
+def test_sim_topk_shard_offsets_and_merge(ops):
+    rs = np.random.RandomState(8)
+    G, D, Q, k, W = 4096, 512, 200, 5, 4
+    g = synth.unit_rows(rs, G, D, nonneg=False)
+    q, _ = synth.planted_queries(rs, g, Q)
+    gq = dev(q)
+    qb, qinv = ops.rows_prepare(gq)
+    parts_s, parts_i = [], []
+    for w in range(W):
+        gs = dev(g[w * G // W:(w + 1) * G // W])
+        gb, ginv = ops.rows_prepare(gs)
+        s, i = ops.sim_topk(qb, gb, k, w * G // W, gq, gs, qinv, ginv)
+        parts_s.append(s)
+        parts_i.append(i)
+    s, i = ops.topk_merge(torch.stack(parts_s), torch.stack(parts_i))
+    osim, oidx = oracle.sim_topk(q, g, k)
+    assert topk_check(q, g, i.cpu().numpy(), osim, oidx) > 0.999
+
+
+# --------------------------------------------------------------------------------------------------- encoder / pipeline
+def test_macvgg_mirror_matches_reference_embeddings(ops, golden):
+    from cvpce_b200 import classification
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    probe = torch.cat([enc.block1[0].weight.reshape(-1)[:8], enc.block2[-2].weight.reshape(-1)[:8]]).numpy()
+    if not np.allclose(probe, golden["mac"]["macvgg_weight_probe"], atol=1e-7):
+        pytest.skip("seeded VGG16 init differs from the authoring container's torch build")
+    enc = enc.cuda()
+    with torch.no_grad():
+        emb = enc(dev(synth.encoder_inputs())).cpu().numpy()
+    np.testing.assert_allclose(emb, golden["mac"]["macvgg_embeddings"], rtol=1e-3, atol=1e-5)
+
+
+def test_classifier_mirror_matches_reference_labels(ops, golden):
+    from cvpce_b200 import classification, production
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda()
+    gallery, queries = synth.classify_case()
+    clf = production.Classifier(enc, synth.GalleryDataset(gallery), batch_size=4, num_workers=0, k=3)
+    res, emb = clf.classify(torch.from_numpy(queries), return_embedding=True)
+    np.testing.assert_allclose(clf.embedding.cpu().numpy(), golden["classify"]["gallery_embedding"], rtol=1e-3, atol=1e-5)
+    np.testing.assert_allclose(emb.cpu().numpy(), golden["classify"]["query_embedding"], rtol=1e-3, atol=1e-5)
+    labels = np.array([[int(a[1:]) for a in row] for row in res])
+    assert np.array_equal(labels, golden["classify"]["labels"])
+    assert clf.classify(torch.empty((0, 3, 64, 64))) == []

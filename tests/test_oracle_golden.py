@@ -2,7 +2,7 @@
 import numpy as np
 
 import oracle
-from oracle import synth
+from cvpce_b200 import synth
 from conftest import topk_check
 
 

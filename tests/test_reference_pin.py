@@ -1,0 +1,56 @@
+"""CPU, authoring container only (skipped where /root/reference is absent, e.g. on the GPU box): pins the oracle and the
+torch port against the UNMODIFIED reference on fresh random inputs, beyond the committed golden vectors."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import shim, torch_port
+from cvpce_b200 import synth
+
+pytestmark = pytest.mark.skipif(not shim.available(), reason="reference tree not present")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    warnings.simplefilter("ignore")
+    return shim.load()
+
+
+def test_crop_loop_matches_reference(ref):
+    img = torch.from_numpy(synth.shelf_image(3, 200, 260))
+    boxes = torch.tensor([[10.9, 20.1, 120.5, 180.7], [0, 0, 260, 200], [100, 50, 101, 150], [30, 30, 90, 60]])
+    want = torch.stack([ref.datautils.resize_for_classification(img[:, y1:y2, x1:x2]) for x1, y1, x2, y2 in boxes.to(dtype=torch.long)])
+    got, _ = oracle.crop_resize(img.numpy(), boxes.numpy(), 256, True)
+    np.testing.assert_allclose(got, want.numpy(), rtol=0, atol=1e-6)
+    assert torch.equal(torch_port.crops_for_boxes(img, boxes), want)
+
+
+def test_encoder_and_nn_port_match_reference(ref):
+    torch.manual_seed(0)
+    enc_ref = ref.models.classification.macvgg_embedder("vgg16", pretrained=False).eval()
+    torch.manual_seed(0)
+    enc_port = torch_port.MACVGGPort().eval()
+    x = torch.from_numpy(synth.encoder_inputs(2, 64, 5))
+    with torch.no_grad():
+        assert torch.equal(enc_ref(x), enc_port(x))
+    g, q = synth.nn_case(20, 90, 128, 77)
+    want = ref.models.classification.nearest_neighbors(torch.from_numpy(g), torch.from_numpy(q), 4)
+    assert torch.equal(torch_port.nearest_neighbors(torch.from_numpy(g), torch.from_numpy(q), 4), want)
+    assert torch.equal(torch_port.nearest_neighbors_chunked(torch.from_numpy(g), torch.from_numpy(q), 4, 7), want)
+    assert np.array_equal(oracle.nearest_neighbors(g, q, 4), want.numpy())
+
+
+def test_reference_own_tests_pass_through_shim(ref, tmp_path):
+    """The reference's hot-path test (test/models/classification_test.py) run unmodified, via a `thesis` alias."""
+    import importlib.util
+    import sys
+    sys.modules["thesis"] = ref
+    sys.modules["thesis.models"] = ref.models
+    sys.modules["thesis.models.classification"] = ref.models.classification
+    spec = importlib.util.spec_from_file_location("ref_classification_test", shim.REFERENCE_ROOT + "/test/models/classification_test.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.test_nearest_neigbors()
