@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--trunk", default="f32", choices=["f32", "bf16"], help="dtype of the torch VGG16 trunk")
     ap.add_argument("--channels-last", action="store_true")
     ap.add_argument("--trunk-batch", type=int, default=128)
+    ap.add_argument("--cudnn-benchmark", action="store_true")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -401,6 +402,7 @@ def main():
     if not torch.cuda.is_available():
         sys.exit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     world, rank, local = dist_setup(args)
+    torch.backends.cudnn.benchmark = bool(args.cudnn_benchmark)
     if args.workload == "c5":
         line = run_ours_c5(args, world, rank, local)
     else:
