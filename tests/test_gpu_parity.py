@@ -162,6 +162,32 @@ def test_crops_multi_image_layouts_affine(ops):
     np.testing.assert_allclose(out.float().cpu().numpy(), want_aff, rtol=1e-2, atol=1e-2)
 
 
+def test_crops_band_kernel_paths(ops, monkeypatch):
+    """The separable band kernel against the oracle and against the direct kernel: band heights 8..64 (few / many
+    crops), ring wrap-around (strong down-sampling), the >16-tap direct fallback inside the band kernel, all
+    output layouts."""
+    img = synth.shelf_image(77, 700, 900)
+    gimg = dev(img)
+    table = ops.make_image_table([gimg])
+    rs = np.random.RandomState(4)
+    few = np.array([[0, 0, 900, 700], [10, 20, 600, 500], [100, 100, 140, 130], [5, 5, 300, 690]], dtype=np.float32)
+    x1, y1 = rs.uniform(0, 700, 700), rs.uniform(0, 500, 700)
+    many = np.stack([x1, y1, x1 + rs.uniform(3, 200, 700), y1 + rs.uniform(3, 200, 700)], 1).astype(np.float32)
+    for boxes, S in ((few, 256), (few, 64), (few, 32), (many, 64), (few, 224)):
+        want, _ = oracle.crop_resize(img, boxes, S, True)
+        out = ops.crop_resize(table, 1, dev(boxes), None, S, True)
+        np.testing.assert_allclose(out.cpu().numpy(), want, rtol=0, atol=1e-5)
+        nhwc = ops.crop_resize(table, 1, dev(boxes), None, S, True, channels_last=True)
+        assert torch.equal(nhwc.contiguous(), out)
+        b16 = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16)
+        b16n = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16, channels_last=True)
+        assert torch.equal(b16, out.to(torch.bfloat16)) and torch.equal(b16n.contiguous(), b16)
+        monkeypatch.setenv("CVPCE_CROP_DIRECT", "1")
+        direct = ops.crop_resize(table, 1, dev(boxes), None, S, True)
+        monkeypatch.delenv("CVPCE_CROP_DIRECT")
+        np.testing.assert_allclose(direct.cpu().numpy(), out.cpu().numpy(), rtol=0, atol=2e-6)
+
+
 def test_crops_strided_view_empty_and_zero(ops):
     img = synth.shelf_image(2, 64, 80)
     big = dev(np.pad(img, ((0, 0), (3, 5), (7, 9))))

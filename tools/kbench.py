@@ -1,0 +1,188 @@
+#!/usr/bin/env python
+"""Per-kernel micro-benchmarks at the BASELINE shapes (CUDA events on the launching stream, L2 flushed between
+iterations). Development tool: prints one JSON line per kernel; bench.py stays the contract benchmark.
+
+    python tools/kbench.py [crop] [nms] [pool] [prep] [sim] [--shelves 32] [--iters 5]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from cvpce_b200 import ops, synth  # noqa: E402
+
+HBM = 6540.2
+TENSOR = 1680.3
+try:
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+        _p = json.load(f)
+    HBM, TENSOR = float(_p["hbm_gbs"]), float(_p["bf16_tflops"])
+except Exception:
+    pass
+
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+    _flush.zero_()
+
+
+def timeit(fn, iters=5, warmup=3):
+    for _ in range(warmup):
+        fn()
+    ts = []
+    for _ in range(iters):
+        flush_l2()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.median(ts)), float(min(ts))
+
+
+def report(name, ms, best, nbytes=None, flops=None, **extra):
+    d = {"kernel": name, "ms_median": round(ms, 4), "ms_best": round(best, 4)}
+    if nbytes is not None:
+        d["GBs"] = round(nbytes / ms / 1e6, 1)
+        d["frac_hbm"] = round(nbytes / ms / 1e6 / HBM, 4)
+    if flops is not None:
+        d["TFLOPs"] = round(flops / ms / 1e9, 1)
+        d["frac_tensor"] = round(flops / ms / 1e9 / TENSOR, 4)
+    d.update(extra)
+    print(json.dumps(d), flush=True)
+
+
+def shelves(n, products=200):
+    H, W = synth.SHELF_HW
+    boxes, scores, sizes = [], [], []
+    for i in range(n):
+        b, s = synth.shelf_candidates(100 + i, H, W, products)
+        boxes.append(b)
+        scores.append(s)
+        sizes.append(len(s))
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    return np.concatenate(boxes), np.concatenate(scores), seg, max(sizes)
+
+
+def bench_nms(args):
+    dev = "cuda"
+    b, s, seg, mx = shelves(args.shelves)
+    bd, sd, segd = torch.from_numpy(b).to(dev), torch.from_numpy(s).to(dev), torch.from_numpy(seg).to(dev)
+    ms, best = timeit(lambda: ops.nms_batched(bd, sd, segd, mx, 0.5, None, 200, want_boxes=True), args.iters)
+    _, counts, _, _ = ops.nms_batched(bd, sd, segd, mx, 0.5, None, 200)
+    K = int(counts.sum())
+    report("nms c3 (%d images x ~%d)" % (args.shelves, mx), ms, best, 20.0 * len(s) + 8.0 * K, kept=K)
+    # stress shape: 5000 random candidates x 512 images (the real pre-NMS candidate count)
+    n_img, n = args.stress_images, 5000
+    bb, ss = [], []
+    for i in range(8):
+        x, y = synth.random_boxes(50 + i, n)
+        bb.append(x)
+        ss.append(y)
+    bb = np.concatenate([bb[i % 8] for i in range(n_img)])
+    ss = np.concatenate([ss[i % 8] for i in range(n_img)])
+    seg = (np.arange(n_img + 1) * n).astype(np.int32)
+    bd, sd, segd = torch.from_numpy(bb).to(dev), torch.from_numpy(ss).to(dev), torch.from_numpy(seg).to(dev)
+    ms, best = timeit(lambda: ops.nms_batched(bd, sd, segd, n, 0.5, None, 1000), args.iters)
+    _, counts, _, _ = ops.nms_batched(bd, sd, segd, n, 0.5, None, 1000)
+    K = int(counts.sum())
+    report("nms stress (%d images x %d)" % (n_img, n), ms, best, 20.0 * len(ss) + 8.0 * K, kept=K)
+
+
+def bench_crop(args):
+    dev = "cuda"
+    H, W = synth.SHELF_HW
+    b, s, seg, mx = shelves(args.shelves)
+    bd, sd, segd = torch.from_numpy(b).to(dev), torch.from_numpy(s).to(dev), torch.from_numpy(seg).to(dev)
+    keep, counts, kb, _ = ops.nms_batched(bd, sd, segd, mx, 0.5, None, 200, want_boxes=True)
+    counts_h = counts.cpu().numpy()
+    boxes = torch.cat([kb[int(seg[i]): int(seg[i]) + int(counts_h[i])] for i in range(args.shelves)])
+    idx = torch.repeat_interleave(torch.arange(args.shelves, device=dev), torch.from_numpy(counts_h).to(dev).long()).int()
+    images = [torch.rand((3, H, W), device=dev) for _ in range(args.shelves)]
+    table = ops.make_image_table(images)
+    K = boxes.shape[0]
+    bl = boxes.long()
+    src = float(((bl[:, 2] - bl[:, 0]).clamp(min=0) * (bl[:, 3] - bl[:, 1]).clamp(min=0)).sum())
+    from cvpce_b200 import classification
+    aff = classification.tanh_normalize_affine()
+    for S in args.sizes:
+        for dt, cl in ((torch.float32, False), (torch.float32, True), (torch.bfloat16, True)):
+            esz = 4 if dt == torch.float32 else 2
+            nbytes = 12.0 * src + 3.0 * esz * S * S * K
+            ms, best = timeit(lambda: ops.crop_resize(table, args.shelves, boxes, idx, S, True, 0.5, aff, dt, cl), args.iters)
+            report("crop_resize S=%d %s %s K=%d" % (S, "f32" if esz == 4 else "bf16", "nhwc" if cl else "nchw", K), ms, best, nbytes)
+    ms, best = timeit(lambda: ops.crop_resize(table, args.shelves, boxes, idx, 256, False, 0.5, aff), args.iters)
+    report("crop_resize S=256 f32 nchw plain-bilinear K=%d" % K, ms, best, 12.0 * src + 12.0 * 256 * 256 * K)
+
+
+def bench_pool(args):
+    dev = "cuda"
+    for B in (128, 256):
+        for cl in (False, True):
+            f4 = torch.rand((B, 512, 32, 32), device=dev)
+            f5 = torch.rand((B, 512, 16, 16), device=dev)
+            if cl:
+                f4, f5 = f4.contiguous(memory_format=torch.channels_last), f5.contiguous(memory_format=torch.channels_last)
+            out = torch.empty((B, 1024), device=dev)
+            nb = 4.0 * (f4.numel() + f5.numel()) + 4.0 * 1024 * B
+            ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], out=out), args.iters)
+            report("region_pool MAC B=%d %s" % (B, "nhwc" if cl else "nchw"), ms, best, nb)
+            regs = [ops.rmac_regions(32, 32, 3), ops.rmac_regions(16, 16, 3)]
+            ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
+            report("region_pool R-MAC L=3 B=%d %s" % (B, "nhwc" if cl else "nchw"), ms, best, nb)
+
+
+def bench_prep(args):
+    dev = "cuda"
+    for R, D in ((6400, 1024), (125000, 512), (1000000, 512)):
+        x = torch.randn((R, D), device=dev)
+        ms, best = timeit(lambda: ops.rows_prepare(x, True), args.iters)
+        report("rows_prepare %dx%d" % (R, D), ms, best, 6.0 * R * D + 4.0 * R)
+
+
+def bench_sim(args):
+    dev = "cuda"
+    shapes = [(200, 180, 1024, 1), (6400, 8192, 1024, 5), (25000, 125000, 512, 5), (100000, 125000, 512, 5)]
+    if args.quick:
+        shapes = shapes[:3]
+    for Q, G, D, k in shapes:
+        q = torch.randn((Q, D), device=dev)
+        g = torch.randn((G, D), device=dev)
+        q /= q.norm(dim=1, keepdim=True)
+        g /= g.norm(dim=1, keepdim=True)
+        qb, qi = ops.rows_prepare(q, True)
+        gb, gi = ops.rows_prepare(g, True)
+        ws = torch.empty(ops.sim_topk_workspace_bytes(Q, G, D, k) + 16, dtype=torch.uint8, device=dev)
+        fl = 2.0 * Q * G * D
+        ms, best = timeit(lambda: ops.sim_topk(qb, gb, k, 0, q, g, qi, gi, workspace=ws), args.iters)
+        report("sim_topk exact Q=%d G=%d D=%d k=%d" % (Q, G, D, k), ms, best, flops=fl)
+        ms, best = timeit(lambda: ops.sim_topk(qb, gb, k, 0, workspace=ws), args.iters)
+        report("sim_topk bf16-only Q=%d G=%d D=%d k=%d" % (Q, G, D, k), ms, best, flops=fl)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("which", nargs="*", default=["nms", "crop", "pool", "prep", "sim"])
+    ap.add_argument("--shelves", type=int, default=32)
+    ap.add_argument("--stress-images", type=int, default=512)
+    ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--sizes", type=int, nargs="*", default=[256, 224])
+    ap.add_argument("--quick", action="store_true")
+    args = ap.parse_args()
+    torch.cuda.set_device(0)
+    for w in args.which:
+        {"nms": bench_nms, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
+
+
+if __name__ == "__main__":
+    main()

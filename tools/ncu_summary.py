@@ -1,0 +1,77 @@
+#!/usr/bin/env python
+"""Turns ncu output brought back in gpurun_out/ into the small text summaries committed under profiles/.
+
+    python tools/ncu_summary.py launches gpurun_out/<tag>/launches.csv  > profiles/<name>_launches.txt
+    python tools/ncu_summary.py full     gpurun_out/<tag>/prof.ncu-rep  > profiles/<name>_ncu_full.txt
+"""
+import collections
+import csv
+import io
+import re
+import subprocess
+import sys
+
+FULL_METRICS = [
+    "gpu__time_duration.sum",
+    "launch__grid_size", "launch__block_size", "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic",
+    "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    "dram__cycles_active.avg.pct_of_peak_sustained_elapsed",
+    "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "smsp__inst_executed.sum", "sm__cycles_elapsed.max",
+]
+
+
+def launches(path):
+    with open(path) as f:
+        lines = [ln for ln in f if not ln.startswith("==")]
+    agg = collections.OrderedDict()
+    order = []
+    for row in csv.DictReader(lines):
+        if row.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        v = float(row["Metric Value"].replace(",", ""))
+        u = row["Metric Unit"]
+        v = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
+        name = re.sub(r"\(.*", "", row["Kernel Name"])
+        name = re.sub(r"^void ", "", name)[:100]
+        a = agg.setdefault(name, [0, 0.0])
+        a[0] += 1
+        a[1] += v
+        order.append((name, v))
+    tot = sum(a[1] for a in agg.values())
+    n = sum(a[0] for a in agg.values())
+    print("# ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised: compare SHARES)")
+    print("# %d launches, %.1f us total" % (n, tot))
+    print("%12s %7s %6s  %s" % ("total_us", "share", "n", "kernel"))
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print("%12.1f %6.2f%% %6d  %s" % (a[1], 100 * a[1] / tot, a[0], k))
+    own = sum(a[1] for k, a in agg.items() if k.startswith("cvpce::"))
+    print("# own kernels (cvpce::*): %.1f us = %.2f%% of all GPU time in the profiled command" % (own, 100 * own / tot))
+
+
+def full(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    print("# ncu --set full --clock-control none: selected raw metrics per captured launch (%s)" % path)
+    seen = collections.Counter()
+    for d in data:
+        name = re.sub(r"^void ", "", d[idx["Kernel Name"]])
+        short = re.sub(r"\(.*", "", name)
+        seen[short] += 1
+        if seen[short] > 2:
+            continue
+        print("\n== %s   [launch #%d of this kernel]" % (name[:140], seen[short]))
+        for m in FULL_METRICS:
+            if m in idx:
+                print("  %-78s %s %s" % (m, d[idx[m]], units[idx[m]]))
+    print("\n# launches captured per kernel: " + ", ".join("%s x%d" % kv for kv in seen.items()))
+
+
+if __name__ == "__main__":
+    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
