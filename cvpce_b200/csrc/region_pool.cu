@@ -4,13 +4,23 @@
 // clamp(min=eps)) and :79-85 (MACResNet).  R-MAC (regions + per-region L2 + sum) is the north-star extension.
 //
 // One thread-block CLUSTER (8 CTAs) per crop: CTA r of the cluster owns the r-th channel slab of every feature map,
-// streams those planes once from HBM (128-bit loads, one warp per plane, warp-shuffle max), keeps the region maxima
-// in shared memory, and the norms that span all channels (per-region L2 and the final L2) are all-reduced across the
-// cluster through distributed shared memory -- no workspace, no second launch, the descriptor is written once.
-// With several regions per map the plane is staged in shared memory and every region is evaluated from there.
+// streams it once from HBM, keeps the region maxima in shared memory, and the norms that span all channels (per-region
+// L2 and the final L2) are all-reduced across the cluster through distributed shared memory -- no workspace, no second
+// launch, the descriptor is written once.
+//
+// Every feature value is read from HBM exactly once, whatever the number of (overlapping) regions: the host splits the
+// rows and the columns of a map into the elementary SEGMENTS between region boundaries, the streaming pass reduces each
+// segment once, and a region is then the maximum over the few segments it spans.
+//  * NCHW maps: one warp per plane.  MAC: 128-bit streaming loads + warp-shuffle max.  R-MAC: lane = column; the warp
+//    walks the rows once (coalesced 128-byte rows) keeping the column maxima of the current ROW segment, parks them in
+//    shared memory, then lane r reduces the row segments x column range of region r.
+//  * channels-last (NHWC) maps: 4 channels per thread (one 128-bit load per pixel), one row per thread group; the
+//    maxima of every COLUMN segment of the row go to shared memory, then one thread per (region, channel) reduces the
+//    region's rows x column segments.
 #include "common.cuh"
 #include <cooperative_groups.h>
 #include <math.h>
+#include <algorithm>
 
 namespace cg = cooperative_groups;
 
@@ -18,9 +28,11 @@ namespace cvpce {
 
 constexpr int kPoolThreads = 256;
 constexpr int kPoolWarps = kPoolThreads / 32;
-constexpr int kPlaneCap = 1024;  // floats staged per warp (32x32 map)
 constexpr int kPoolCluster = 8;
 constexpr int kMaxRegionsTotal = 64;
+constexpr int kMaxSegs = 16;   // elementary row / column segments per map handled by the separable paths
+constexpr int kCmPitch = 33;   // per-warp column-maxima rows, padded against bank conflicts
+constexpr int kWarpScratch = kMaxSegs * kCmPitch + 4 * kMaxSegs * kMaxSegs;  // NCHW R-MAC: column maxima + cell maxima (<= 4 planes) per warp
 
 struct PoolMap {
   const void* data;
@@ -32,17 +44,22 @@ struct PoolMap {
   int vals_offset;              // float offset of this map's [n_regions][slab] block in smem
   int desc_offset;              // float offset of this map's [slab] block in the descriptor smem
   int whole;                    // 1: single region covering the whole map
+  int nxs, nys;                 // elementary column / row segments (0: too many -> generic path)
+  unsigned char xb[kMaxSegs + 1], yb[kMaxSegs + 1];  // segment s = [b[s], b[s+1])  (maps up to 255 cells per side)
+  int nhwc;                     // 1: channels-last fast path applies (unit channel stride, aligned channel quads)
 };
 
 struct PoolParams {
   PoolMap maps[CVPCE_POOL_MAX_MAPS];
   int4 regions[kMaxRegionsTotal];  // (y0,x0,y1,x1)
+  uchar4 segs[kMaxRegionsTotal];   // (first row segment, end row segment, first column segment, end column segment)
   int n_maps, B;
   int per_region_l2, final_l2;
   float eps;
   float* out;
   long long out_stride;
   int vals_total, desc_total, pairs_total;
+  int scratch_floats;  // shared scratch: NHWC cell maxima [nys][nxs][slab] | NCHW [warps][kWarpScratch]
 };
 
 template <int DTYPE>
@@ -65,11 +82,244 @@ __device__ __forceinline__ uint4 ldg_stream_u4(const uint4* p) {
                : "l"(p));
   return r;
 }
+__device__ __forceinline__ float ldg_stream_f1(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
 __device__ __forceinline__ float bf16lo(unsigned u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(unsigned u) { return __uint_as_float(u & 0xffff0000u); }
 
+// 4 consecutive channels of one pixel
 template <int DTYPE>
-__global__ void __launch_bounds__(kPoolThreads) region_pool_kernel(const __grid_constant__ PoolParams p) {
+__device__ __forceinline__ float4 load_quad(const char* p) {
+  if (DTYPE == CVPCE_F32) return ldg_stream_f4(reinterpret_cast<const float4*>(p));
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return make_float4(bf16lo(r.x), bf16hi(r.x), bf16lo(r.y), bf16hi(r.y));
+}
+__device__ __forceinline__ void max4(float4& a, const float4& b) {
+  a.x = fmaxf(a.x, b.x);
+  a.y = fmaxf(a.y, b.y);
+  a.z = fmaxf(a.z, b.z);
+  a.w = fmaxf(a.w, b.w);
+}
+
+// monotone float <-> int mapping so that shared-memory atomicMax (s32) orders floats of either sign
+__device__ __forceinline__ int f2ord(float f) {
+  const int i = __float_as_int(f);
+  return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// channels-last phase 1 for one map: region maxima of channels [c_lo, c_lo + nplanes) of crop n -> vals.
+// Stage A: thread group g (nplanes/4 threads, 4 channels each) walks rows g, g+G, ... with NB independent 128-bit loads
+// in flight; the maximum of every column segment of the row is folded into cells[row segment][column segment][channel]
+// with shared-memory atomicMax.  Stage B: one thread per (region, channel) reduces the region's cells.
+// MAC is the one-cell, one-region case of the same code.
+// ------------------------------------------------------------------------------------------------------------------------
+template <int DTYPE, int NB>
+__device__ __forceinline__ void pool_map_nhwc(const PoolParams& p, const PoolMap& mp, int n, int c_lo, int nplanes, float* scratch,
+                                              float* vals) {
+  constexpr int ESZ = (DTYPE == CVPCE_F32) ? 4 : 2;
+  const int tid = threadIdx.x;
+  const int tpp = nplanes >> 2;  // threads per pixel
+  const int groups = kPoolThreads / tpp;
+  const int g = tid / tpp, cq = tid - g * tpp;
+  const int ns = mp.nxs;
+  int* cells = reinterpret_cast<int*>(scratch);  // [nys][ns][nplanes], order-mapped floats
+  const int ncell = mp.nys * ns * nplanes;
+  const int neg_inf = f2ord(-INFINITY);
+  for (int i = tid; i < ncell; i += kPoolThreads) cells[i] = neg_inf;
+  __syncthreads();
+  if (g < groups) {
+    const char* base = reinterpret_cast<const char*>(mp.data) + ((long long)n * mp.sn + c_lo + 4 * cq) * ESZ;
+    const long long xstep = mp.sw * ESZ;
+    const int x_first = mp.xb[0], x_last = mp.xb[ns];
+    for (int y = g; y < mp.H; y += groups) {
+      if (y < mp.yb[0] || y >= mp.yb[mp.nys]) continue;  // row outside every region
+      int ys = 0;
+      while (y >= mp.yb[ys + 1]) ++ys;
+      int* dst = cells + (ys * ns) * nplanes + 4 * cq;
+      const char* rowp = base + (long long)y * mp.sh * ESZ;
+      int sx = 0, next = mp.xb[1];
+      float4 acc = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+      for (int xb0 = x_first; xb0 < x_last; xb0 += NB) {
+        float4 v[NB];
+#pragma unroll
+        for (int u = 0; u < NB; ++u)
+          if (xb0 + u < x_last) v[u] = load_quad<DTYPE>(rowp + (xb0 + u) * xstep);
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+          const int x = xb0 + u;
+          if (x < x_last) {
+            if (x == next) {  // CTA-uniform: column-segment boundary
+              atomicMax(dst, f2ord(acc.x));
+              atomicMax(dst + 1, f2ord(acc.y));
+              atomicMax(dst + 2, f2ord(acc.z));
+              atomicMax(dst + 3, f2ord(acc.w));
+              acc = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+              dst += nplanes;
+              ++sx;
+              next = mp.xb[sx + 1];
+            }
+            max4(acc, v[u]);
+          }
+        }
+      }
+      atomicMax(dst, f2ord(acc.x));
+      atomicMax(dst + 1, f2ord(acc.y));
+      atomicMax(dst + 2, f2ord(acc.z));
+      atomicMax(dst + 3, f2ord(acc.w));
+    }
+  }
+  __syncthreads();
+  for (int it = tid; it < mp.n_regions * nplanes; it += kPoolThreads) {
+    const int r = it / nplanes, pc = it - r * nplanes;
+    const uchar4 sg = p.segs[mp.region_begin + r];
+    int v0 = neg_inf, v1 = neg_inf;
+    for (int ys = sg.x; ys < sg.y; ++ys) {
+      const int* crow = cells + (ys * ns) * nplanes + pc;
+      int xs = sg.z;
+      for (; xs + 1 < sg.w; xs += 2) {
+        v0 = max(v0, crow[xs * nplanes]);
+        v1 = max(v1, crow[(xs + 1) * nplanes]);
+      }
+      if (xs < sg.w) v0 = max(v0, crow[xs * nplanes]);
+    }
+    vals[mp.vals_offset + r * mp.slab + pc] = ord2f(max(v0, v1));
+  }
+  __syncthreads();  // the scratch is reused by the next map
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// NCHW, whole-map maximum of one plane by one warp (MAC)
+// ------------------------------------------------------------------------------------------------------------------------
+template <int DTYPE>
+__device__ __forceinline__ float plane_max_whole(const PoolMap& mp, long long poff, int lane) {
+  constexpr int VEC = (DTYPE == CVPCE_F32) ? 4 : 8;
+  constexpr int ESZ = (DTYPE == CVPCE_F32) ? 4 : 2;
+  const int HW = mp.H * mp.W;
+  const char* pbase = reinterpret_cast<const char*>(mp.data) + poff * ESZ;
+  const bool vec_ok = (mp.sw == 1 && mp.sh == mp.W) && (HW % VEC == 0) && ((reinterpret_cast<uintptr_t>(pbase) & 15u) == 0);
+  float v = -INFINITY;
+  if (vec_ok) {
+    const int nv = HW / VEC;
+    if (DTYPE == CVPCE_F32) {
+      const float4* src = reinterpret_cast<const float4*>(pbase);
+      int i = lane;
+      for (; i + 96 < nv; i += 128) {  // 4 independent 128-bit loads in flight per lane
+        const float4 a = ldg_stream_f4(src + i), b = ldg_stream_f4(src + i + 32);
+        const float4 c = ldg_stream_f4(src + i + 64), d = ldg_stream_f4(src + i + 96);
+        v = fmaxf(v, fmaxf(fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)), fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w))));
+        v = fmaxf(v, fmaxf(fmaxf(fmaxf(c.x, c.y), fmaxf(c.z, c.w)), fmaxf(fmaxf(d.x, d.y), fmaxf(d.z, d.w))));
+      }
+      for (; i < nv; i += 32) {
+        const float4 a = ldg_stream_f4(src + i);
+        v = fmaxf(v, fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)));
+      }
+    } else {
+      const uint4* src = reinterpret_cast<const uint4*>(pbase);
+      for (int i = lane; i < nv; i += 32) {
+        const uint4 a = ldg_stream_u4(src + i);
+        v = fmaxf(v, fmaxf(fmaxf(fmaxf(bf16lo(a.x), bf16hi(a.x)), fmaxf(bf16lo(a.y), bf16hi(a.y))),
+                           fmaxf(fmaxf(bf16lo(a.z), bf16hi(a.z)), fmaxf(bf16lo(a.w), bf16hi(a.w)))));
+      }
+    }
+  } else {
+    for (int i = lane; i < HW; i += 32) {
+      const int y = i / mp.W, x = i - y * mp.W;
+      v = fmaxf(v, load_elem<DTYPE>(mp.data, poff + y * mp.sh + x * mp.sw));
+    }
+  }
+  return warp_max(v);
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// NCHW, several regions (R-MAC), W <= 32 and H <= 32: a warp handles 32/Wp planes at a time (Wp = W rounded up to 8, 16
+// or 32), lane = (plane, column).  Every lane first pulls its whole column into registers (up to 32 independent loads
+// in flight), folds it into the maxima of the row segments (boundaries are warp-uniform), parks them in cm[s][lane];
+// then one lane per (plane, cell) reduces the cell's columns and one lane per (plane, region) the region's cells.
+// ------------------------------------------------------------------------------------------------------------------------
+template <int DTYPE>
+__device__ __forceinline__ void planes_regions_nchw(const PoolParams& p, const PoolMap& mp, int n, int c_lo, int nplanes, int warp,
+                                                    int lane, float* wscratch, float* vals) {
+  const int Wp = mp.W > 16 ? 32 : (mp.W > 8 ? 16 : 8);
+  const int ppw = 32 / Wp;  // planes per warp pass
+  const int x = lane % Wp, psub = lane / Wp;
+  const int y_first = mp.yb[0], y_last = mp.yb[mp.nys];
+  float* cm = wscratch;                           // [nys][kCmPitch]
+  float* cells = wscratch + kMaxSegs * kCmPitch;  // [ppw][nys][nxs]
+  const int ncell = mp.nys * mp.nxs;
+  for (int pg = warp; pg * ppw < nplanes; pg += kPoolWarps) {
+    const int pc = pg * ppw + psub;
+    const bool live = x < mp.W && pc < nplanes;
+    const long long poff = (long long)n * mp.sn + (long long)(c_lo + pc) * mp.sc + (long long)x * mp.sw;
+    float colv[32];
+#pragma unroll
+    for (int y = 0; y < 32; ++y) {
+      colv[y] = -INFINITY;
+      if (live && y >= y_first && y < y_last) colv[y] = load_elem<DTYPE>(mp.data, poff + (long long)y * mp.sh);
+    }
+    int sy = 0, next = mp.yb[1];
+    float v = -INFINITY;
+#pragma unroll
+    for (int y = 0; y < 32; ++y) {
+      if (y >= y_first && y < y_last) {  // warp-uniform
+        if (y == next) {                 // warp-uniform: row-segment boundary
+          cm[sy * kCmPitch + lane] = v;
+          v = -INFINITY;
+          ++sy;
+          next = mp.yb[sy + 1];
+        }
+        v = fmaxf(v, colv[y]);
+      }
+    }
+    cm[sy * kCmPitch + lane] = v;
+    __syncwarp();
+    for (int c = lane; c < ncell * ppw; c += 32) {
+      const int ps = c / ncell, cc = c - ps * ncell;
+      const int ys = cc / mp.nxs, xs = cc - ys * mp.nxs;
+      const float* row = cm + ys * kCmPitch + ps * Wp;
+      float v0 = -INFINITY, v1 = -INFINITY;
+      int xx = mp.xb[xs];
+      const int xe = mp.xb[xs + 1];
+      for (; xx + 1 < xe; xx += 2) {
+        v0 = fmaxf(v0, row[xx]);
+        v1 = fmaxf(v1, row[xx + 1]);
+      }
+      if (xx < xe) v0 = fmaxf(v0, row[xx]);
+      cells[c] = fmaxf(v0, v1);
+    }
+    __syncwarp();
+    for (int it = lane; it < mp.n_regions * ppw; it += 32) {
+      const int ps = it / mp.n_regions, r = it - ps * mp.n_regions;
+      const int pcr = pg * ppw + ps;
+      if (pcr >= nplanes) continue;
+      const uchar4 sg = p.segs[mp.region_begin + r];
+      float v0 = -INFINITY, v1 = -INFINITY;
+      for (int ys = sg.x; ys < sg.y; ++ys) {
+        const float* crow = cells + ps * ncell + ys * mp.nxs;
+        int xs = sg.z;
+        for (; xs + 1 < sg.w; xs += 2) {
+          v0 = fmaxf(v0, crow[xs]);
+          v1 = fmaxf(v1, crow[xs + 1]);
+        }
+        if (xs < sg.w) v0 = fmaxf(v0, crow[xs]);
+      }
+      vals[mp.vals_offset + r * mp.slab + pcr] = fmaxf(v0, v1);
+    }
+    __syncwarp();  // cm / cells are reused by this warp's next pass
+  }
+}
+
+// GENERAL = false: every map is pooled over its whole extent (MAC, the reference's mode) -- the region code is not
+// compiled in, which keeps the streaming kernel at 4 resident CTAs per SM.
+// NHWC_ONLY = true: every map takes the channels-last path -- the per-plane NCHW code (and its 32-register column
+// buffer) is not compiled in, so the region kernel also fits 4 resident CTAs per SM.
+template <int DTYPE, bool GENERAL, bool NHWC_ONLY>
+__global__ void __launch_bounds__(kPoolThreads, GENERAL ? (NHWC_ONLY ? 3 : 2) : 4) region_pool_kernel(const __grid_constant__ PoolParams p) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned crank = cluster.block_rank();
   const unsigned csize = cluster.num_blocks();
@@ -79,7 +329,7 @@ __global__ void __launch_bounds__(kPoolThreads) region_pool_kernel(const __grid_
   extern __shared__ __align__(16) float smem[];
   float* vals = smem;                         // [vals_total]
   float* desc = vals + p.vals_total;          // [desc_total]
-  float* planes = desc + p.desc_total;        // [kPoolWarps][kPlaneCap]
+  float* scratch = desc + p.desc_total;       // [scratch_floats]
   __shared__ float part[kMaxRegionsTotal];    // partial sum of squares per (map,region), read by the cluster
   __shared__ float denom[kMaxRegionsTotal];
   __shared__ float fpart;                     // partial sum of squares of the descriptor slab
@@ -90,82 +340,41 @@ __global__ void __launch_bounds__(kPoolThreads) region_pool_kernel(const __grid_
     const PoolMap& mp = p.maps[m];
     const int c_lo = (int)crank * mp.slab;
     const int nplanes = max(0, min(mp.slab, mp.C - c_lo));
-    const int HW = mp.H * mp.W;
-    const bool contiguous = (mp.sw == 1 && mp.sh == mp.W);
-    constexpr int VEC = (DTYPE == CVPCE_F32) ? 4 : 8;
-    constexpr int ESZ = (DTYPE == CVPCE_F32) ? 4 : 2;
+    if (NHWC_ONLY || mp.nhwc) {  // CTA-uniform
+      if (m > 0) __syncthreads();  // warps of the previous (NCHW) map may still be reading their part of the scratch
+      if (nplanes > 0) pool_map_nhwc<DTYPE, GENERAL ? 8 : 4>(p, mp, n, c_lo, nplanes, scratch, vals);
+      continue;
+    }
+    if (NHWC_ONLY) continue;
+    if (GENERAL && !mp.whole && mp.nys > 0 && mp.W <= 32 && mp.H <= 32) {  // CTA-uniform
+      planes_regions_nchw<DTYPE>(p, mp, n, c_lo, nplanes, warp, lane, scratch + warp * kWarpScratch, vals);
+      continue;
+    }
     for (int pc = warp; pc < nplanes; pc += kPoolWarps) {
       const long long poff = (long long)n * mp.sn + (long long)(c_lo + pc) * mp.sc;
-      const char* pbase = reinterpret_cast<const char*>(mp.data) + poff * ESZ;
-      const bool vec_ok = contiguous && (HW % VEC == 0) && ((reinterpret_cast<uintptr_t>(pbase) & 15u) == 0);
       float* vout = vals + mp.vals_offset + pc;
-      if (mp.whole) {
-        float v = -INFINITY;
-        if (vec_ok) {
-          const int nv = HW / VEC;
-          if (DTYPE == CVPCE_F32) {
-            const float4* src = reinterpret_cast<const float4*>(pbase);
-            int i = lane;
-            for (; i + 96 < nv; i += 128) {  // 4 independent 128-bit loads in flight per lane
-              const float4 a = ldg_stream_f4(src + i), b = ldg_stream_f4(src + i + 32);
-              const float4 c = ldg_stream_f4(src + i + 64), d = ldg_stream_f4(src + i + 96);
-              v = fmaxf(v, fmaxf(fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)), fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w))));
-              v = fmaxf(v, fmaxf(fmaxf(fmaxf(c.x, c.y), fmaxf(c.z, c.w)), fmaxf(fmaxf(d.x, d.y), fmaxf(d.z, d.w))));
-            }
-            for (; i < nv; i += 32) {
-              const float4 a = ldg_stream_f4(src + i);
-              v = fmaxf(v, fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)));
-            }
-          } else {
-            const uint4* src = reinterpret_cast<const uint4*>(pbase);
-            for (int i = lane; i < nv; i += 32) {
-              const uint4 a = ldg_stream_u4(src + i);
-              v = fmaxf(v, fmaxf(fmaxf(fmaxf(bf16lo(a.x), bf16hi(a.x)), fmaxf(bf16lo(a.y), bf16hi(a.y))),
-                                 fmaxf(fmaxf(bf16lo(a.z), bf16hi(a.z)), fmaxf(bf16lo(a.w), bf16hi(a.w)))));
-            }
-          }
-        } else {
-          for (int i = lane; i < HW; i += 32) {
-            const int y = i / mp.W, x = i - y * mp.W;
-            v = fmaxf(v, load_elem<DTYPE>(mp.data, poff + y * mp.sh + x * mp.sw));
-          }
-        }
-        v = warp_max(v);
+      if (!GENERAL || mp.whole) {
+        const float v = plane_max_whole<DTYPE>(mp, poff, lane);
         if (lane == 0) vout[0] = v;
       } else {
-        const bool staged = HW <= kPlaneCap;
-        float* pl = planes + warp * kPlaneCap;
-        if (staged) {
-          if (vec_ok && DTYPE == CVPCE_F32) {
-            const float4* src = reinterpret_cast<const float4*>(pbase);
-            for (int i = lane; i < HW / 4; i += 32) reinterpret_cast<float4*>(pl)[i] = ldg_stream_f4(src + i);
-          } else {
-            for (int i = lane; i < HW; i += 32) {
-              const int y = i / mp.W, x = i - y * mp.W;
-              pl[i] = load_elem<DTYPE>(mp.data, poff + y * mp.sh + x * mp.sw);
-            }
-          }
-          __syncwarp();
-        }
-        for (int r = 0; r < mp.n_regions; ++r) {
+        for (int r = 0; r < mp.n_regions; ++r) {  // generic: any strides, any size, any region list
           const int4 rg = p.regions[mp.region_begin + r];
           const int rw = rg.w - rg.y, rh = rg.z - rg.x;
           float v = -INFINITY;
           for (int i = lane; i < rw * rh; i += 32) {
             const int y = rg.x + i / rw, x = rg.y + i % rw;
-            v = fmaxf(v, staged ? pl[y * mp.W + x] : load_elem<DTYPE>(mp.data, poff + y * mp.sh + x * mp.sw));
+            v = fmaxf(v, load_elem<DTYPE>(mp.data, poff + y * mp.sh + x * mp.sw));
           }
           v = warp_max(v);
           if (lane == 0) vout[r * mp.slab] = v;
         }
-        __syncwarp();
       }
     }
   }
   __syncthreads();
 
   // ---- phase 2: per-region L2 norms over ALL channels (cluster all-reduce through DSMEM) -----------------------------
-  if (p.per_region_l2) {
+  if (GENERAL && p.per_region_l2) {
     for (int pair = warp; pair < p.pairs_total; pair += kPoolWarps) {
       // locate the map of this (map,region) pair
       int m = 0;
@@ -199,7 +408,7 @@ __global__ void __launch_bounds__(kPoolThreads) region_pool_kernel(const __grid_
       float d = 0.f;
       for (int r = 0; r < mp.n_regions; ++r) {
         float v = vals[mp.vals_offset + r * mp.slab + pc];
-        if (p.per_region_l2) v = v / denom[mp.region_begin + r];
+        if (GENERAL && p.per_region_l2) v = v / denom[mp.region_begin + r];
         d = (r == 0) ? v : d + v;
       }
       desc[mp.desc_offset + pc] = d;
@@ -293,6 +502,29 @@ extern "C" int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, in
   return count;
 }
 
+// Elementary segments between the distinct boundaries of a list of [lo,hi) intervals: b[0..ns]; returns ns (0 if more
+// than kMaxSegs or a boundary does not fit a byte).
+namespace cvpce {
+static int make_segments(const int* lo, const int* hi, int n, unsigned char* b) {
+  int pts[2 * CVPCE_POOL_MAX_REGIONS];
+  int np = 0;
+  for (int i = 0; i < n; ++i) {
+    pts[np++] = lo[i];
+    pts[np++] = hi[i];
+  }
+  std::sort(pts, pts + np);
+  np = (int)(std::unique(pts, pts + np) - pts);
+  if (np - 1 > kMaxSegs || pts[np - 1] > 255) return 0;
+  for (int i = 0; i < np; ++i) b[i] = (unsigned char)pts[i];
+  return np - 1;
+}
+static int seg_index(const unsigned char* b, int ns, int v) {
+  for (int i = 0; i <= ns; ++i)
+    if (b[i] == v) return i;
+  return 0;
+}
+}  // namespace cvpce
+
 extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
                                        const int32_t* regions, const int32_t* n_regions, int per_region_l2,
                                        int final_l2, float eps, float* out, int64_t out_stride, void* stream) {
@@ -313,7 +545,8 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   p.eps = eps;
   p.out = out;
   p.out_stride = out_stride;
-  int rbeg = 0, col = 0, vals = 0, desc = 0;
+  int rbeg = 0, col = 0, vals = 0, desc = 0, scratch = kPoolWarps * kWarpScratch;
+  bool all_whole = true;
   const int32_t* rg = regions;
   for (int m = 0; m < n_maps; ++m) {
     const cvpce_feature_map& fm = maps[m];
@@ -327,14 +560,25 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
     CVPCE_REQUIRE(pm.n_regions >= 1 && pm.n_regions <= CVPCE_POOL_MAX_REGIONS && rbeg + pm.n_regions <= kMaxRegionsTotal,
                   CVPCE_ERR_UNSUPPORTED, "region_pool: map %d has %d regions (per map <= %d, total <= %d)", m, pm.n_regions, CVPCE_POOL_MAX_REGIONS, kMaxRegionsTotal);
     pm.whole = 0;
+    int x0[CVPCE_POOL_MAX_REGIONS], x1[CVPCE_POOL_MAX_REGIONS], y0[CVPCE_POOL_MAX_REGIONS], y1[CVPCE_POOL_MAX_REGIONS];
     for (int r = 0; r < pm.n_regions; ++r) {
       int4 q = rg ? make_int4(rg[0], rg[1], rg[2], rg[3]) : make_int4(0, 0, fm.H, fm.W);
       if (rg) rg += 4;
       CVPCE_REQUIRE(q.x >= 0 && q.y >= 0 && q.z > q.x && q.w > q.y && q.z <= fm.H && q.w <= fm.W, CVPCE_ERR_INVALID_ARG,
                     "region_pool: map %d region %d = (%d,%d,%d,%d) is empty or outside the %dx%d map", m, r, q.x, q.y, q.z, q.w, fm.H, fm.W);
       p.regions[rbeg + r] = q;
+      y0[r] = q.x; x0[r] = q.y; y1[r] = q.z; x1[r] = q.w;
       if (pm.n_regions == 1 && q.x == 0 && q.y == 0 && q.z == fm.H && q.w == fm.W) pm.whole = 1;
     }
+    if (!pm.whole) all_whole = false;
+    // elementary row / column segments between region boundaries (each is reduced once by the streaming pass)
+    pm.nxs = make_segments(x0, x1, pm.n_regions, pm.xb);
+    pm.nys = make_segments(y0, y1, pm.n_regions, pm.yb);
+    if (pm.nxs == 0 || pm.nys == 0) pm.nxs = pm.nys = 0;
+    for (int r = 0; r < pm.n_regions; ++r)
+      p.segs[rbeg + r] = pm.nxs ? make_uchar4((unsigned char)seg_index(pm.yb, pm.nys, y0[r]), (unsigned char)seg_index(pm.yb, pm.nys, y1[r]),
+                                              (unsigned char)seg_index(pm.xb, pm.nxs, x0[r]), (unsigned char)seg_index(pm.xb, pm.nxs, x1[r]))
+                                : make_uchar4(0, 0, 0, 0);
     rbeg += pm.n_regions;
     pm.out_offset = col;
     col += fm.C;
@@ -343,17 +587,41 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
     vals += pm.n_regions * pm.slab;
     pm.desc_offset = desc;
     desc += pm.slab;
+    // channels-last fast path: unit channel stride, every CTA's slab made of whole, 16-byte (f32) / 8-byte (bf16) aligned quads
+    const int esz = dtype == CVPCE_F32 ? 4 : 2;
+    const uintptr_t align_mask = (uintptr_t)(4 * esz - 1);
+    pm.nhwc = (fm.stride_c == 1 && fm.C > 1 && fm.stride_w >= fm.C && fm.C % (4 * kPoolCluster) == 0 && pm.slab <= 4 * kPoolThreads &&
+               pm.nxs > 0 && (reinterpret_cast<uintptr_t>(fm.data) & align_mask) == 0 && fm.stride_n % 4 == 0 &&
+               fm.stride_h % 4 == 0 && fm.stride_w % 4 == 0)
+                  ? 1 : 0;
+    if (pm.nhwc) {
+      const long long need = (long long)pm.nys * pm.nxs * pm.slab;  // cell maxima
+      if (need > 24 * 1024) pm.nhwc = 0;  // segment-maxima scratch capped at 96 KB
+      else if (need > scratch) scratch = (int)need;
+    }
   }
   CVPCE_REQUIRE(out_stride >= col, CVPCE_ERR_INVALID_ARG, "region_pool: out_stride %lld < descriptor size %d", (long long)out_stride, col);
   p.vals_total = (vals + 3) & ~3;
   p.desc_total = (desc + 3) & ~3;
   p.pairs_total = rbeg;
-  const size_t smem = (size_t)(p.vals_total + p.desc_total + kPoolWarps * kPlaneCap) * sizeof(float);
+  p.scratch_floats = (scratch + 3) & ~3;
+  const size_t smem = (size_t)(p.vals_total + p.desc_total + p.scratch_floats) * sizeof(float);
   CVPCE_REQUIRE(smem <= 200 * 1024, CVPCE_ERR_UNSUPPORTED, "region_pool: %zu bytes of shared memory needed (regions x channels too large)", smem);
   CVPCE_REQUIRE((long long)B * kPoolCluster < 2147483647ll, CVPCE_ERR_UNSUPPORTED, "region_pool: B too large");
 
-  auto kern = dtype == CVPCE_F32 ? region_pool_kernel<CVPCE_F32> : region_pool_kernel<CVPCE_BF16>;
-  if (smem > 48 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const bool general = !all_whole || per_region_l2;
+  bool all_nhwc = true;
+  for (int m = 0; m < n_maps; ++m) all_nhwc = all_nhwc && p.maps[m].nhwc;
+  void (*kern)(PoolParams);
+  if (dtype == CVPCE_F32) {
+    kern = all_nhwc ? (general ? region_pool_kernel<CVPCE_F32, true, true> : region_pool_kernel<CVPCE_F32, false, true>)
+                    : (general ? region_pool_kernel<CVPCE_F32, true, false> : region_pool_kernel<CVPCE_F32, false, false>);
+  } else {
+    kern = all_nhwc ? (general ? region_pool_kernel<CVPCE_BF16, true, true> : region_pool_kernel<CVPCE_BF16, false, true>)
+                    : (general ? region_pool_kernel<CVPCE_BF16, true, false> : region_pool_kernel<CVPCE_BF16, false, false>);
+  }
+  // the default 48 KB limit covers static + dynamic shared memory: opt in with a margin for the static part
+  if (smem > 40 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(B * kPoolCluster));
   cfg.blockDim = dim3(kPoolThreads);

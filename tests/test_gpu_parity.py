@@ -245,6 +245,38 @@ def test_rmac_regions_mode(ops):
     np.testing.assert_allclose(out, want, rtol=1e-6, atol=0)
 
 
+@pytest.mark.parametrize("hw", [(32, 16), (28, 14)])
+def test_rmac_vgg_shapes_layouts_dtypes(ops, hw):
+    """R-MAC (north-star extension; oracle = Tolias et al. restatement, parity unpinned by the reference) on VGG-sized
+    maps through every kernel path: NCHW separable, channels-last separable, bf16, and the generic path (a region
+    list with more than 8 distinct ranges)."""
+    rs = np.random.RandomState(hw[0])
+    B = 5
+    f4 = np.maximum(rs.randn(B, 512, hw[0], hw[0]), 0).astype(np.float32)
+    f5 = np.maximum(rs.randn(B, 512, hw[1], hw[1]), 0).astype(np.float32)
+    regions = [oracle.rmac_regions(hw[0], hw[0], 3).tolist(), oracle.rmac_regions(hw[1], hw[1], 3).tolist()]
+    want = oracle.region_pool_embed([f4, f5], regions, per_region_l2=True)
+    want_raw = oracle.region_pool_embed([f4, f5], regions, per_region_l2=False, final_l2=False)
+    g4, g5 = dev(f4), dev(f5)
+    c4, c5 = g4.contiguous(memory_format=torch.channels_last), g5.contiguous(memory_format=torch.channels_last)
+    for a, b in ((g4, g5), (c4, c5), (g4, c5)):
+        out = ops.region_pool_embed([a, b], regions=regions, per_region_l2=True).cpu().numpy()
+        np.testing.assert_allclose(out, want, rtol=1e-5, atol=1e-7)
+        raw = ops.region_pool_embed([a, b], regions=regions, per_region_l2=False, final_l2=False).cpu().numpy()
+        np.testing.assert_allclose(raw, want_raw, rtol=1e-6, atol=0)  # sums of exact maxima
+    b4, b5 = g4.bfloat16(), g5.bfloat16()
+    want_bf = oracle.region_pool_embed([b4.float().cpu().numpy(), b5.float().cpu().numpy()], regions, per_region_l2=True)
+    for a, b in ((b4, b5), (b4.contiguous(memory_format=torch.channels_last), b5.contiguous(memory_format=torch.channels_last))):
+        np.testing.assert_allclose(ops.region_pool_embed([a, b], regions=regions, per_region_l2=True).cpu().numpy(), want_bf,
+                                   rtol=1e-5, atol=1e-7)
+    # irregular list: 12 regions with 12 distinct row and column ranges -> generic (non-separable) path
+    irregular = [[(i, i // 2, hw[0] - (i % 3), hw[0] - i // 3) for i in range(12)], [(0, 0, hw[1], hw[1])]]
+    want_irr = oracle.region_pool_embed([f4, f5], irregular, per_region_l2=True)
+    for a, b in ((g4, g5), (c4, c5)):
+        np.testing.assert_allclose(ops.region_pool_embed([a, b], regions=irregular, per_region_l2=True).cpu().numpy(), want_irr,
+                                   rtol=1e-5, atol=1e-7)
+
+
 def test_l2norm_rows(ops):
     x = np.random.RandomState(1).randn(77, 1000).astype(np.float32)
     x[5] = 0
