@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--k", type=int, default=5)
     ap.add_argument("--trunk", default="f32", choices=["f32", "bf16"], help="dtype of the torch VGG16 trunk")
     ap.add_argument("--channels-last", action="store_true")
+    ap.add_argument("--plain-trunk", action="store_true", help="call the torch trunk module by module in NCHW (the reference's way) "
+                    "instead of channels-last + torch.cudnn_convolution_relu")
     ap.add_argument("--trunk-batch", type=int, default=128)
     ap.add_argument("--cudnn-benchmark", action="store_true")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
@@ -113,6 +115,20 @@ def measured_peaks():
         return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(kernel, algorithmic_bytes):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full` capture of
+    this command (profiles/ncu_traffic.json, written by tools/ncu_summary.py traffic); None when no capture matches the
+    workload (the capture's algorithmic bytes per launch must agree within 5 %)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f).get(kernel)
+        if t and abs(t["algorithmic_bytes_per_launch"] - algorithmic_bytes) <= 0.05 * algorithmic_bytes:
+            return t["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 def dist_setup(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -176,7 +192,10 @@ def build_encoder(args, device):
     enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).to(device)
     if args.trunk == "bf16":
         enc = enc.to(torch.bfloat16)
-    if args.channels_last:
+    if not args.plain_trunk:
+        enc.enable_fast_trunk()
+        args.channels_last = True
+    elif args.channels_last:
         enc = enc.to(memory_format=torch.channels_last)
     return enc
 
@@ -273,11 +292,22 @@ def run_ours_shelves(args, world, rank, local):
         ent["share_of_step"] = round(d["ms"] / ms_total, 4)
         kernels[name] = ent
     ours_ms = sum(d["ms"] for d in stages.values())
-    dom = max((n for n in stages if n != "sim_topk"), key=lambda n: stages[n]["ms"])
+    # dominant kernel = the one of OUR kernels with the largest share of the step (summed over its launches)
+    dom = max(stages, key=lambda n: stages[n]["ms"])
     dd = stages[dom]
-    dom_gbs = dd["bytes"] / dd["launches"] / (dd["ms"] / dd["launches"] / 1e3) / 1e9
-    roofline = {"kernel": dom, "bound": "hbm", "achieved": round(dom_gbs, 1), "peak": peaks["hbm"], "unit": "GB/s",
-                "frac": round(dom_gbs / peaks["hbm"], 4), "traffic": None, "peak_source": peaks["source"] + " (hbm_gbs, burst copy)"}
+    traffic = ncu_traffic(dom, dd["bytes"] / dd["launches"])
+    if dom == "sim_topk":
+        dom_tf = dd["flops"] / dd["launches"] / (dd["ms"] / dd["launches"] / 1e3) / 1e12
+        roofline = {"kernel": dom, "bound": "tensor", "achieved": round(dom_tf, 1), "peak": peaks["tensor_sustained"], "unit": "TFLOP/s",
+                    "frac": round(dom_tf / peaks["tensor_sustained"], 4), "traffic": traffic,
+                    "peak_source": peaks["source"] + " (bf16_tflops_sustained: timed inside a long step)"}
+    else:
+        dom_gbs = dd["bytes"] / dd["launches"] / (dd["ms"] / dd["launches"] / 1e3) / 1e9
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": round(dom_gbs, 1), "peak": peaks["hbm"], "unit": "GB/s",
+                    "frac": round(dom_gbs / peaks["hbm"], 4), "traffic": traffic,
+                    "launches_per_step": dd["launches"] / args.steps, "avg_launch_ms": round(dd["ms"] / dd["launches"], 4),
+                    "algorithmic_bytes_per_launch": dd["bytes"] / dd["launches"],
+                    "peak_source": peaks["source"] + " (hbm_gbs, measured copy bandwidth)"}
 
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -285,8 +315,9 @@ def run_ours_shelves(args, world, rank, local):
         "dtype": "f32" if args.trunk == "f32" else "bf16", "data": "synthetic",
         "config": {"workload": "%s: %d shelves 2048x1536 x ~%d products per GPU -> NMS(0.5, top200) -> 256x256 crops -> VGG16(random init)+MAC"
                                " -> cosine top-%d vs %d x 1024 gallery" % (args.workload, n_shelves, args.products, args.k, G),
-                   "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16 (%s%s, tf32 convs %s)" % (
-                       args.trunk, ", channels_last" if args.channels_last else "", torch.backends.cudnn.allow_tf32),
+                   "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16, not rebuilt (%s%s%s, tf32 convs %s)" % (
+                       args.trunk, ", channels_last" if args.channels_last else "",
+                       "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32),
                    "similarity": "tcgen05 bf16 + exact fp32 re-score" if args.sim == "tc" else "cuda-core fp32",
                    "l2": "inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9),
                    "parallelism": "dp%d (independent images, no data-path collective)" % world},

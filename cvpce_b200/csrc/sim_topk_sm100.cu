@@ -390,39 +390,49 @@ __global__ void __launch_bounds__(128) sim_select_kernel(const float* __restrict
       my_i = ci[lane];
     }
   } else {
-    float last_s = INFINITY;
-    int last_i = -1;
-    bool first = true;
+    // every split's list is already sorted by (score desc, index asc) and the splits cover increasing index ranges:
+    // KP rounds of "best head wins"; lane l owns the heads of splits l, l+32, ...
+    constexpr int kMaxOwn = 2;  // n_split <= 64
+    int pos[kMaxOwn];
+#pragma unroll
+    for (int o = 0; o < kMaxOwn; ++o) pos[o] = 0;
     for (int r = 0; r < KP; ++r) {
       float bs = -INFINITY;
-      int bi = -1;
-      for (int c = lane; c < C; c += 32) {
-        const float s = cs[c];
-        const int i = ci[c];
-        if (i < 0) continue;
-        const bool after_last = first || before(last_s, last_i, s, i);
-        if (after_last && before(s, i, bs, bi)) {
-          bs = s;
-          bi = i;
+      int bi = -1, bo = 0;
+#pragma unroll
+      for (int o = 0; o < kMaxOwn; ++o) {
+        const int sp = lane + 32 * o;
+        if (sp < n_split && pos[o] < KP) {
+          const float sc = cs[sp * KP + pos[o]];
+          const int ix = ci[sp * KP + pos[o]];
+          if (ix >= 0 && before(sc, ix, bs, bi)) {
+            bs = sc;
+            bi = ix;
+            bo = o;
+          }
         }
       }
+      float ws = bs;
+      int wi = bi;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        const float os = __shfl_xor_sync(0xffffffffu, bs, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (before(os, oi, bs, bi)) {
-          bs = os;
-          bi = oi;
+        const float os = __shfl_xor_sync(0xffffffffu, ws, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
+        if (before(os, oi, ws, wi)) {
+          ws = os;
+          wi = oi;
         }
       }
-      if (lane == r) {
-        my_s = bs;
-        my_i = bi;
+      if (wi < 0) break;  // warp-uniform: candidates exhausted
+      if (wi == bi) {     // indices are unique across splits: exactly one lane advances
+#pragma unroll
+        for (int o = 0; o < kMaxOwn; ++o)
+          if (o == bo) ++pos[o];
       }
-      last_s = bs;
-      last_i = bi;
-      first = false;
-      if (bi < 0) break;  // warp-uniform: candidates exhausted
+      if (lane == r) {
+        my_s = ws;
+        my_i = wi;
+      }
     }
   }
   // ---- stage 2: exact fp32 re-score of the KP survivors
@@ -555,6 +565,12 @@ static TcPlan make_plan(int Q, int G, int D, int k, bool rescore) {
   // gallery splits: (a) keep every SM busy when there are few query blocks, (b) keep the gallery range one wave of CTAs
   // streams within ~64 MB so that it stays L2-resident while all query blocks of the wave pass over it, (c) avoid a
   // ragged last wave.
+  // Every CTA pays a fixed cost before its pipeline is in steady state: barrier/TMEM set-up, the first TMA round trips
+  // and, above all, the warm-up of the per-row candidate lists (while a list is still filling almost every similarity
+  // of the first tile takes the insertion path).  Measured on B200: ~20 us per CTA; a 128 x 256 x D tile takes
+  // 2*128*256*D / (peak/148) ~ 5.9 us at D = 1024.  Expressed in tile units so that the model stays dimensionless.
+  const double tile_us = 2.0 * BM * BN * (double)D / 11.0e6;
+  const double cta_overhead_tiles = 20.0 / tile_us;
   int best = 1;
   double best_cost = 1e30;
   const int max_split = pl.n_tiles < 64 ? pl.n_tiles : 64;
@@ -564,10 +580,10 @@ static TcPlan make_plan(int Q, int G, int D, int k, bool rescore) {
     if (used != s) continue;
     const long long ctas = (long long)pl.m_blocks * s;
     const long long waves = (ctas + sms - 1) / sms;
-    double cost = (double)waves * tps;                                // time in tile units
+    double cost = (double)waves * (tps + cta_overhead_tiles);        // time in tile units
     const double range_mb = (double)tps * BN * D * 2 / (1024.0 * 1024.0);
     if (range_mb > 64.0 && pl.m_blocks > 1) cost *= 1.0 + 0.25 * (range_mb / 64.0 - 1.0) / 8.0;  // mild L2 penalty
-    cost *= 1.0 + 0.002 * s;                                          // merge / prologue overhead per split
+    cost *= 1.0 + 0.002 * s;                                          // merge overhead per split
     if (cost < best_cost) {
       best_cost = cost;
       best = s;
