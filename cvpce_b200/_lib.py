@@ -18,6 +18,16 @@ POOL_MAX_REGIONS = 32
 c_void_p, c_int, c_float, c_int64, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_int64, ctypes.c_size_t
 
 
+class FpnLevel(ctypes.Structure):
+    """struct cvpce_fpn_level"""
+    _fields_ = [("logits", c_void_p), ("regression", c_void_p), ("anchors", c_void_p), ("logits_stride", c_int64),
+                ("regression_stride", c_int64), ("anchors_stride", c_int64), ("n_anchors", ctypes.c_int32)]
+
+
+SELECT_MAX_LEVELS = 8
+SELECT_MAX_TOPK = 2048
+
+
 class FeatureMap(ctypes.Structure):
     """struct cvpce_feature_map"""
     _fields_ = [("data", c_void_p), ("C", ctypes.c_int32), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
@@ -32,6 +42,10 @@ SIGNATURES = {
     "cvpce_shutdown": (c_int, []),
     "cvpce_nms_batched": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cvpce_nms_segments": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_float, c_float, c_int, c_void_p, c_void_p,
+                                   c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cvpce_select_candidates": (c_int, [ctypes.POINTER(FpnLevel), c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
+                                        c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cvpce_crop_resize": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p]),
     "cvpce_region_pool_embed": (c_int, [ctypes.POINTER(FeatureMap), c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,

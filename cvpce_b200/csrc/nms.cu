@@ -45,7 +45,9 @@ __device__ __forceinline__ bool iou_exceeds(const float4 a, const float4 b, cons
 struct NmsParams {
   const float4* boxes;
   const float* scores;
-  const int32_t* seg_offsets;
+  const int32_t* seg_offsets;  // CSR form: segment b = [seg_offsets[b], seg_offsets[b+1])
+  const int32_t* seg_counts;   // strided form (seg_offsets == nullptr): segment b = [b*seg_stride, b*seg_stride + seg_counts[b])
+  int seg_stride;
   int max_n;      // capacity of the shared arrays
   int sort_cap;   // power of two >= max_n
   float iou_thr;
@@ -74,8 +76,8 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
   const int b = blockIdx.x;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
-  const int seg = p.seg_offsets[b];
-  const int n = p.seg_offsets[b + 1] - seg;
+  const int seg = p.seg_offsets ? p.seg_offsets[b] : b * p.seg_stride;
+  const int n = p.seg_offsets ? p.seg_offsets[b + 1] - seg : p.seg_counts[b];
   if (n > p.max_n || n < 0) {
     if (tid == 0) p.keep_counts[b] = -1;
     return;
@@ -226,14 +228,11 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
 
 }  // namespace cvpce
 
-extern "C" int cvpce_nms_batched(const float* boxes, const float* scores, const int32_t* seg_offsets, int n_images,
-                                 int max_n, float iou_threshold, float min_score, int max_keep, int64_t* keep,
-                                 int32_t* keep_counts, const float* box_scale, float* kept_boxes, float* kept_scores,
-                                 void* stream) {
-  using namespace cvpce;
-  CVPCE_REQUIRE(n_images >= 0 && max_n >= 0, CVPCE_ERR_INVALID_ARG, "nms: negative size (n_images=%d max_n=%d)", n_images, max_n);
-  if (n_images == 0) return CVPCE_OK;
-  CVPCE_REQUIRE(seg_offsets && keep_counts, CVPCE_ERR_INVALID_ARG, "nms: seg_offsets / keep_counts is null");
+namespace cvpce {
+
+static int launch_nms(NmsParams& p, const float* boxes, const float* scores, int n_images, int max_n, float iou_threshold,
+                      float min_score, int max_keep, int64_t* keep, int32_t* keep_counts, const float* box_scale,
+                      float* kept_boxes, float* kept_scores, void* stream) {
   CVPCE_REQUIRE(max_n <= CVPCE_NMS_MAX_N, CVPCE_ERR_UNSUPPORTED, "nms: max_n=%d exceeds CVPCE_NMS_MAX_N=%d", max_n, CVPCE_NMS_MAX_N);
   if (int rc = require_sm100()) return rc;
   if (max_n > 0) {
@@ -241,10 +240,8 @@ extern "C" int cvpce_nms_batched(const float* boxes, const float* scores, const 
     CVPCE_REQUIRE(aligned16(boxes) && (!kept_boxes || aligned16(kept_boxes)), CVPCE_ERR_INVALID_ARG,
                   "nms: boxes / kept_boxes must be 16-byte aligned");
   }
-  NmsParams p;
   p.boxes = reinterpret_cast<const float4*>(boxes);
   p.scores = scores;
-  p.seg_offsets = seg_offsets;
   p.max_n = max_n > 0 ? max_n : 1;
   int cap = 2;
   while (cap < p.max_n) cap <<= 1;
@@ -269,4 +266,40 @@ extern "C" int cvpce_nms_batched(const float* boxes, const float* scores, const 
   nms_batched_kernel<<<n_images, threads, smem, (cudaStream_t)stream>>>(p);
   CVPCE_LAUNCH_OK("nms_batched_kernel");
   return CVPCE_OK;
+}
+
+}  // namespace cvpce
+
+extern "C" int cvpce_nms_batched(const float* boxes, const float* scores, const int32_t* seg_offsets, int n_images,
+                                 int max_n, float iou_threshold, float min_score, int max_keep, int64_t* keep,
+                                 int32_t* keep_counts, const float* box_scale, float* kept_boxes, float* kept_scores,
+                                 void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(n_images >= 0 && max_n >= 0, CVPCE_ERR_INVALID_ARG, "nms: negative size (n_images=%d max_n=%d)", n_images, max_n);
+  if (n_images == 0) return CVPCE_OK;
+  CVPCE_REQUIRE(seg_offsets && keep_counts, CVPCE_ERR_INVALID_ARG, "nms: seg_offsets / keep_counts is null");
+  NmsParams p;
+  p.seg_offsets = seg_offsets;
+  p.seg_counts = nullptr;
+  p.seg_stride = 0;
+  return launch_nms(p, boxes, scores, n_images, max_n, iou_threshold, min_score, max_keep, keep, keep_counts, box_scale,
+                    kept_boxes, kept_scores, stream);
+}
+
+extern "C" int cvpce_nms_segments(const float* boxes, const float* scores, int seg_stride, const int32_t* seg_counts,
+                                  int n_images, float iou_threshold, float min_score, int max_keep, int64_t* keep,
+                                  int32_t* keep_counts, const float* box_scale, float* kept_boxes, float* kept_scores,
+                                  void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(n_images >= 0 && seg_stride >= 0, CVPCE_ERR_INVALID_ARG, "nms: negative size (n_images=%d seg_stride=%d)",
+                n_images, seg_stride);
+  if (n_images == 0) return CVPCE_OK;
+  CVPCE_REQUIRE(seg_counts && keep_counts, CVPCE_ERR_INVALID_ARG, "nms: seg_counts / keep_counts is null");
+  CVPCE_REQUIRE((long long)seg_stride * n_images < (1ll << 31), CVPCE_ERR_UNSUPPORTED, "nms: seg_stride * n_images overflows int32");
+  NmsParams p;
+  p.seg_offsets = nullptr;
+  p.seg_counts = seg_counts;
+  p.seg_stride = seg_stride;
+  return launch_nms(p, boxes, scores, n_images, seg_stride, iou_threshold, min_score, max_keep, keep, keep_counts, box_scale,
+                    kept_boxes, kept_scores, stream);
 }

@@ -69,6 +69,91 @@ def nms_batched(boxes, scores, seg_offsets, max_n, iou_threshold=0.5, min_score=
     return keep, counts, kept_boxes, kept_scores
 
 
+def nms_segments(boxes, scores, seg_stride, seg_counts, iou_threshold=0.5, min_score=None, max_keep=0, box_scale=None,
+                 want_boxes=False, want_scores=False):
+    """nms_batched over fixed-stride segments (image b = rows [b*seg_stride, b*seg_stride + seg_counts[b])): the layout
+    select_candidates writes.  Same returns as nms_batched; no host synchronisation."""
+    _need_cuda("nms_segments", boxes, scores, seg_counts, box_scale)
+    if boxes.dtype != torch.float32 or scores.dtype != torch.float32 or not boxes.is_contiguous() or not scores.is_contiguous():
+        raise RuntimeError("nms_segments: boxes / scores must be contiguous float32")
+    seg_counts = seg_counts.contiguous().to(torch.int32)
+    n_images = seg_counts.numel()
+    total = boxes.shape[0]
+    if total < n_images * seg_stride:
+        raise RuntimeError("nms_segments: boxes has %d rows, needs n_images*seg_stride = %d" % (total, n_images * seg_stride))
+    keep = torch.empty(total, dtype=torch.int64, device=boxes.device)
+    counts = torch.empty(n_images, dtype=torch.int32, device=boxes.device)
+    kept_boxes = torch.empty((total, 4), dtype=torch.float32, device=boxes.device) if want_boxes else None
+    kept_scores = torch.empty(total, dtype=torch.float32, device=boxes.device) if want_scores else None
+    if box_scale is not None:
+        box_scale = box_scale.contiguous().float()
+    rc = _lib.load().cvpce_nms_segments(_ptr(boxes), _ptr(scores), int(seg_stride), _ptr(seg_counts), n_images,
+                                        threshold_as_cpu_op(float(iou_threshold)),
+                                        float("-inf") if min_score is None else float(min_score), int(max_keep),
+                                        _ptr(keep), _ptr(counts), _ptr(box_scale), _ptr(kept_boxes), _ptr(kept_scores), _stream())
+    _lib.check(rc, "cvpce_nms_segments")
+    return keep, counts, kept_boxes, kept_scores
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# pre-NMS candidate selection  (tv:models/detection/retinanet.py:527-557, tv:models/detection/_utils.py:183-224)
+# ---------------------------------------------------------------------------------------------------------------------
+BBOX_XFORM_CLIP = math.log(1000.0 / 16)
+
+
+def select_candidates(cls_logits, bbox_regression, anchors, image_sizes, score_thresh=0.05, topk=1000, weights=None,
+                      bbox_xform_clip=BBOX_XFORM_CLIP, want_labels=True):
+    """Sigmoid, threshold, per-level top-k, box decode, clip and concatenation over FPN levels for a whole batch, one launch.
+
+    cls_logits: list over levels of f32 [B,A_l,C] (views of the concatenated head output are fine: only the last two dims
+    must be contiguous); bbox_regression: list of f32 [B,A_l,4]; anchors: list of f32 [A_l,4] (one set shared by the
+    batch) or of [B,A_l,4]; image_sizes: i32 [B,2] device tensor or a list of (h, w).
+    Returns (boxes f32 [B*L*topk,4], scores f32 [B*L*topk], labels i64|None, seg_counts i32 [B], level_counts i32 [B,L],
+    seg_stride): image b's candidates are rows [b*seg_stride, b*seg_stride + seg_counts[b])."""
+    n_levels = len(cls_logits)
+    if n_levels == 0 or n_levels != len(bbox_regression) or n_levels != len(anchors):
+        raise RuntimeError("select_candidates: need the same, non-zero number of levels in logits / regression / anchors")
+    _need_cuda("select_candidates", *cls_logits, *bbox_regression, *anchors)
+    device = cls_logits[0].device
+    B, _, C = cls_logits[0].shape
+    if not isinstance(image_sizes, torch.Tensor):
+        image_sizes = torch.tensor([[int(h), int(w)] for h, w in image_sizes], dtype=torch.int32).to(device, non_blocking=True)
+    image_sizes = image_sizes.contiguous().to(torch.int32)
+    _need_cuda("select_candidates", image_sizes)
+    levels = (_lib.FpnLevel * n_levels)()
+    hold = []
+    for l, (lg, rg, an) in enumerate(zip(cls_logits, bbox_regression, anchors)):
+        if lg.dtype != torch.float32 or rg.dtype != torch.float32:
+            raise RuntimeError("select_candidates: head outputs must be float32")
+        A = lg.shape[1]
+        if lg.shape != (B, A, C) or rg.shape != (B, A, 4) or an.shape[-2:] != (A, 4):
+            raise RuntimeError("select_candidates: level %d shapes %s / %s / %s do not agree" % (l, tuple(lg.shape), tuple(rg.shape), tuple(an.shape)))
+        if A > 0 and (lg.stride(2) != 1 or (lg.stride(1) != C and A > 1)):
+            lg = lg.contiguous()
+        if A > 0 and (rg.stride(2) != 1 or (rg.stride(1) != 4 and A > 1) or rg.data_ptr() % 16 or (rg.stride(0) % 4 and B > 1)):
+            rg = rg.contiguous()
+        an = an.float()
+        if not an.is_contiguous() or an.data_ptr() % 16:
+            an = an.contiguous().clone()
+        hold += [lg, rg, an]
+        levels[l] = _lib.FpnLevel(lg.data_ptr(), rg.data_ptr(), an.data_ptr(), lg.stride(0) if B > 1 else 0,
+                                  rg.stride(0) if B > 1 else 0, an.stride(0) if an.dim() == 3 and B > 1 else 0, A)
+    seg_stride = n_levels * int(topk)
+    boxes = torch.empty((B * seg_stride, 4), dtype=torch.float32, device=device)
+    scores = torch.empty(B * seg_stride, dtype=torch.float32, device=device)
+    labels = torch.empty(B * seg_stride, dtype=torch.int64, device=device) if want_labels else None
+    seg_counts = torch.empty(B, dtype=torch.int32, device=device)
+    level_counts = torch.empty((B, n_levels), dtype=torch.int32, device=device)
+    w = None if weights is None else (ctypes.c_float * 4)(*[float(v) for v in weights])
+    rc = _lib.load().cvpce_select_candidates(levels, n_levels, B, C, float(score_thresh), int(topk), _ptr(image_sizes),
+                                             ctypes.cast(w, ctypes.c_void_p) if w is not None else None,
+                                             float(bbox_xform_clip), _ptr(boxes), _ptr(scores), _ptr(labels),
+                                             _ptr(seg_counts), _ptr(level_counts), _stream())
+    _lib.check(rc, "cvpce_select_candidates")
+    del hold
+    return boxes, scores, labels, seg_counts, level_counts, seg_stride
+
+
 def nms(boxes, scores, iou_threshold):
     """Drop-in for torchvision.ops.nms(boxes, scores, iou_threshold) -> int64[K] (one D2H read of the count)."""
     _need_cuda("nms", boxes, scores)

@@ -8,7 +8,7 @@ import sys
 
 import torch
 
-from . import classification, datautils, ops, production
+from . import classification, datautils, detection, ops, production
 
 _saved = []
 
@@ -67,6 +67,16 @@ def apply(ref=None):
     _swap(retinanet.box_ops, "batched_nms", _batched_nms)                       # tv:retinanet.py:560
     if ref is None:
         return
+    gln = getattr(getattr(ref.models, "proposals", None), "GaussianLayerNetwork", None)
+    if gln is not None:  # single-class detector: sigmoid/top-k/decode/clip + NMS in two launches (tv:retinanet.py:508-571)
+        def _gln_postprocess(self, head_outputs, anchors, image_shapes):
+            if not head_outputs["cls_logits"][0].is_cuda:
+                raise RuntimeError("cvpce_b200.patch: postprocess_detections called with CPU tensors; no CPU fallback")
+            if head_outputs["cls_logits"][0].shape[-1] != 1:  # multi-class heads keep torchvision's loop (+ patched NMS)
+                return retinanet.RetinaNet.postprocess_detections(self, head_outputs, anchors, image_shapes)
+            return detection.retinanet_postprocess_detections(self, head_outputs, anchors, image_shapes)
+        _saved.append((gln, "postprocess_detections", None))
+        gln.postprocess_detections = _gln_postprocess                            # proposals.py:161 (inherited method)
     rc, rp, rd = ref.models.classification, ref.production, ref.datautils
     _swap(rc, "nearest_neighbors", classification.nearest_neighbors)            # classification.py:90
     _swap(rp, "nearest_neighbors", classification.nearest_neighbors)            # production.py:6 (from-import alias)
@@ -86,4 +96,7 @@ def apply(ref=None):
 def revert():
     while _saved:
         obj, name, old = _saved.pop()
-        setattr(obj, name, old)
+        if old is None:
+            delattr(obj, name)  # the attribute was inherited before the patch
+        else:
+            setattr(obj, name, old)

@@ -183,3 +183,61 @@ class GalleryDataset:
 
     def __getitem__(self, i):
         return self.images[i], self.images[i], [], "g%d" % i
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# detector-head outputs for the pre-NMS candidate selection (tv:retinanet.py:508-571)
+# ---------------------------------------------------------------------------------------------------------------------
+FPN_STRIDES = (8, 16, 32, 64, 128)       # P3..P7 of the GLN / RetinaNet FPN
+FPN_SIZES = (32, 64, 128, 256, 512)      # tv:retinanet.py _default_anchorgen
+
+
+def fpn_anchors(H, W):
+    """RetinaNet-style anchors per FPN level: 9 per cell (3 scales x 3 aspect ratios), f32 [A_l,4] xyxy, cell-major with
+    the 9 anchors innermost (the layout the head's permute/reshape produces)."""
+    out = []
+    for stride, size in zip(FPN_STRIDES, FPN_SIZES):
+        fh, fw = -(-H // stride), -(-W // stride)
+        scales = np.array([size * 2 ** (i / 3) for i in range(3)], dtype=np.float64)
+        ratios = np.array([0.5, 1.0, 2.0])
+        hr = np.sqrt(ratios)
+        wr = 1.0 / hr
+        ws = (wr[:, None] * scales[None, :]).reshape(-1)
+        hs = (hr[:, None] * scales[None, :]).reshape(-1)
+        base = np.round(np.stack([-ws, -hs, ws, hs], axis=1) / 2)
+        sy, sx = np.meshgrid(np.arange(fh) * stride, np.arange(fw) * stride, indexing="ij")
+        shifts = np.stack([sx.reshape(-1), sy.reshape(-1), sx.reshape(-1), sy.reshape(-1)], axis=1)
+        out.append((shifts[:, None, :] + base[None, :, :]).reshape(-1, 4).astype(np.float32))
+    return out
+
+
+# name -> (seed, image sizes [(h,w)], padded batch size (H,W), num_classes, logit mean, logit std, quantise step, topk)
+HEAD_CASES = {
+    "dense_2img": (11, [(200, 264), (184, 248)], (200, 264), 1, -2.0, 2.0, 0.0, 1000),
+    "sparse": (12, [(200, 264)], (200, 264), 1, -6.5, 1.5, 0.0, 1000),
+    "multiclass": (13, [(136, 200)], (136, 200), 3, -2.5, 2.0, 0.0, 300),
+    "ties": (14, [(200, 264)], (200, 264), 1, -1.0, 1.5, 1.0, 1000),        # 1.0-quantised logits: large tie groups
+    "fullsize": (15, [(800, 1066)], (800, 1066), 1, -4.0, 1.5, 0.0, 1000),  # the GLN transform's 800 x <=1333 frame
+}
+
+
+def head_case(name):
+    """Seeded head outputs of one case: (logits [f32 [B,A_l,C]], regression [f32 [B,A_l,4]], anchors [f32 [A_l,4]],
+    image_sizes, num_classes, topk)."""
+    seed, sizes, (H, W), C, mu, sd, q, topk = HEAD_CASES[name]
+    rs = np.random.RandomState(seed)
+    anchors = fpn_anchors(H, W)
+    B = len(sizes)
+    logits, regression = [], []
+    for a in anchors:
+        A = a.shape[0]
+        lg = (mu + sd * rs.standard_normal((B, A, C))).astype(np.float32)
+        if q > 0:
+            lg = (np.round(lg / q) * q).astype(np.float32)
+        rg = (0.4 * rs.standard_normal((B, A, 4))).astype(np.float32)
+        # a few extreme deltas: exercise the bbox_xform_clip clamp and the clip to the image
+        m = rs.random_sample((B, A)) < 0.01
+        rg[m] *= 12.0
+        logits.append(lg)
+        regression.append(rg)
+    return logits, regression, anchors, sizes, C, topk

@@ -80,6 +80,53 @@ CVPCE_API int cvpce_nms_batched(const float* boxes, const float* scores, const i
                       int64_t* keep, int32_t* keep_counts,
                       const float* box_scale, float* kept_boxes, float* kept_scores, void* stream);
 
+/* Same kernel over fixed-stride segments: image b owns rows [b*seg_stride, b*seg_stride + seg_counts[b]) of boxes / scores
+ * (seg_counts i32 [n_images], device; seg_stride <= CVPCE_NMS_MAX_N) -- the layout cvpce_select_candidates writes, so the
+ * detector post-processing (f1 -> a1 -> a2) is two launches with no host synchronisation in between.  keep / kept_boxes /
+ * kept_scores use the same row positions. */
+CVPCE_API int cvpce_nms_segments(const float* boxes, const float* scores, int seg_stride, const int32_t* seg_counts, int n_images,
+                       float iou_threshold, float min_score, int max_keep,
+                       int64_t* keep, int32_t* keep_counts,
+                       const float* box_scale, float* kept_boxes, float* kept_scores, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * f1  Pre-NMS candidate selection of the RetinaNet / GLN head (the step that feeds a1).
+ * Replaces: the per-image, per-FPN-level loop of tv:models/detection/retinanet.py:527-557
+ *           (RetinaNet.postprocess_detections, inherited unchanged by cvpce/models/proposals.py:161 GaussianLayerNetwork):
+ *           torch.sigmoid(logits).flatten() -> `> score_thresh` -> topk(min(topk_candidates, n)) -> anchor / label index
+ *           -> BoxCoder.decode_single (tv:models/detection/_utils.py:183-224) -> clip_boxes_to_image -> torch.cat over
+ *           levels; ~25 small launches and one host sync (torch.where) per level per image in the reference.
+ *
+ * levels [host] n_levels (<= CVPCE_SELECT_MAX_LEVELS) descriptors of the head outputs split per FPN level:
+ *   logits     f32 [n_images, n_anchors, num_classes], image stride logits_stride (elements), inner dims contiguous;
+ *   regression f32 [n_images, n_anchors, 4], image stride regression_stride, rows 16-byte aligned;
+ *   anchors    f32 [n_anchors, 4] xyxy, image stride anchors_stride (0: one anchor set shared by all images).
+ * image_sizes i32 [n_images,2] (device) = (height, width) of the resized images boxes are clipped to.
+ * weights [host] nullable f32[4] BoxCoder weights (RetinaNet: 1,1,1,1); bbox_xform_clip = log(1000/16) in torchvision.
+ * Candidates of a level are ordered (score descending, flat (anchor, class) index ascending) -- torch.topk leaves the
+ * order of equal scores unspecified -- and levels are concatenated in order.  Scores are sigmoid values computed with a
+ * fixed IEEE fp32 operation sequence (reproducible on the host; within a few ulp of ATen's), boxes follow
+ * decode_single's fp32 operation order with the same exp.
+ *
+ * Outputs: image b's candidates are rows [b*seg_stride, b*seg_stride + seg_counts[b]) with seg_stride = n_levels*topk:
+ *   boxes f32 [n_images*seg_stride, 4] (16-byte aligned), scores f32 [n_images*seg_stride],
+ *   labels (nullable) i64 [n_images*seg_stride], seg_counts i32 [n_images],
+ *   level_counts (nullable) i32 [n_images, n_levels].  1 <= topk <= CVPCE_SELECT_MAX_TOPK.
+ */
+typedef struct cvpce_fpn_level {
+  const float* logits;
+  const float* regression;
+  const float* anchors;
+  int64_t logits_stride, regression_stride, anchors_stride;
+  int32_t n_anchors;
+} cvpce_fpn_level;
+#define CVPCE_SELECT_MAX_LEVELS 8
+#define CVPCE_SELECT_MAX_TOPK 2048
+CVPCE_API int cvpce_select_candidates(const cvpce_fpn_level* levels, int n_levels, int n_images, int num_classes,
+                            float score_thresh, int topk, const int32_t* image_sizes, const float* weights,
+                            float bbox_xform_clip, float* boxes, float* scores, int64_t* labels,
+                            int32_t* seg_counts, int32_t* level_counts, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * a3 + a4 (+ a5, a6)  Batched ROI crop -> pad-to-square -> (antialiased) bilinear resize.
  * Replaces: the per-box python loop  image[:, y1:y2, x1:x2]  over boxes.to(long) at cvpce/production.py:20

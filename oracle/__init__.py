@@ -157,3 +157,58 @@ def sim_topk_f32(queries, gallery, k=1):
 def nearest_neighbors(anchors, queries, k=1):
     """Same argument order and return convention as classification.nearest_neighbors: int64[Q,k]."""
     return sim_topk(queries, anchors, k=k, normalize=True)[1]
+
+
+BBOX_XFORM_CLIP = float(np.log(1000.0 / 16))  # tv:models/detection/_utils.py BoxCoder default
+
+
+def det_sigmoid(x):
+    L = lib()
+    L.oracle_det_sigmoid.restype = ctypes.c_float
+    return np.array([L.oracle_det_sigmoid(ctypes.c_float(float(v))) for v in np.asarray(x, dtype=np.float32).reshape(-1)],
+                    dtype=np.float32)
+
+
+def select_candidates(logits, regression, anchors, image_sizes, score_thresh=0.05, topk=1000, weights=None):
+    """Pre-NMS candidate selection of RetinaNet.postprocess_detections (tv:retinanet.py:527-557), oracle.c:
+    oracle_select_level per (image, level).
+    logits: list over levels of f32[B,A_l,C]; regression: list of f32[B,A_l,4]; anchors: list of f32[A_l,4];
+    image_sizes: [(h,w)]*B.  Returns per image (boxes f32[N,4], scores f32[N], labels i64[N], level_counts i64[L])."""
+    L = lib()
+    L.oracle_select_level.restype = ctypes.c_int64
+    B = logits[0].shape[0]
+    C = logits[0].shape[2]
+    w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+    out = []
+    for b in range(B):
+        bs, ss, ls, cnt = [], [], [], []
+        for lg, rg, an in zip(logits, regression, anchors):
+            A = lg.shape[1]
+            lgb = np.ascontiguousarray(lg[b], dtype=np.float32)
+            rgb = np.ascontiguousarray(rg[b], dtype=np.float32)
+            anb = np.ascontiguousarray(an, dtype=np.float32)
+            cap = max(1, min(int(topk), A * C))
+            ob = np.empty((cap, 4), dtype=np.float32)
+            os_ = np.empty(cap, dtype=np.float32)
+            ol = np.empty(cap, dtype=np.int64)
+            k = L.oracle_select_level(_p(lgb), _p(rgb), _p(anb), ctypes.c_int64(A), ctypes.c_int64(C),
+                                      ctypes.c_float(float(score_thresh)), ctypes.c_int64(int(topk)),
+                                      ctypes.c_int64(int(image_sizes[b][0])), ctypes.c_int64(int(image_sizes[b][1])),
+                                      _p(w) if w is not None else None, ctypes.c_float(BBOX_XFORM_CLIP), _p(ob), _p(os_), _p(ol))
+            bs.append(ob[:k])
+            ss.append(os_[:k])
+            ls.append(ol[:k])
+            cnt.append(k)
+        out.append((np.concatenate(bs), np.concatenate(ss), np.concatenate(ls), np.array(cnt, dtype=np.int64)))
+    return out
+
+
+def postprocess_detections(logits, regression, anchors, image_sizes, score_thresh=0.05, topk=1000, nms_thresh=0.5,
+                           detections_per_img=300):
+    """RetinaNet.postprocess_detections for a single-class head (tv:retinanet.py:508-571): selection, batched_nms,
+    [:detections_per_img].  Returns per image (boxes, scores, labels)."""
+    res = []
+    for boxes, scores, labels, _ in select_candidates(logits, regression, anchors, image_sizes, score_thresh, topk):
+        keep = nms(boxes, scores, nms_thresh)[:detections_per_img]
+        res.append((boxes[keep], scores[keep], labels[keep]))
+    return res

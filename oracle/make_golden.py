@@ -125,6 +125,50 @@ def golden_classify(ref):
     print("classify:", {k: v.shape for k, v in out.items()}, out["labels"].tolist())
 
 
+def golden_head(ref):
+    """RetinaNet.postprocess_detections as inherited by the reference's GaussianLayerNetwork (proposals.py:161-182;
+    tv:retinanet.py:508-571) on seeded head outputs.  The arguments of the batched_nms call inside it are recorded too:
+    they are the pre-NMS candidates (boxes, scores, labels after sigmoid / threshold / top-k / decode / clip / cat)."""
+    from torchvision.models.detection import retinanet
+    import cvpce.models.proposals as proposals
+    out = {}
+    for name, (seed, sizes, hw, C, mu, sd, q, topk) in synth.HEAD_CASES.items():
+        logits, regression, anchors, sizes, C, topk = synth.head_case(name)
+        model = proposals.gln(num_classes=C, pretrained_backbone=False).eval()
+        model.topk_candidates = topk
+        B = len(sizes)
+        head = {"cls_logits": [torch.from_numpy(l) for l in logits], "bbox_regression": [torch.from_numpy(r) for r in regression]}
+        anc = [[torch.from_numpy(a) for a in anchors] for _ in range(B)]
+        captured = []
+        real = retinanet.box_ops.batched_nms
+
+        def spy(boxes, scores, idxs, thr):
+            captured.append((boxes.clone(), scores.clone(), idxs.clone()))
+            return real(boxes, scores, idxs, thr)
+
+        retinanet.box_ops.batched_nms = spy
+        try:
+            with torch.no_grad():
+                dets = model.postprocess_detections(head, anc, [tuple(s) for s in sizes])
+        finally:
+            retinanet.box_ops.batched_nms = real
+        for b in range(B):
+            cb, cs, cl = captured[b]
+            pre = "%s/%d/" % (name, b)
+            if name == "fullsize":   # keep the fixture small: candidates as count + per-level sums only
+                out[pre + "cand_count"] = np.array([len(cs)], dtype=np.int64)
+                out[pre + "cand_score_sum"] = np.array([cs.double().sum().item()])
+            else:
+                out[pre + "cand_boxes"] = cb.numpy()
+                out[pre + "cand_scores"] = cs.numpy()
+                out[pre + "cand_labels"] = cl.numpy()
+            out[pre + "det_boxes"] = dets[b]["boxes"].numpy()
+            out[pre + "det_scores"] = dets[b]["scores"].numpy()
+            out[pre + "det_labels"] = dets[b]["labels"].numpy()
+    np.savez_compressed(os.path.join(OUT, "head.npz"), **out)
+    print("head:", {k: v.shape for k, v in out.items() if k.endswith(("cand_scores", "det_scores", "cand_count"))})
+
+
 def main():
     if not shim.available():
         sys.exit("reference tree not present; golden vectors can only be regenerated in the authoring container")
@@ -137,6 +181,7 @@ def main():
     golden_mac(ref)
     golden_nn(ref)
     golden_classify(ref)
+    golden_head(ref)
     with open(os.path.join(OUT, "VERSIONS.txt"), "w") as f:
         f.write("torch %s\ntorchvision %s\nnumpy %s\nreference commit 7509e7d (laitalaj/cvpce)\n" %
                 (torch.__version__, torchvision.__version__, np.__version__))

@@ -355,3 +355,90 @@ API void oracle_sim_topk_f32(const float* q, const float* g, int64_t Q, int64_t 
     }
   }
 }
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Pre-NMS candidate selection.  tv:models/detection/retinanet.py:527-557, one (image, level):
+ *   scores = sigmoid(logits).flatten(); keep = scores > score_thresh; topk(min(topk_candidates, #keep));
+ *   anchor = idx // num_classes, label = idx % num_classes; BoxCoder.decode_single (tv:models/detection/_utils.py:183-224);
+ *   clip_boxes_to_image (tv:ops/boxes.py).
+ * exp / sigmoid: ATen's vectorised kernels (Sleef) are third-party compiled code; their results are reproduced to a few
+ * ulp by oracle_det_expf -- a fixed sequence of IEEE fp32 operations (Cephes expf polynomial) that the CUDA kernel
+ * repeats bit for bit.  Equal scores are ordered by ascending flat index (torch.topk: unspecified).
+ * Returns the number of candidates written (score-descending).
+ * --------------------------------------------------------------------------------------------------------------- */
+static float bits_to_float(uint32_t u) {
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+API float oracle_det_expf(float x) {
+  if (x != x) return x;
+  if (x > 88.7228394f) return INFINITY;
+  if (x < -103.972084f) return 0.f;
+  const float n = rintf(x * 1.44269502f);
+  float r = fmaf(n, -0.693359375f, x);
+  r = fmaf(n, 2.12194440e-4f, r);
+  float p = 1.9875691500e-4f;
+  p = fmaf(p, r, 1.3981999507e-3f);
+  p = fmaf(p, r, 8.3334519073e-3f);
+  p = fmaf(p, r, 4.1665795894e-2f);
+  p = fmaf(p, r, 1.6666665459e-1f);
+  p = fmaf(p, r, 5.0000001201e-1f);
+  float y = fmaf(p, r * r, r);
+  y = y + 1.f;
+  const int ni = (int)n;
+  const int n1 = ni / 2, n2 = ni - n1;
+  y = y * bits_to_float((uint32_t)(127 + n1) << 23);
+  return y * bits_to_float((uint32_t)(127 + n2) << 23);
+}
+
+API float oracle_det_sigmoid(float x) { return 1.f / (1.f + oracle_det_expf(-x)); }
+
+static float clampf(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); } /* NaN propagates */
+
+API int64_t oracle_select_level(const float* logits, const float* regression, const float* anchors, int64_t n_anchors,
+                                int64_t num_classes, float score_thresh, int64_t topk, int64_t img_h, int64_t img_w,
+                                const float* weights, float xform_clip, float* out_boxes, float* out_scores,
+                                int64_t* out_labels) {
+  const int64_t n = n_anchors * num_classes;
+  if (n <= 0 || topk <= 0) return 0;
+  sortkey* cand = (sortkey*)malloc(sizeof(sortkey) * (size_t)n);
+  int64_t m = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const float s = oracle_det_sigmoid(logits[i]);
+    if (s > score_thresh) { /* retinanet.py:533-536 */
+      cand[m].s = s;
+      cand[m].i = (int32_t)i;
+      ++m;
+    }
+  }
+  qsort(cand, (size_t)m, sizeof(sortkey), cmp_desc_stable);
+  const int64_t k = m < topk ? m : topk; /* det_utils._topk_min, retinanet.py:539-541 */
+  const float wx = weights ? weights[0] : 1.f, wy = weights ? weights[1] : 1.f;
+  const float ww = weights ? weights[2] : 1.f, wh = weights ? weights[3] : 1.f;
+  for (int64_t r = 0; r < k; ++r) {
+    const int64_t a = cand[r].i / num_classes; /* retinanet.py:543-544 */
+    const float* rc = regression + 4 * a;
+    const float* an = anchors + 4 * a;
+    const float w = an[2] - an[0], h = an[3] - an[1];       /* _utils.py:195-198 */
+    const float hw0 = 0.5f * w, hh0 = 0.5f * h;
+    const float cx = an[0] + hw0, cy = an[1] + hh0;
+    const float dx = rc[0] / wx, dy = rc[1] / wy;            /* _utils.py:200-204 */
+    float dw = rc[2] / ww, dh = rc[3] / wh;
+    dw = dw > xform_clip ? xform_clip : dw;                  /* _utils.py:207-208 */
+    dh = dh > xform_clip ? xform_clip : dh;
+    const float mx = dx * w, my = dy * h;
+    const float pcx = mx + cx, pcy = my + cy;                /* _utils.py:210-211 */
+    const float pw = oracle_det_expf(dw) * w, ph = oracle_det_expf(dh) * h; /* _utils.py:212-213 */
+    const float c2w = 0.5f * pw, c2h = 0.5f * ph;            /* _utils.py:216-217 */
+    out_boxes[4 * r + 0] = clampf(pcx - c2w, 0.f, (float)img_w); /* _utils.py:219-222, boxes.py clip_boxes_to_image */
+    out_boxes[4 * r + 1] = clampf(pcy - c2h, 0.f, (float)img_h);
+    out_boxes[4 * r + 2] = clampf(pcx + c2w, 0.f, (float)img_w);
+    out_boxes[4 * r + 3] = clampf(pcy + c2h, 0.f, (float)img_h);
+    out_scores[r] = cand[r].s;
+    out_labels[r] = cand[r].i % num_classes;
+  }
+  free(cand);
+  return k;
+}

@@ -16,7 +16,7 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def golden():
-    return {name: np.load(os.path.join(GOLDEN, name + ".npz")) for name in ("nms", "crops", "mac", "nn", "classify")}
+    return {name: np.load(os.path.join(GOLDEN, name + ".npz")) for name in ("nms", "crops", "mac", "nn", "classify", "head")}
 
 
 @pytest.fixture(scope="session")
@@ -48,3 +48,25 @@ def topk_check(q, g, got_idx, oracle_sim, oracle_idx, tol=2e-6):
     clear = (gap_prev > 4 * tol) & (gap_next > 4 * tol)
     assert np.array_equal(got_idx[clear], oracle_idx[clear]), "index mismatch at clearly separated ranks"
     return float((got_idx == oracle_idx).mean())
+
+
+def rows_check(got_boxes, got_scores, ref_boxes, ref_scores, score_rtol=1e-6, box_atol=2e-3, window=3):
+    """Near-tie-aware comparison of score-descending detection rows against torchvision's: same count, scores equal in
+    order within `score_rtol` (ATen's vectorised sigmoid/exp and the fixed-sequence ones differ by a few ulp), and every
+    row's box equal within `box_atol` px to the reference row at the same position or -- where neighbouring scores are
+    within `score_rtol` of each other, i.e. their order is decided by the last ulp -- at a position <= `window` away."""
+    got_boxes, ref_boxes = np.asarray(got_boxes, dtype=np.float64), np.asarray(ref_boxes, dtype=np.float64)
+    got_scores, ref_scores = np.asarray(got_scores, dtype=np.float64), np.asarray(ref_scores, dtype=np.float64)
+    assert got_scores.shape == ref_scores.shape, (got_scores.shape, ref_scores.shape)
+    np.testing.assert_allclose(got_scores, ref_scores, rtol=score_rtol, atol=0)
+    n = len(ref_scores)
+    bad = np.nonzero(np.abs(got_boxes - ref_boxes).max(axis=1) > box_atol)[0] if n else []
+    for i in bad:
+        ok = False
+        for j in range(max(0, i - window), min(n, i + window + 1)):
+            if abs(ref_scores[j] - got_scores[i]) <= 2 * score_rtol * abs(ref_scores[j]) and \
+                    np.abs(got_boxes[i] - ref_boxes[j]).max() <= box_atol:
+                ok = True
+                break
+        assert ok, "row %d differs from the reference beyond a near-tie swap: %s vs %s" % (i, got_boxes[i], ref_boxes[i])
+    return len(bad)

@@ -409,3 +409,89 @@ def test_classifier_mirror_matches_reference_labels(ops, golden):
     labels = np.array([[int(a[1:]) for a in row] for row in res])
     assert np.array_equal(labels, golden["classify"]["labels"])
     assert clf.classify(torch.empty((0, 3, 64, 64))) == []
+
+
+# ------------------------------------------------------------------------------ f1: pre-NMS candidate selection (+ a1, a2)
+def _head_to_device(name):
+    logits, regression, anchors, sizes, C, topk = synth.head_case(name)
+    # like torchvision: one concatenated head output split into per-level VIEWS (tv:retinanet.py:640-648)
+    lg_all = dev(np.concatenate(logits, axis=1))
+    rg_all = dev(np.concatenate(regression, axis=1))
+    n_per = [a.shape[0] for a in anchors]
+    return (list(lg_all.split(n_per, dim=1)), list(rg_all.split(n_per, dim=1)), [dev(a) for a in anchors], sizes, C, topk,
+            (logits, regression, anchors))
+
+
+@pytest.mark.parametrize("name", list(synth.HEAD_CASES))
+def test_select_candidates_bit_exact_vs_oracle(ops, name):
+    lg, rg, an, sizes, C, topk, host = _head_to_device(name)
+    boxes, scores, labels, seg_counts, level_counts, stride = ops.select_candidates(lg, rg, an, sizes, 0.05, topk)
+    want = oracle.select_candidates(*host, sizes, 0.05, topk)
+    boxes, scores, labels = boxes.cpu().numpy(), scores.cpu().numpy(), labels.cpu().numpy()
+    seg_counts, level_counts = seg_counts.cpu().numpy(), level_counts.cpu().numpy()
+    assert stride == len(lg) * topk
+    for b, (wb, ws, wl, wc) in enumerate(want):
+        n = int(seg_counts[b])
+        assert n == len(ws), (name, b)
+        assert np.array_equal(level_counts[b], wc), (name, b)
+        sl = slice(b * stride, b * stride + n)
+        assert np.array_equal(scores[sl].view(np.uint32), ws.view(np.uint32)), (name, b)   # bit-exact scores
+        assert np.array_equal(labels[sl], wl), (name, b)
+        assert np.array_equal(boxes[sl].view(np.uint32), wb.view(np.uint32)), (name, b)     # bit-exact decoded boxes
+
+
+@pytest.mark.parametrize("name", ["dense_2img", "sparse", "fullsize"])
+def test_postprocess_detections_matches_reference_gln(ops, golden, name):
+    from cvpce_b200 import detection
+    from conftest import rows_check
+    lg, rg, an, sizes, C, topk, host = _head_to_device(name)
+    dets = detection.postprocess_detections({"cls_logits": lg, "bbox_regression": rg}, [an] * len(sizes), sizes,
+                                            score_thresh=0.05, topk_candidates=topk, nms_thresh=0.5, detections_per_img=1000)
+    want = oracle.postprocess_detections(*host, sizes, 0.05, topk, 0.5, 1000)
+    for b, d in enumerate(dets):
+        pre = "%s/%d/" % (name, b)
+        assert np.array_equal(d["boxes"].cpu().numpy(), want[b][0])       # bit-exact vs the oracle
+        assert np.array_equal(d["scores"].cpu().numpy(), want[b][1])
+        rows_check(d["boxes"].cpu().numpy(), d["scores"].cpu().numpy(), golden["head"][pre + "det_boxes"],
+                   golden["head"][pre + "det_scores"])                     # and the real GLN post-processing within ulps
+        assert np.array_equal(d["labels"].cpu().numpy(), golden["head"][pre + "det_labels"])
+
+
+def test_select_candidates_edge_cases(ops):
+    lg, rg, an, sizes, C, topk, host = _head_to_device("sparse")
+    # nothing passes / NaN logits / topk = 1 / constant logits (one giant tie group: the lowest flat indices win)
+    _, _, _, cnt, _, _ = ops.select_candidates(lg, rg, an, sizes, 0.999999, topk)
+    assert int(cnt.sum()) == 0
+    nan_lg = [torch.full_like(l, float("nan")) for l in lg]
+    _, _, _, cnt, _, _ = ops.select_candidates(nan_lg, rg, an, sizes, 0.05, topk)
+    assert int(cnt.sum()) == 0
+    _, s1, _, cnt, lc, st = ops.select_candidates(lg, rg, an, sizes, 0.05, 1)
+    want = oracle.select_candidates(*host, sizes, 0.05, 1)[0]
+    assert np.array_equal(lc.cpu().numpy()[0], want[3]) and np.array_equal(s1[: int(cnt[0])].cpu().numpy(), want[1])
+    const_lg = [torch.full_like(l, 0.25) for l in lg]
+    b, s, l, cnt, lc, st = ops.select_candidates(const_lg, rg, an, sizes, 0.05, topk)
+    host_const = ([np.full_like(x, 0.25) for x in host[0]], host[1], host[2])
+    want = oracle.select_candidates(*host_const, sizes, 0.05, topk)[0]
+    n = int(cnt[0])
+    assert n == len(want[1]) and np.array_equal(b[:n].cpu().numpy(), want[0])
+    # negative / zero threshold: every finite logit passes
+    _, s0, _, cnt0, _, _ = ops.select_candidates(lg, rg, an, sizes, 0.0, 50)
+    want = oracle.select_candidates(*host, sizes, 0.0, 50)[0]
+    assert np.array_equal(s0[: int(cnt0[0])].cpu().numpy(), want[1])
+    with pytest.raises(RuntimeError):
+        ops.select_candidates(lg, rg, an, sizes, 0.05, 4096)     # topk above CVPCE_SELECT_MAX_TOPK
+
+
+def test_nms_segments_equals_csr_form(ops):
+    b, s, thr, per_img = synth.nms_cases()["random5000"]
+    n = len(s)
+    stride = n + 37
+    boxes = np.zeros((2 * stride, 4), np.float32)
+    scores = np.zeros(2 * stride, np.float32)
+    boxes[:n], scores[:n] = b, s
+    m = n // 3
+    boxes[stride:stride + m], scores[stride:stride + m] = b[:m], s[:m]
+    keep, counts, kb, _ = ops.nms_segments(dev(boxes), dev(scores), stride, dev(np.array([n, m], np.int32)), thr, want_boxes=True)
+    keep, counts = keep.cpu().numpy(), counts.cpu().numpy()
+    assert np.array_equal(keep[: counts[0]], oracle.nms(b, s, thr))
+    assert np.array_equal(keep[stride: stride + counts[1]], oracle.nms(b[:m], s[:m], thr))

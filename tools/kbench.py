@@ -2,7 +2,7 @@
 """Per-kernel micro-benchmarks at the BASELINE shapes (CUDA events on the launching stream, L2 flushed between
 iterations). Development tool: prints one JSON line per kernel; bench.py stays the contract benchmark.
 
-    python tools/kbench.py [crop] [nms] [pool] [prep] [sim] [--shelves 32] [--iters 5]
+    python tools/kbench.py [crop] [nms] [select] [pool] [prep] [sim] [--shelves 32] [--iters 5]
 """
 import argparse
 import json
@@ -99,6 +99,31 @@ def bench_nms(args):
     report("nms stress (%d images x %d)" % (n_img, n), ms, best, 20.0 * len(ss) + 8.0 * K, kept=K)
 
 
+def bench_select(args):
+    """f1 + a1: candidate selection and the whole detector post-processing at the GLN frame (800 x 1066, 5 FPN levels)."""
+    from cvpce_b200 import detection
+    dev = "cuda"
+    H, W = 800, 1066
+    anchors = [torch.from_numpy(a).to(dev) for a in synth.fpn_anchors(H, W)]
+    n_per = [a.shape[0] for a in anchors]
+    A = sum(n_per)
+    for B in (1, args.shelves):
+        g = torch.Generator(device=dev).manual_seed(5)
+        for mu, tag in ((-4.6, "trained-like"), (-1.0, "dense")):
+            lg = (mu + 1.5 * torch.randn((B, A, 1), device=dev, generator=g))
+            rg = 0.3 * torch.randn((B, A, 4), device=dev, generator=g)
+            lgs, rgs = list(lg.split(n_per, dim=1)), list(rg.split(n_per, dim=1))
+            sizes = torch.tensor([[H, W]] * B, dtype=torch.int32, device=dev)
+            _, _, _, cnt, _, _ = ops.select_candidates(lgs, rgs, anchors, sizes, 0.05, 1000)
+            ncand = int(cnt.sum())
+            nbytes = 4.0 * A * B + 56.0 * ncand
+            ms, best = timeit(lambda: ops.select_candidates(lgs, rgs, anchors, sizes, 0.05, 1000, want_labels=False), args.iters)
+            report("select_candidates B=%d %s (%d anchors/img, %d cand)" % (B, tag, A, ncand), ms, best, nbytes)
+            head = {"cls_logits": lgs, "bbox_regression": rgs}
+            ms, best = timeit(lambda: detection.postprocess_detections_batch(head, anchors, sizes, 0.05, 1000, 0.5, 1000), args.iters)
+            report("postprocess (select+nms) B=%d %s" % (B, tag), ms, best, nbytes + 20.0 * ncand)
+
+
 def bench_crop(args):
     dev = "cuda"
     H, W = synth.SHELF_HW
@@ -172,7 +197,7 @@ def bench_sim(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("which", nargs="*", default=["nms", "crop", "pool", "prep", "sim"])
+    ap.add_argument("which", nargs="*", default=["nms", "select", "crop", "pool", "prep", "sim"])
     ap.add_argument("--shelves", type=int, default=32)
     ap.add_argument("--stress-images", type=int, default=512)
     ap.add_argument("--iters", type=int, default=5)
@@ -181,7 +206,7 @@ def main():
     args = ap.parse_args()
     torch.cuda.set_device(0)
     for w in args.which:
-        {"nms": bench_nms, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
+        {"nms": bench_nms, "select": bench_select, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
 
 
 if __name__ == "__main__":
