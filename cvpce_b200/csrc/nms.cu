@@ -49,6 +49,9 @@ struct NmsParams {
   const int32_t* seg_counts;   // strided form (seg_offsets == nullptr): segment b = [b*seg_stride, b*seg_stride + seg_counts[b])
   int seg_stride;
   int max_n;      // capacity of the shared arrays
+  int region_a;   // bytes of the shared region that holds the sort keys, then the grid
+  float win_scale;  // half-extent of a candidate's search window in units of its own width / height
+  int brute;      // threshold < 0 (or NaN): disjoint boxes suppress each other, every cell is visited
   int sort_cap;   // power of two >= max_n
   float iou_thr;
   float min_score;
@@ -60,18 +63,34 @@ struct NmsParams {
   float* kept_scores;
 };
 
+constexpr int kNmsGrid = 32;                     // kNmsGrid x kNmsGrid cells over the range of box centres
+constexpr int kNmsCells = kNmsGrid * kNmsGrid;
+constexpr int kNmsCellCap = 20;                  // kept boxes per cell; the rest go to the overflow list
+// bytes of the region that holds the sort keys first and the grid afterwards
+__host__ __device__ constexpr size_t nms_grid_bytes(int max_n) {
+  return (size_t)kNmsCells * 4 + (size_t)kNmsCells * kNmsCellCap * 2 + (((size_t)max_n * 2 + 15) & ~(size_t)15);
+}
+
+__device__ __forceinline__ bool finite4(const float4 b) {
+  return (fabsf(b.x) <= 3.0e38f) && (fabsf(b.y) <= 3.0e38f) && (fabsf(b.z) <= 3.0e38f) && (fabsf(b.w) <= 3.0e38f);
+}
+
 __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: keys u64[sort_cap] | sbox float4[max_n] | removed u8[max_n] (padded) | static parts below
+  // layout: region A = keys u64[sort_cap] during the sort, then {cell_count i32[cells] | cell_entry u16[cells*cap] |
+  // overflow u16[max_n]}; sbox float4[max_n]; orig u16[max_n] (index of sorted position i in the segment)
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);
-  float4* sbox = reinterpret_cast<float4*>(smem_raw + (size_t)p.sort_cap * 8);
-  unsigned char* removed = reinterpret_cast<unsigned char*>(sbox + p.max_n);
+  int* cell_count = reinterpret_cast<int*>(smem_raw);
+  unsigned short* cell_entry = reinterpret_cast<unsigned short*>(smem_raw + (size_t)kNmsCells * 4);
+  unsigned short* overflow = cell_entry + (size_t)kNmsCells * kNmsCellCap;
+  float4* sbox = reinterpret_cast<float4*>(smem_raw + p.region_a);
+  unsigned short* orig = reinterpret_cast<unsigned short*>(sbox + p.max_n);
 
   __shared__ unsigned long long panel_mask[kNmsPanel];
   __shared__ float4 kbox[kNmsPanel];
-  __shared__ int s_panel_kept;
-  __shared__ int s_total_kept;
-  __shared__ int s_stop;
+  __shared__ int suppressed[kNmsPanel];
+  __shared__ float s_red[4][32];
+  __shared__ int s_total_kept, s_stop, s_overflow;
 
   const int b = blockIdx.x;
   const int tid = threadIdx.x, nthr = blockDim.x;
@@ -112,29 +131,107 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
       __syncthreads();
     }
   }
-  // ---- 2. gather boxes in sorted order -------------------------------------------------------------------------
+  // ---- 2. gather boxes in sorted order; range of the box centres -----------------------------------------------------
+  float cx_lo = 3.0e38f, cx_hi = -3.0e38f, cy_lo = 3.0e38f, cy_hi = -3.0e38f;
   for (int i = tid; i < n; i += nthr) {
     const int idx = (int)(keys[i] & 0xffffffffu);
-    sbox[i] = __ldg(p.boxes + seg + idx);
-    removed[i] = 0;
+    const float4 bx = __ldg(p.boxes + seg + idx);
+    sbox[i] = bx;
+    orig[i] = (unsigned short)idx;
+    if (finite4(bx)) {
+      const float cx = 0.5f * (bx.x + bx.z), cy = 0.5f * (bx.y + bx.w);
+      cx_lo = fminf(cx_lo, cx);
+      cx_hi = fmaxf(cx_hi, cx);
+      cy_lo = fminf(cy_lo, cy);
+      cy_hi = fmaxf(cy_hi, cy);
+    }
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cx_lo = fminf(cx_lo, __shfl_xor_sync(0xffffffffu, cx_lo, o));
+    cx_hi = fmaxf(cx_hi, __shfl_xor_sync(0xffffffffu, cx_hi, o));
+    cy_lo = fminf(cy_lo, __shfl_xor_sync(0xffffffffu, cy_lo, o));
+    cy_hi = fmaxf(cy_hi, __shfl_xor_sync(0xffffffffu, cy_hi, o));
+  }
+  if (lane == 0) {
+    s_red[0][warp] = cx_lo;
+    s_red[1][warp] = cx_hi;
+    s_red[2][warp] = cy_lo;
+    s_red[3][warp] = cy_hi;
+  }
+  __syncthreads();  // also: every key has been read, region A can become the grid
+  for (int w = 0; w < nwarps; ++w) {
+    cx_lo = fminf(cx_lo, s_red[0][w]);
+    cx_hi = fmaxf(cx_hi, s_red[1][w]);
+    cy_lo = fminf(cy_lo, s_red[2][w]);
+    cy_hi = fmaxf(cy_hi, s_red[3][w]);
+  }
+  // cell of a coordinate: monotone in the coordinate, so a centre inside a window lies in a cell inside the window's range
+  const float inv_x = (float)kNmsGrid / fmaxf(cx_hi - cx_lo, 1e-30f), inv_y = (float)kNmsGrid / fmaxf(cy_hi - cy_lo, 1e-30f);
+  auto cell_x = [&](float x) { return min(kNmsGrid - 1, max(0, (int)fminf(fmaxf((x - cx_lo) * inv_x, 0.f), (float)kNmsGrid))); };
+  auto cell_y = [&](float y) { return min(kNmsGrid - 1, max(0, (int)fminf(fmaxf((y - cy_lo) * inv_y, 0.f), (float)kNmsGrid))); };
+  for (int i = tid; i < kNmsCells; i += nthr) cell_count[i] = 0;
+  if (tid < kNmsPanel) suppressed[tid] = 0;
   if (tid == 0) {
     s_total_kept = 0;
     s_stop = 0;
+    s_overflow = 0;
   }
   __syncthreads();
 
   const float thr = p.iou_thr;
   const int max_keep = p.max_keep > 0 ? p.max_keep : 0x7fffffff;
   const float2 scale = p.box_scale ? p.box_scale[b] : make_float2(1.f, 1.f);
+  const int T = nthr / kNmsPanel;  // threads that share one candidate of the panel (2..16)
+  const float abs_margin_x = 1e-6f * (cx_hi - cx_lo), abs_margin_y = 1e-6f * (cy_hi - cy_lo);
 
-  // ---- 3. panels -----------------------------------------------------------------------------------------------
+  // ---- 3. panels of 64 candidates in sorted order -------------------------------------------------------------------
   for (int p0 = 0; p0 < n; p0 += kNmsPanel) {
     const int pn = min(kNmsPanel, n - p0);
-    // A: intra-panel bitmask rows (bit c of row r set iff c > r and IoU(r,c) > thr)
+    // A: is the candidate suppressed by a box kept in an EARLIER panel?  Only kept boxes whose centre lies in the
+    //    candidate's window can exceed the threshold (header comment), so only those grid cells are visited.
+    {
+      const int c = tid / T, sub = tid - c * T;
+      if (c < pn) {
+        const float4 a = sbox[p0 + c];
+        const float w = a.z - a.x, h = a.w - a.y;
+        const bool full = p.brute || !finite4(a);
+        if (full || (w > 0.f && h > 0.f)) {  // an empty box has no intersection: it is never suppressed
+          int x0 = 0, x1 = kNmsGrid - 1, y0 = 0, y1 = kNmsGrid - 1;
+          if (!full) {
+            const float cxa = 0.5f * (a.x + a.z), cya = 0.5f * (a.y + a.w);
+            const float hx = w * p.win_scale + abs_margin_x + 1e-6f * fabsf(cxa);
+            const float hy = h * p.win_scale + abs_margin_y + 1e-6f * fabsf(cya);
+            x0 = cell_x(cxa - hx);
+            x1 = cell_x(cxa + hx);
+            y0 = cell_y(cya - hy);
+            y1 = cell_y(cya + hy);
+          }
+          const int ncx = x1 - x0 + 1, ncells = ncx * (y1 - y0 + 1);
+          bool hit = false;
+          for (int q = sub; q < ncells && !hit; q += T) {
+            const int qy = q / ncx;
+            const int cell = (y0 + qy) * kNmsGrid + x0 + (q - qy * ncx);
+            const int cnt = min(cell_count[cell], kNmsCellCap);
+            for (int e = 0; e < cnt; ++e) {
+              if (iou_exceeds(sbox[cell_entry[cell * kNmsCellCap + e]], a, thr)) {
+                hit = true;
+                break;
+              }
+            }
+          }
+          const int nover = s_overflow;
+          for (int e = sub; e < nover && !hit; e += T)
+            if (iou_exceeds(sbox[overflow[e]], a, thr)) hit = true;
+          if (hit) suppressed[c] = 1;
+        }
+      }
+    }
+    __syncthreads();
+    // B: intra-panel bitmask rows (bit c of row r set iff c > r and IoU(r,c) > thr)
     for (int r = warp; r < kNmsPanel; r += nwarps) {
       unsigned lo = 0, hi = 0;
-      if (r < pn) {  // warp-uniform
+      if (r < pn && !suppressed[r]) {  // warp-uniform
         const float4 br = sbox[p0 + r];
         const int c0 = lane, c1 = lane + 32;
         const bool b0 = (c0 > r && c0 < pn) ? iou_exceeds(br, sbox[p0 + c0], thr) : false;
@@ -145,21 +242,22 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
       if (lane == 0) panel_mask[r] = ((unsigned long long)hi << 32) | lo;
     }
     __syncthreads();
-    // B: one warp resolves the panel serially; every lane runs the same scalar recurrence (broadcast LDS)
+    // C: one warp resolves the panel serially (every lane runs the same scalar recurrence), writes the kept rows and
+    //    files the newly kept boxes in the grid
     if (warp == 0) {
       const int i0 = p0 + lane, i1 = p0 + lane + 32;
       bool r0 = true, r1 = true;  // "removed" (out of range, suppressed earlier, or below min_score)
       float sc0 = 0.f, sc1 = 0.f;
       int id0 = 0, id1 = 0;
       if (lane < pn) {
-        id0 = (int)(keys[i0] & 0xffffffffu);
+        id0 = orig[i0];
         sc0 = __ldg(p.scores + seg + id0);
-        r0 = removed[i0] || !(sc0 > p.min_score || sc0 != sc0);
+        r0 = suppressed[lane] || !(sc0 > p.min_score || sc0 != sc0);
       }
       if (lane + 32 < pn) {
-        id1 = (int)(keys[i1] & 0xffffffffu);
+        id1 = orig[i1];
         sc1 = __ldg(p.scores + seg + id1);
-        r1 = removed[i1] || !(sc1 > p.min_score || sc1 != sc1);
+        r1 = suppressed[lane + 32] || !(sc1 > p.min_score || sc1 != sc1);
       }
       unsigned long long rem =
           ((unsigned long long)__ballot_sync(0xffffffffu, r1) << 32) | __ballot_sync(0xffffffffu, r0);
@@ -189,39 +287,38 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
           const int rank = __popcll(keepbits & ((1ull << pos) - 1ull));
           if (rank < take) {
             const float4 bx = sbox[p0 + pos];
-            kbox[rank] = bx;
             const size_t o = (size_t)seg + base + rank;
             p.keep[o] = (long long)(h ? id1 : id0);
             if (p.kept_boxes)
               p.kept_boxes[o] = make_float4(__fmul_rn(bx.x, scale.x), __fmul_rn(bx.y, scale.y),
                                             __fmul_rn(bx.z, scale.x), __fmul_rn(bx.w, scale.y));
             if (p.kept_scores) p.kept_scores[o] = h ? sc1 : sc0;
+            // grid insertion: by centre cell; boxes that cannot intersect anything are left out
+            const float w = bx.z - bx.x, hgt = bx.w - bx.y;
+            if (p.brute || !(w <= 0.f || hgt <= 0.f)) {
+              int slot = kNmsCellCap;
+              int cell = 0;
+              if (finite4(bx)) {
+                cell = cell_y(0.5f * (bx.y + bx.w)) * kNmsGrid + cell_x(0.5f * (bx.x + bx.z));
+                slot = atomicAdd(&cell_count[cell], 1);
+              }
+              if (slot < kNmsCellCap)
+                cell_entry[cell * kNmsCellCap + slot] = (unsigned short)(p0 + pos);
+              else
+                overflow[atomicAdd(&s_overflow, 1)] = (unsigned short)(p0 + pos);
+            }
           }
         }
       }
+      suppressed[lane] = 0;
+      suppressed[lane + 32] = 0;
       if (lane == 0) {
-        s_panel_kept = take;
         s_total_kept = base + take;
         if (base + take >= max_keep || below) s_stop = 1;
       }
     }
     __syncthreads();
     if (s_stop) break;
-    // C: the panel's kept boxes suppress the rest of the list
-    const int nk = s_panel_kept;
-    if (nk > 0) {
-      for (int j = p0 + kNmsPanel + tid; j < n; j += nthr) {
-        if (removed[j]) continue;
-        const float4 bj = sbox[j];
-        for (int t = 0; t < nk; ++t) {
-          if (iou_exceeds(kbox[t], bj, thr)) {
-            removed[j] = 1;
-            break;
-          }
-        }
-      }
-    }
-    __syncthreads();
   }
   if (tid == 0) p.keep_counts[b] = s_total_kept;
 }
@@ -254,7 +351,15 @@ static int launch_nms(NmsParams& p, const float* boxes, const float* scores, int
   p.box_scale = reinterpret_cast<const float2*>(box_scale);
   p.kept_boxes = reinterpret_cast<float4*>(kept_boxes);
   p.kept_scores = kept_scores;
-  const size_t smem = (size_t)cap * 8 + (size_t)p.max_n * 16 + (((size_t)p.max_n + 15) & ~(size_t)15);
+  size_t region_a = (size_t)cap * 8;
+  if (region_a < nms_grid_bytes(p.max_n)) region_a = nms_grid_bytes(p.max_n);
+  p.region_a = (int)region_a;
+  // IoU > t needs the overlap to exceed t * max(w_a, w_b) in x (and likewise in y), which bounds the distance of the two
+  // centres by w_a * max(0.5, 0.5/t - 0.5); 1/64 of slack covers the fp32 rounding of the IoU and of the centres
+  p.brute = !(iou_threshold >= 0.f);
+  p.win_scale = p.brute ? 0.f : (iou_threshold >= 0.5f ? 0.5f : (iou_threshold > 1e-3f ? 0.5f / iou_threshold - 0.5f : INFINITY)) * (1.f + 1.f / 64);
+  if (!p.brute && !(iou_threshold > 1e-3f)) p.brute = 1;
+  const size_t smem = region_a + (size_t)p.max_n * 16 + (((size_t)p.max_n * 2 + 15) & ~(size_t)15);
   int threads = cap / 2;
   if (threads < 128) threads = 128;
   if (threads > 1024) threads = 1024;

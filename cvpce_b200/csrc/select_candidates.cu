@@ -89,27 +89,85 @@ __device__ __forceinline__ bool sel_key(const float x, const SelParams& p, uint3
   return true;
 }
 
-// f(flat index, logit) for every candidate of the level; 128-bit loads once the pointer is 16-byte aligned (per-level views
-// of the concatenated head output start at arbitrary multiples of 4 bytes), 2 x 16 B in flight per thread
+// f(flat index, logit) for every candidate of the level whose logit passes the conservative pre-filter, with DENSE lanes:
+// a trained detector leaves ~1 logit in 10 above the pre-filter, so evaluating the sigmoid where the logit is loaded
+// would run ~70 instructions per element at ~10% lane utilisation.  Instead every warp compacts the survivors of its
+// 128-bit loads (ballot + popc) into a private shared-memory queue and, whenever 32 are waiting, evaluates one per lane.
+// Per-level views of the concatenated head output start at arbitrary multiples of 4 bytes: scalar head/tail, 2 x 16 B
+// in flight per thread in between.
+constexpr int kSelQueue = 32 + 8 * 32;  // a full batch left over + one iteration's survivors (2 loads x 4 x 32 lanes)
+
+constexpr size_t kSelDynSmem = (size_t)(kSelThreads / 32) * kSelQueue * 8;  // 73,728 B
+
+struct WarpQueue {
+  float* x;  // [kSelQueue] of this warp
+  int* i;
+  int n;     // warp-uniform
+};
+
+__device__ __forceinline__ void queue_push(WarpQueue& q, const bool pass, const float x, const int i) {
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned m = __ballot_sync(0xffffffffu, pass);
+  if (pass) {
+    const int pos = q.n + __popc(m & ((1u << lane) - 1u));
+    q.x[pos] = x;
+    q.i[pos] = i;
+  }
+  q.n += __popc(m);
+}
+
 template <class F>
-__device__ __forceinline__ void stream_level(const float* __restrict__ logits, const int n, F f) {
+__device__ __forceinline__ void queue_drain(WarpQueue& q, const bool all, F& f) {
+  const int lane = threadIdx.x & 31;
+  __syncwarp();
+  while (q.n >= 32 || (all && q.n > 0)) {
+    const int take = min(q.n, 32);
+    const int pos = q.n - take + lane;
+    if (lane < take) f(q.i[pos], q.x[pos]);
+    q.n -= take;
+  }
+  __syncwarp();
+}
+
+template <class F>
+__device__ __forceinline__ void stream_level(const float* __restrict__ logits, const int n, const float prefilter,
+                                             float* queue_x, int* queue_i, F f) {
   const int tid = threadIdx.x;
+  WarpQueue q;
+  q.x = queue_x + (tid >> 5) * kSelQueue;
+  q.i = queue_i + (tid >> 5) * kSelQueue;
+  q.n = 0;
   int head = (int)((4u - (unsigned)((reinterpret_cast<uintptr_t>(logits) >> 2) & 3u)) & 3u);
   head = min(head, n);
-  if (tid < head) f(tid, __ldg(logits + tid));
   const float4* v = reinterpret_cast<const float4*>(logits + head);
   const int nv = (n - head) >> 2;
-#pragma unroll 2
-  for (int j = tid; j < nv; j += kSelThreads) {
-    const float4 x = __ldg(v + j);
-    const int i = head + 4 * j;
-    f(i, x.x);
-    f(i + 1, x.y);
-    f(i + 2, x.z);
-    f(i + 3, x.w);
-  }
   const int t0 = head + 4 * nv;
-  if (tid < n - t0) f(t0 + tid, __ldg(logits + t0 + tid));
+  if (tid < 32) {  // warp 0: the unaligned head and tail elements (at most 3 + 3)
+    float x = 0.f;
+    int i = -1;
+    if (tid < head) i = tid;
+    else if (tid - head < n - t0) i = t0 + tid - head;
+    if (i >= 0) x = __ldg(logits + i);
+    queue_push(q, i >= 0 && x >= prefilter, x, i);
+  }
+  for (int j0 = (tid >> 5) * 32; j0 < nv; j0 += 2 * kSelThreads) {  // warp-uniform trip count
+    const int ja = j0 + (tid & 31), jb = ja + kSelThreads;
+    const bool va = ja < nv, vb = jb < nv;
+    float4 xa = make_float4(0.f, 0.f, 0.f, 0.f), xb = xa;
+    if (va) xa = __ldg(v + ja);
+    if (vb) xb = __ldg(v + jb);
+    const int ia = head + 4 * ja, ib = head + 4 * jb;
+    queue_push(q, va && xa.x >= prefilter, xa.x, ia);
+    queue_push(q, va && xa.y >= prefilter, xa.y, ia + 1);
+    queue_push(q, va && xa.z >= prefilter, xa.z, ia + 2);
+    queue_push(q, va && xa.w >= prefilter, xa.w, ia + 3);
+    queue_push(q, vb && xb.x >= prefilter, xb.x, ib);
+    queue_push(q, vb && xb.y >= prefilter, xb.y, ib + 1);
+    queue_push(q, vb && xb.z >= prefilter, xb.z, ib + 2);
+    queue_push(q, vb && xb.w >= prefilter, xb.w, ib + 3);
+    queue_drain(q, false, f);
+  }
+  queue_drain(q, true, f);
 }
 
 // exclusive prefix sum of v over the block (blockDim.x == kSelThreads); total returned through *total
@@ -145,6 +203,9 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_candidates_kernel(const
   cg::cluster_group cluster = cg::this_cluster();
   __shared__ unsigned long long list[kSelListCap];
   __shared__ int hist[kSelBins];
+  extern __shared__ __align__(16) unsigned char sel_dyn_smem[];  // per-warp compaction queues
+  float* queue_x = reinterpret_cast<float*>(sel_dyn_smem);
+  int* queue_i = reinterpret_cast<int*>(queue_x + (kSelThreads / 32) * kSelQueue);
   __shared__ int warp_tot[33];
   __shared__ int s_bin, s_above, s_pop;
   __shared__ int s_n_certain, s_n_boundary;
@@ -170,7 +231,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_candidates_kernel(const
     for (int iter = 0;; ++iter) {
       for (int i = tid; i < kSelBins; i += kSelThreads) hist[i] = 0;
       __syncthreads();
-      stream_level(logits, n, [&](int, float x) {
+      stream_level(logits, n, p.prefilter, queue_x, queue_i, [&](int, float x) {
         uint32_t key;
         if (sel_key(x, p, key)) {
           const uint32_t rel = key - lo;
@@ -220,7 +281,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_candidates_kernel(const
     }
     __syncthreads();
     if (!ordered_ties) {
-      stream_level(logits, n, [&](int i, float x) {
+      stream_level(logits, n, p.prefilter, queue_x, queue_i, [&](int i, float x) {
         uint32_t key;
         if (sel_key(x, p, key) && key >= lo) {
           const unsigned long long e = ((unsigned long long)(~key) << 32) | (unsigned)i;
@@ -395,12 +456,40 @@ extern "C" int cvpce_select_candidates(const cvpce_fpn_level* levels, int n_leve
   p.seg_counts = seg_counts;
   p.level_counts = level_counts;
 
-  int csize = 1;
-  while (csize < n_levels) csize <<= 1;
+  static thread_local bool configured = false;
+  if (!configured) {
+    CVPCE_CUDA_OK(cudaFuncSetAttribute(select_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSelDynSmem));
+    configured = true;
+  }
+  // one CTA per level; if this device refuses a cluster of exactly n_levels CTAs, pad to the next power of two (the
+  // padding CTAs only take part in the count exchange)
+  static thread_local int exact_ok[CVPCE_SELECT_MAX_LEVELS + 1] = {0};  // 0 unknown, 1 yes, -1 no
+  int csize = n_levels;
+  if (exact_ok[n_levels] == 0) {
+    cudaLaunchConfig_t q = {};
+    q.gridDim = dim3(n_levels, 1, 1);
+    q.blockDim = dim3(kSelThreads, 1, 1);
+    q.dynamicSmemBytes = kSelDynSmem;
+    cudaLaunchAttribute qa[1];
+    qa[0].id = cudaLaunchAttributeClusterDimension;
+    qa[0].val.clusterDim.x = n_levels;
+    qa[0].val.clusterDim.y = 1;
+    qa[0].val.clusterDim.z = 1;
+    q.attrs = qa;
+    q.numAttrs = 1;
+    int n_clusters = 0;
+    const cudaError_t e = cudaOccupancyMaxActiveClusters(&n_clusters, select_candidates_kernel, &q);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    exact_ok[n_levels] = (e == cudaSuccess && n_clusters > 0) ? 1 : -1;
+  }
+  if (exact_ok[n_levels] < 0) {
+    csize = 1;
+    while (csize < n_levels) csize <<= 1;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(csize, n_images, 1);
   cfg.blockDim = dim3(kSelThreads, 1, 1);
-  cfg.dynamicSmemBytes = 0;
+  cfg.dynamicSmemBytes = kSelDynSmem;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;

@@ -90,6 +90,15 @@ def golden_mac(ref):
         out["macvgg_embeddings"] = enc(x).numpy()
     w0 = enc.block1[0].weight.detach().reshape(-1)
     out["macvgg_weight_probe"] = torch.cat([w0[:8], enc.block2[-2].weight.detach().reshape(-1)[:8]]).numpy()
+    # (3) MACResNet (classification.py:53-85) over a seeded random-init resnet50 (BatchNorm in eval mode), descriptor
+    # layers (2, 3): 512 + 1024 channels -> 1536-d.  The reference's own factory (classification.py:111-121) passes
+    # constructor arguments the installed torchvision no longer accepts; the class itself is used unchanged.
+    from torchvision.models import resnet
+    torch.manual_seed(synth.WEIGHT_SEED + 1)
+    enc = ref.models.classification.MACResNet(resnet.resnet50(weights=None), [2, 3]).eval().requires_grad_(False)
+    with torch.no_grad():
+        out["macresnet_embeddings"] = enc(x).numpy()
+    out["macresnet_weight_probe"] = enc.blocks[0][0][0].weight.detach().reshape(-1)[:8].numpy()
     np.savez_compressed(os.path.join(OUT, "mac.npz"), **out)
     print("mac:", {k: v.shape for k, v in out.items()})
 

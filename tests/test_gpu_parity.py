@@ -495,3 +495,33 @@ def test_nms_segments_equals_csr_form(ops):
     keep, counts = keep.cpu().numpy(), counts.cpu().numpy()
     assert np.array_equal(keep[: counts[0]], oracle.nms(b, s, thr))
     assert np.array_equal(keep[stride: stride + counts[1]], oracle.nms(b[:m], s[:m], thr))
+
+
+@pytest.mark.parametrize("thr", [0.05, 0.3, 0.5, 0.7, 0.0])
+def test_nms_grid_window_adversarial_geometry(ops, thr):
+    """The kernel only tests a candidate against kept boxes whose centre lies in a window around it (a necessary condition
+    for IoU > thr) and files kept boxes in a 32x32 grid with an overflow list: nested / concentric boxes (one cell
+    overflows), clusters, extreme aspect ratios, tiny and huge boxes, degenerate and duplicated boxes -- keep lists must
+    stay bit-exact with the all-pairs oracle at every threshold."""
+    rs = np.random.RandomState(int(thr * 100) + 3)
+    parts = []
+    c = rs.uniform(400, 600, (1, 2))
+    half = np.linspace(2, 380, 700)[:, None] * rs.uniform(0.9, 1.1, (700, 2))          # concentric: all centres in one cell
+    parts.append(np.concatenate([c - half, c + half], 1))
+    ctr = rs.uniform(0, 1000, (40, 2))[rs.randint(0, 40, 1500)] + rs.normal(0, 6, (1500, 2))   # 40 tight clusters
+    wh = rs.uniform(20, 90, (1500, 2))
+    parts.append(np.concatenate([ctr - wh / 2, ctr + wh / 2], 1))
+    ctr = rs.uniform(0, 1000, (600, 2))                                                 # extreme aspect ratios
+    wh = np.stack([rs.uniform(2, 900, 600), rs.uniform(2, 30, 600)], 1)[:, rs.permutation(2)]
+    parts.append(np.concatenate([ctr - wh / 2, ctr + wh / 2], 1))
+    ctr = rs.uniform(0, 1000, (300, 2))                                                 # tiny boxes
+    wh = rs.uniform(1e-3, 0.5, (300, 2))
+    parts.append(np.concatenate([ctr - wh / 2, ctr + wh / 2], 1))
+    parts.append(np.array([[0, 0, 1000, 1000], [-5000, -5000, 6000, 6000], [10, 10, 10, 50], [30, 40, 20, 60]], np.float64))
+    boxes = np.concatenate(parts).astype(np.float32)
+    boxes = np.concatenate([boxes, boxes[rs.randint(0, len(boxes), 200)]])               # exact duplicates
+    scores = rs.uniform(0, 1, len(boxes)).astype(np.float32)
+    scores[rs.randint(0, len(scores), 300)] = 0.5                                       # score ties
+    want = oracle.nms(boxes, scores, thr)
+    got = ops.nms(dev(boxes), dev(scores), thr).cpu().numpy()
+    assert np.array_equal(got, want), (thr, len(got), len(want))

@@ -31,14 +31,23 @@ for d in rows[2:]:
                 print('  stall %-60s %.2f' % (h.replace('smsp__average_warps_issue_stalled_', '').replace('_per_issue_active.ratio', ''), v))
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hi = next(i for i, r in enumerate(rows) if 'Source' in r and 'Instructions Executed' in r)
-hdr = rows[hi]
-data = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
-ia, ins, smp = hdr.index('Source'), hdr.index('Instructions Executed'), hdr.index('# Samples')
-ti = sum(int(r[ins]) for r in data if r[ins].isdigit()) or 1
-ts = sum(int(r[smp]) for r in data if r[smp].isdigit()) or 1
-print("-- hottest SASS by stall samples (idx, %inst, %samples)")
-hot = sorted(range(len(data)), key=lambda n: -int(data[n][smp] or 0))[:nhot]
-for n in sorted(hot):
-    r = data[n]
-    print('%5d %6.2f%%i %6.2f%%s  %s' % (n, 100 * int(r[ins]) / ti, 100 * int(r[smp]) / ts, r[ia].strip()[:100]))
+# one table per profiled launch, each starting with its own header row; show the first launch of every kernel name
+starts = [i for i, r in enumerate(rows) if 'Source' in r and 'Instructions Executed' in r]
+names = [d[idx['Kernel Name']] for d in rows_raw[2:]] if (rows_raw := list(csv.reader(io.StringIO(raw)))) else []
+seen = set()
+for t, hi in enumerate(starts):
+    name = names[t] if t < len(names) else "launch %d" % t
+    if name in seen:
+        continue
+    seen.add(name)
+    hdr = rows[hi]
+    end = starts[t + 1] if t + 1 < len(starts) else len(rows)
+    data = [r for r in rows[hi + 1:end] if len(r) == len(hdr)]
+    ia, ins, smp = hdr.index('Source'), hdr.index('Instructions Executed'), hdr.index('# Samples')
+    ti = sum(int(r[ins]) for r in data if r[ins].isdigit()) or 1
+    ts = sum(int(r[smp]) for r in data if r[smp].isdigit()) or 1
+    print("-- %s: hottest SASS by stall samples (idx, %%inst, %%samples)" % name[:80])
+    hot = sorted(range(len(data)), key=lambda n: -int(data[n][smp] if data[n][smp].isdigit() else 0))[:nhot]
+    for n in sorted(hot):
+        r = data[n]
+        print('%5d %6.2f%%i %6.2f%%s  %s' % (n, 100 * int(r[ins] or 0) / ti, 100 * int(r[smp] or 0) / ts, r[ia].strip()[:100]))
