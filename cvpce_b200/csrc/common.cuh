@@ -50,4 +50,103 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Ascending bitonic sort of `cap` (a power of two >= 2) 64-bit keys in shared memory by the whole block.
+// The network is the textbook one; what is tuned is where each compare-exchange step runs, because a step that goes
+// through shared memory costs one full pass over the keys plus a block barrier:
+//   * strides 32..1 of every stage run in registers, one warp per 64-key chunk (lane holds keys lane and lane+32;
+//     stride 32 is in-thread, 16..1 are 64-bit warp shuffles) -- and the first six stages (k <= 64) entirely so;
+//   * strides >= 64 are fused three at a time: a thread loads the 8 keys of a radix-8 butterfly, runs 3 steps in
+//     registers and stores them (consecutive threads touch consecutive keys: conflict-free).
+// 8192 keys: 20 passes + barriers instead of 91.  Every thread of the block must call it; keys must be visible
+// (barrier) before the call and are visible to all threads after it.
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void sort_cx(unsigned long long& lo, unsigned long long& hi, const bool up) {
+  if ((lo > hi) == up) {
+    const unsigned long long t = lo;
+    lo = hi;
+    hi = t;
+  }
+}
+
+// strides 32..1 of stage k (or, with first == true, all stages 2..64) for the 64-key chunks, one warp per chunk
+__device__ __forceinline__ void sort_warp_pass(unsigned long long* keys, const int cap, const int k, const bool first) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int c = warp; c < (cap >> 6); c += nwarps) {
+    const int ia = (c << 6) + lane, ib = ia + 32;
+    unsigned long long a = keys[ia], b = keys[ib];
+    for (int kk = first ? 2 : k; kk <= (first ? 64 : k); kk <<= 1) {
+      const bool up_a = (ia & kk) == 0, up_b = (ib & kk) == 0;
+      if (kk >= 64) sort_cx(a, b, up_a);  // stride 32 (only from stage 64 on)
+#pragma unroll
+      for (int j = 16; j > 0; j >>= 1) {
+        if (j < kk) {
+          const unsigned long long pa = __shfl_xor_sync(0xffffffffu, a, j), pb = __shfl_xor_sync(0xffffffffu, b, j);
+          const bool lower = (lane & j) == 0;
+          // the lower partner keeps the minimum when the run ascends
+          a = ((a < pa) == (lower == up_a)) ? a : pa;
+          b = ((b < pb) == (lower == up_b)) ? b : pb;
+        }
+      }
+    }
+    keys[ia] = a;
+    keys[ib] = b;
+  }
+}
+
+template <int R>  // R fused steps: strides j, j/2, .., j >> (R-1) (all >= 64) of stage k
+__device__ __forceinline__ void sort_high_pass(unsigned long long* keys, const int cap, const int k, const int j) {
+  const int jl = j >> (R - 1);
+  for (int t = threadIdx.x; t < (cap >> R); t += blockDim.x) {
+    const int base = ((t & ~(jl - 1)) << R) | (t & (jl - 1));
+    const bool up = (base & k) == 0;
+    unsigned long long e[1 << R];
+#pragma unroll
+    for (int m = 0; m < (1 << R); ++m) e[m] = keys[base + m * jl];
+#pragma unroll
+    for (int s = R - 1; s >= 0; --s) {
+#pragma unroll
+      for (int m = 0; m < (1 << R); ++m)
+        if (!(m & (1 << s))) sort_cx(e[m], e[m | (1 << s)], up);
+    }
+#pragma unroll
+    for (int m = 0; m < (1 << R); ++m) keys[base + m * jl] = e[m];
+  }
+}
+
+__device__ __forceinline__ void block_bitonic_sort_u64(unsigned long long* keys, const int cap) {
+  if (cap < 64) {  // tiny inputs: plain network
+    for (int k = 2; k <= cap; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = threadIdx.x; t < (cap >> 1); t += blockDim.x) {
+          const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+          sort_cx(keys[i], keys[i | j], (i & k) == 0);
+        }
+        __syncthreads();
+      }
+    }
+    return;
+  }
+  sort_warp_pass(keys, cap, 64, true);
+  __syncthreads();
+  for (int k = 128; k <= cap; k <<= 1) {
+    int j = k >> 1;
+    while (j >= 64) {
+      if (j >= 256) {
+        sort_high_pass<3>(keys, cap, k, j);
+        j >>= 3;
+      } else if (j >= 128) {
+        sort_high_pass<2>(keys, cap, k, j);
+        j >>= 2;
+      } else {
+        sort_high_pass<1>(keys, cap, k, j);
+        j >>= 1;
+      }
+      __syncthreads();
+    }
+    sort_warp_pass(keys, cap, k, false);
+    __syncthreads();
+  }
+}
+
 }  // namespace cvpce

@@ -19,6 +19,23 @@ namespace cvpce {
 
 constexpr int kNmsPanel = 64;
 
+// development aid (build with CVPCE_NVCC_EXTRA=-DCVPCE_PHASE_TIMERS): cycles per phase of block 0, thread 0
+#ifdef CVPCE_PHASE_TIMERS
+__device__ long long g_nms_phase[8];
+#define PHASE_INIT long long _t_last = clock64();
+#define PHASE_COUNT g_nms_phase[5] += 1;
+#define PHASE_MARK(k)                                         \
+  if (blockIdx.x == 0 && threadIdx.x == 0) {                  \
+    const long long _now = clock64();                         \
+    g_nms_phase[k] += _now - _t_last;                         \
+    _t_last = _now;                                           \
+  }
+#else
+#define PHASE_INIT
+#define PHASE_MARK(k)
+#define PHASE_COUNT ;
+#endif
+
 __device__ __forceinline__ uint32_t desc_score_key(float s) {
   // ascending order of this key == descending score; NaN first (torch.sort(descending=True) puts NaN first)
   if (s != s) return 0u;
@@ -50,6 +67,7 @@ struct NmsParams {
   int seg_stride;
   int max_n;      // capacity of the shared arrays
   int region_a;   // bytes of the shared region that holds the sort keys, then the grid
+  float size_ratio; // a kept box b can only suppress a if w_b > size_ratio * w_a (and likewise in y)
   float win_scale;  // half-extent of a candidate's search window in units of its own width / height
   int brute;      // threshold < 0 (or NaN): disjoint boxes suppress each other, every cell is visited
   int sort_cap;   // power of two >= max_n
@@ -63,12 +81,20 @@ struct NmsParams {
   float* kept_scores;
 };
 
-constexpr int kNmsGrid = 32;                     // kNmsGrid x kNmsGrid cells over the range of box centres
-constexpr int kNmsCells = kNmsGrid * kNmsGrid;
-constexpr int kNmsCellCap = 20;                  // kept boxes per cell; the rest go to the overflow list
+constexpr int kNmsGrid = 32;      // finest level: kNmsGrid x kNmsGrid cells over the range of box centres
+constexpr int kNmsLevels = 6;     // level l: (32 >> l)^2 cells, holds kept boxes of (normalised) size [2^l, 2^(l+1)) fine cells
+constexpr int kNmsCells = 1024 + 256 + 64 + 16 + 4 + 1;
+constexpr int kNmsCellCap = 16;   // kept boxes per cell; the rest go to the overflow list
+__device__ __forceinline__ int nms_level_base(int l) { return (4096 - (4096 >> (2 * l))) / 3; }  // 0,1024,1280,1344,1360,1364
+// size class of a box whose larger side measures v fine cells (monotone in v)
+__device__ __forceinline__ int nms_level(float v) {
+  if (!(v >= 2.f)) return 0;
+  if (v >= 32.f) return kNmsLevels - 1;
+  return ilogbf(v);
+}
 // bytes of the region that holds the sort keys first and the grid afterwards
 __host__ __device__ constexpr size_t nms_grid_bytes(int max_n) {
-  return (size_t)kNmsCells * 4 + (size_t)kNmsCells * kNmsCellCap * 2 + (((size_t)max_n * 2 + 15) & ~(size_t)15);
+  return ((size_t)kNmsCells * 4 + (size_t)kNmsCells * kNmsCellCap * 2 + (size_t)max_n * 2 + 15) & ~(size_t)15;
 }
 
 __device__ __forceinline__ bool finite4(const float4 b) {
@@ -77,7 +103,7 @@ __device__ __forceinline__ bool finite4(const float4 b) {
 
 __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: region A = keys u64[sort_cap] during the sort, then {cell_count i32[cells] | cell_entry u16[cells*cap] |
+  // layout: region A = keys u64[sort_cap] during the sort, then {cell_count i32[cells] | cell_entry u16[cells*cap] (6 levels, 32x32 .. 1x1) |
   // overflow u16[max_n]}; sbox float4[max_n]; orig u16[max_n] (index of sorted position i in the segment)
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);
   int* cell_count = reinterpret_cast<int*>(smem_raw);
@@ -109,6 +135,7 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
   int cap = 2;
   while (cap < n) cap <<= 1;
 
+  PHASE_INIT
   // ---- 1. keys -------------------------------------------------------------------------------------------------
   for (int i = tid; i < cap; i += nthr) {
     unsigned long long k = ~0ull;
@@ -116,21 +143,8 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
     keys[i] = k;
   }
   __syncthreads();
-  for (int k = 2; k <= cap; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = tid; t < (cap >> 1); t += nthr) {
-        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // insert a 0 bit at position log2(j)
-        const int l = i | j;
-        const unsigned long long a = keys[i], c = keys[l];
-        const bool up = ((i & k) == 0);
-        if ((a > c) == up) {
-          keys[i] = c;
-          keys[l] = a;
-        }
-      }
-      __syncthreads();
-    }
-  }
+  block_bitonic_sort_u64(keys, cap);  // common.cuh: strides <= 32 in registers, larger ones fused three at a time
+  PHASE_MARK(0)
   // ---- 2. gather boxes in sorted order; range of the box centres -----------------------------------------------------
   float cx_lo = 3.0e38f, cx_hi = -3.0e38f, cy_lo = 3.0e38f, cy_hi = -3.0e38f;
   for (int i = tid; i < n; i += nthr) {
@@ -179,6 +193,7 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
   }
   __syncthreads();
 
+  PHASE_MARK(1)
   const float thr = p.iou_thr;
   const int max_keep = p.max_keep > 0 ? p.max_keep : 0x7fffffff;
   const float2 scale = p.box_scale ? p.box_scale[b] : make_float2(1.f, 1.f);
@@ -188,6 +203,19 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
   // ---- 3. panels of 64 candidates in sorted order -------------------------------------------------------------------
   for (int p0 = 0; p0 < n; p0 += kNmsPanel) {
     const int pn = min(kNmsPanel, n - p0);
+    // the resolving warp needs the panel's scores in step C: issue the (L2-latency) loads now, they land during A and B
+    float sc0 = 0.f, sc1 = 0.f;
+    int id0 = 0, id1 = 0;
+    if (warp == 0) {
+      if (lane < pn) {
+        id0 = orig[p0 + lane];
+        sc0 = __ldg(p.scores + seg + id0);
+      }
+      if (lane + 32 < pn) {
+        id1 = orig[p0 + lane + 32];
+        sc1 = __ldg(p.scores + seg + id1);
+      }
+    }
     // A: is the candidate suppressed by a box kept in an EARLIER panel?  Only kept boxes whose centre lies in the
     //    candidate's window can exceed the threshold (header comment), so only those grid cells are visited.
     {
@@ -197,7 +225,10 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
         const float w = a.z - a.x, h = a.w - a.y;
         const bool full = p.brute || !finite4(a);
         if (full || (w > 0.f && h > 0.f)) {  // an empty box has no intersection: it is never suppressed
-          int x0 = 0, x1 = kNmsGrid - 1, y0 = 0, y1 = kNmsGrid - 1;
+          // Kept boxes are filed by size class (level) and centre cell.  b can only suppress a if every side of b is
+          // within (t, 1/t) of a's, so a visits the levels of sizes t*m_a .. m_a/t only, and in each of them the
+          // cells its window covers: a bounded number of cells whatever the mix of box sizes.
+          int x0 = 0, x1 = kNmsGrid - 1, y0 = 0, y1 = kNmsGrid - 1, l0 = 0, l1 = kNmsLevels - 1;
           if (!full) {
             const float cxa = 0.5f * (a.x + a.z), cya = 0.5f * (a.y + a.w);
             const float hx = w * p.win_scale + abs_margin_x + 1e-6f * fabsf(cxa);
@@ -206,17 +237,24 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
             x1 = cell_x(cxa + hx);
             y0 = cell_y(cya - hy);
             y1 = cell_y(cya + hy);
+            const float m = fmaxf(w * inv_x, h * inv_y);
+            l0 = nms_level(m * p.size_ratio);
+            l1 = nms_level(m / p.size_ratio);
           }
-          const int ncx = x1 - x0 + 1, ncells = ncx * (y1 - y0 + 1);
           bool hit = false;
-          for (int q = sub; q < ncells && !hit; q += T) {
-            const int qy = q / ncx;
-            const int cell = (y0 + qy) * kNmsGrid + x0 + (q - qy * ncx);
-            const int cnt = min(cell_count[cell], kNmsCellCap);
-            for (int e = 0; e < cnt; ++e) {
-              if (iou_exceeds(sbox[cell_entry[cell * kNmsCellCap + e]], a, thr)) {
-                hit = true;
-                break;
+          for (int l = l0; l <= l1 && !hit; ++l) {
+            const int g = kNmsGrid >> l, X0 = x0 >> l, Y0 = y0 >> l;
+            const int ncx = (x1 >> l) - X0 + 1, ncells = ncx * ((y1 >> l) - Y0 + 1);
+            const int base = nms_level_base(l) + Y0 * g + X0;
+            for (int q = sub; q < ncells && !hit; q += T) {
+              const int qy = q / ncx;
+              const int cell = base + qy * g + (q - qy * ncx);
+              const int cnt = min(cell_count[cell], kNmsCellCap);
+              for (int e = 0; e < cnt; ++e) {
+                if (iou_exceeds(sbox[cell_entry[cell * kNmsCellCap + e]], a, thr)) {
+                  hit = true;
+                  break;
+                }
               }
             }
           }
@@ -228,6 +266,7 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
       }
     }
     __syncthreads();
+    PHASE_MARK(2)
     // B: intra-panel bitmask rows (bit c of row r set iff c > r and IoU(r,c) > thr)
     for (int r = warp; r < kNmsPanel; r += nwarps) {
       unsigned lo = 0, hi = 0;
@@ -242,34 +281,32 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
       if (lane == 0) panel_mask[r] = ((unsigned long long)hi << 32) | lo;
     }
     __syncthreads();
+    PHASE_MARK(3)
     // C: one warp resolves the panel serially (every lane runs the same scalar recurrence), writes the kept rows and
     //    files the newly kept boxes in the grid
     if (warp == 0) {
-      const int i0 = p0 + lane, i1 = p0 + lane + 32;
       bool r0 = true, r1 = true;  // "removed" (out of range, suppressed earlier, or below min_score)
-      float sc0 = 0.f, sc1 = 0.f;
-      int id0 = 0, id1 = 0;
-      if (lane < pn) {
-        id0 = orig[i0];
-        sc0 = __ldg(p.scores + seg + id0);
-        r0 = suppressed[lane] || !(sc0 > p.min_score || sc0 != sc0);
-      }
-      if (lane + 32 < pn) {
-        id1 = orig[i1];
-        sc1 = __ldg(p.scores + seg + id1);
-        r1 = suppressed[lane + 32] || !(sc1 > p.min_score || sc1 != sc1);
-      }
-      unsigned long long rem =
-          ((unsigned long long)__ballot_sync(0xffffffffu, r1) << 32) | __ballot_sync(0xffffffffu, r0);
-      unsigned long long keepbits = 0;
-#pragma unroll 8
-      for (int i = 0; i < kNmsPanel; ++i) {
-        const unsigned long long m = panel_mask[i];
-        if (!((rem >> i) & 1ull)) {
-          keepbits |= (1ull << i);
-          rem |= m;
+      if (lane < pn) r0 = suppressed[lane] || !(sc0 > p.min_score || sc0 != sc0);
+      if (lane + 32 < pn) r1 = suppressed[lane + 32] || !(sc1 > p.min_score || sc1 != sc1);
+      // rem: bit i set = candidate i is out (out of range, suppressed by an earlier panel or an earlier kept candidate of
+      // this panel, below min_score).  Row masks only have bits c > r, so bit i is final once step i has run and
+      // kept = ~rem at the end.  32-bit halves with compile-time bit positions: two dependent instructions per step.
+      unsigned rem_lo = __ballot_sync(0xffffffffu, r0), rem_hi = __ballot_sync(0xffffffffu, r1);
+      const uint2* mask2 = reinterpret_cast<const uint2*>(panel_mask);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const uint2 m = mask2[i];
+        if (!(rem_lo & (1u << i))) {
+          rem_lo |= m.x;
+          rem_hi |= m.y;
         }
       }
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const uint2 m = mask2[32 + i];
+        if (!(rem_hi & (1u << i))) rem_hi |= m.y;
+      }
+      const unsigned long long keepbits = ~(((unsigned long long)rem_hi << 32) | rem_lo);
       const int base = s_total_kept;
       const int room = max_keep - base;
       const int cnt = __popcll(keepbits);
@@ -299,7 +336,8 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
               int slot = kNmsCellCap;
               int cell = 0;
               if (finite4(bx)) {
-                cell = cell_y(0.5f * (bx.y + bx.w)) * kNmsGrid + cell_x(0.5f * (bx.x + bx.z));
+                const int l = nms_level(fmaxf(w * inv_x, hgt * inv_y));
+                cell = nms_level_base(l) + (cell_y(0.5f * (bx.y + bx.w)) >> l) * (kNmsGrid >> l) + (cell_x(0.5f * (bx.x + bx.z)) >> l);
                 slot = atomicAdd(&cell_count[cell], 1);
               }
               if (slot < kNmsCellCap)
@@ -318,6 +356,8 @@ __global__ void __launch_bounds__(1024, 1) nms_batched_kernel(const NmsParams p)
       }
     }
     __syncthreads();
+    PHASE_MARK(4)
+    if (blockIdx.x == 0 && tid == 0) PHASE_COUNT
     if (s_stop) break;
   }
   if (tid == 0) p.keep_counts[b] = s_total_kept;
@@ -359,12 +399,13 @@ static int launch_nms(NmsParams& p, const float* boxes, const float* scores, int
   p.brute = !(iou_threshold >= 0.f);
   p.win_scale = p.brute ? 0.f : (iou_threshold >= 0.5f ? 0.5f : (iou_threshold > 1e-3f ? 0.5f / iou_threshold - 0.5f : INFINITY)) * (1.f + 1.f / 64);
   if (!p.brute && !(iou_threshold > 1e-3f)) p.brute = 1;
+  p.size_ratio = p.brute ? 0.f : fminf(iou_threshold, 1.f) * (1.f - 1.f / 64);
   const size_t smem = region_a + (size_t)p.max_n * 16 + (((size_t)p.max_n * 2 + 15) & ~(size_t)15);
   int threads = cap / 2;
   if (threads < 128) threads = 128;
   if (threads > 1024) threads = 1024;
   static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem + 2048 > 48 * 1024 && smem > configured) {  // the 48 KB default limit counts the static part (~1.3 KB) too
     CVPCE_CUDA_OK(cudaFuncSetAttribute(nms_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
@@ -408,3 +449,15 @@ extern "C" int cvpce_nms_segments(const float* boxes, const float* scores, int s
   return launch_nms(p, boxes, scores, n_images, seg_stride, iou_threshold, min_score, max_keep, keep, keep_counts, box_scale,
                     kept_boxes, kept_scores, stream);
 }
+
+#ifdef CVPCE_PHASE_TIMERS
+extern "C" __attribute__((visibility("default"))) int cvpce_debug_nms_phases(long long* out8, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out8, cvpce::g_nms_phase, sizeof(long long) * 8);
+  if (reset) {
+    long long z[8] = {0};
+    cudaMemcpyToSymbol(cvpce::g_nms_phase, z, sizeof(z));
+  }
+  return 0;
+}
+#endif

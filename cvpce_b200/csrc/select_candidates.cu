@@ -281,7 +281,19 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_candidates_kernel(const
     }
     __syncthreads();
     if (!ordered_ties) {
-      stream_level(logits, n, p.prefilter, queue_x, queue_i, [&](int i, float x) {
+      // only scores >= the boundary bin's lower edge are collected: pre-filter on the logit of that edge (conservative
+      // margin >> the few-ulp error of det_sigmoid), so a dense head does not pay a second sigmoid per anchor
+      float collect_filter = p.prefilter;
+      if (width != 0) {
+        const float s_lo = __uint_as_float(lo + p.key_base);
+        if (s_lo > 0.f && s_lo < 1.f) {
+          const float x_lo = logf(s_lo / (1.f - s_lo));
+          collect_filter = fmaxf(collect_filter, x_lo - 1e-3f * fmaxf(1.f, fabsf(x_lo)));
+        } else if (s_lo >= 1.f) {
+          collect_filter = fmaxf(collect_filter, 8.f);  // sigmoid(x) rounds to 1 only for x > 16
+        }
+      }
+      stream_level(logits, n, collect_filter, queue_x, queue_i, [&](int i, float x) {
         uint32_t key;
         if (sel_key(x, p, key) && key >= lo) {
           const unsigned long long e = ((unsigned long long)(~key) << 32) | (unsigned)i;
@@ -317,21 +329,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_candidates_kernel(const
     while (cap < n_list) cap <<= 1;
     for (int i = n_list + tid; i < cap; i += kSelThreads) list[i] = ~0ull;
     __syncthreads();
-    for (int k = 2; k <= cap; k <<= 1) {
-      for (int j = k >> 1; j > 0; j >>= 1) {
-        for (int t = tid; t < (cap >> 1); t += kSelThreads) {
-          const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-          const int l = i | j;
-          const unsigned long long a = list[i], c = list[l];
-          const bool up = ((i & k) == 0);
-          if ((a > c) == up) {
-            list[i] = c;
-            list[l] = a;
-          }
-        }
-        __syncthreads();
-      }
-    }
+    block_bitonic_sort_u64(list, cap);
     n_sel = min(n_list, p.topk);
   }
 
