@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--cudnn-benchmark", action="store_true")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
+    ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
+                    "(800x1066 frame, 5 FPN levels) -> candidate selection -> NMS -> ... instead of scored candidate boxes")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-crops", type=int, default=32)
     return ap.parse_args()
@@ -228,10 +230,34 @@ def run_ours_shelves(args, world, rank, local):
     boxes_d = torch.from_numpy(boxes_h).to(device)
     scores_d = torch.from_numpy(scores_h).to(device)
     seg_d = torch.from_numpy(seg_h).to(device)
+    head_h = None
+    if args.from_head:
+        # head outputs whose decoded candidates are the same scored boxes (synth.head_from_candidates), kept as one
+        # concatenated tensor per output split into per-level views, like torchvision's RetinaNet does
+        from cvpce_b200 import synth
+        lgs, rgs = [], []
+        for i in range(n_shelves):
+            lg, rg, anc, scale = synth.head_from_candidates(boxes_h[seg_h[i]:seg_h[i + 1]], scores_h[seg_h[i]:seg_h[i + 1]],
+                                                            synth.SHELF_HW, 1000 + rank * n_shelves + i)
+            lgs.append(lg)
+            rgs.append(rg)
+        n_per = [a.shape[0] for a in anc]
+        head_h = (torch.from_numpy(np.stack(lgs)).pin_memory(), torch.from_numpy(np.stack(rgs)).pin_memory())
+        anchors_d = [torch.from_numpy(a).to(device) for a in anc]
+        frame_d = torch.tensor([list(synth.GLN_FRAME)] * n_shelves, dtype=torch.int32, device=device)
+        scale_d = torch.tensor([[float(scale[0]), float(scale[1])]] * n_shelves, dtype=torch.float32, device=device)
+        head_d = (head_h[0].to(device), head_h[1].to(device))
+
+    def run_step(imgs, cand=None, head=None):
+        if args.from_head:
+            lg, rg = head if head is not None else head_d
+            return hp.step_from_head(imgs, list(lg.split(n_per, dim=1)), list(rg.split(n_per, dim=1)), anchors_d, frame_d, scale_d)
+        b, sc, sg = cand if cand is not None else (boxes_d, scores_d, seg_d)
+        return hp.step(imgs, b, sc, sg, max_n)
 
     # -------- device-resident timing ("value")
     for _ in range(args.warmup):
-        out = hp.step(images, boxes_d, scores_d, seg_d, max_n)
+        out = run_step(images)
     K_crops = int(out["counts"].sum())
     hp.launches = 0
     hp.timer = pipeline.StageTimer()
@@ -240,7 +266,7 @@ def run_ours_shelves(args, world, rank, local):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        out = hp.step(images, boxes_d, scores_d, seg_d, max_n)
+        out = run_step(images)
     e1.record()
     barrier(world)
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
@@ -254,13 +280,17 @@ def run_ours_shelves(args, world, rank, local):
     # -------- end-to-end timing: pinned host inputs, H2D + D2H inside the timed region
     images_h = [im.cpu().pin_memory() for im in images]
     boxes_p, scores_p, seg_p = torch.from_numpy(boxes_h).pin_memory(), torch.from_numpy(scores_h).pin_memory(), torch.from_numpy(seg_h).pin_memory()
-    h2d = sum(im.numel() * 4 for im in images_h) + boxes_p.numel() * 4 + scores_p.numel() * 4 + seg_p.numel() * 4
+    h2d = sum(im.numel() * 4 for im in images_h)
+    h2d += (head_h[0].numel() + head_h[1].numel()) * 4 if args.from_head else (boxes_p.numel() + scores_p.numel() + seg_p.numel()) * 4
     del images
 
     def e2e_step():
         imgs = [im.to(device, non_blocking=True) for im in images_h]
-        o = hp.step(imgs, boxes_p.to(device, non_blocking=True), scores_p.to(device, non_blocking=True),
-                    seg_p.to(device, non_blocking=True), max_n)
+        if args.from_head:
+            o = run_step(imgs, head=(head_h[0].to(device, non_blocking=True), head_h[1].to(device, non_blocking=True)))
+        else:
+            o = run_step(imgs, cand=(boxes_p.to(device, non_blocking=True), scores_p.to(device, non_blocking=True),
+                                     seg_p.to(device, non_blocking=True)))
         idx = o["topk_idx"].cpu()
         bx = o["boxes"].cpu()
         return idx, bx
@@ -313,8 +343,9 @@ def run_ours_shelves(args, world, rank, local):
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.trunk == "f32" else "bf16", "data": "synthetic",
-        "config": {"workload": "%s: %d shelves 2048x1536 x ~%d products per GPU -> NMS(0.5, top200) -> 256x256 crops -> VGG16(random init)+MAC"
-                               " -> cosine top-%d vs %d x 1024 gallery" % (args.workload, n_shelves, args.products, args.k, G),
+        "config": {"workload": ("%s: %d shelves 2048x1536 x ~%d products per GPU -> " + ("GLN head outputs (800x1066, 160956 anchors) -> "
+                                "sigmoid/top-1000/decode -> " if args.from_head else "") + "NMS(0.5, top200) -> 256x256 crops -> "
+                                "VGG16(random init)+MAC -> cosine top-%d vs %d x 1024 gallery") % (args.workload, n_shelves, args.products, args.k, G),
                    "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16, not rebuilt (%s%s%s, tf32 convs %s)" % (
                        args.trunk, ", channels_last" if args.channels_last else "",
                        "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32),

@@ -80,13 +80,34 @@ class HotPath:
             keep, counts, kept_boxes, _ = ops.nms_batched(cand_boxes, cand_scores, seg_offsets, max_n, self.iou_threshold,
                                                           self.min_score, self.detections_per_img, want_boxes=True)
         self.launches += 1
+        return self._classify_kept(images, counts, kept_boxes, seg_offsets[:-1].to(torch.int64))
+
+    @torch.no_grad()
+    def step_from_head(self, images, cls_logits, bbox_regression, anchors, frame_sizes, box_scale, score_thresh=0.05,
+                       topk_candidates=1000):
+        """The same step starting one stage earlier: the detector head's per-level outputs of the batch
+        (tv:retinanet.py:508-571) -> candidate selection -> NMS over its fixed-stride segments, boxes rescaled to the
+        original images by box_scale f32[B,2] (tv:transform.py:306-319) -> crops -> ... as in step()."""
+        B = len(images)
+        n_anchors = sum(int(l.shape[1]) for l in cls_logits)
+        with self.timer.span("select_candidates", 4.0 * n_anchors * B):
+            cb, cs, _, seg_counts, _, stride = ops.select_candidates(cls_logits, bbox_regression, anchors, frame_sizes,
+                                                                     score_thresh, topk_candidates, want_labels=False)
+        with self.timer.span("nms", 20.0 * B * stride):
+            _, counts, kept_boxes, _ = ops.nms_segments(cb, cs, stride, seg_counts, self.iou_threshold, self.min_score,
+                                                        self.detections_per_img, box_scale=box_scale, want_boxes=True)
+        self.launches += 2
+        return self._classify_kept(images, counts, kept_boxes, torch.arange(B, device=cb.device, dtype=torch.int64) * stride)
+
+    def _classify_kept(self, images, counts, kept_boxes, seg_begin):
+        B = len(images)
         counts_h = counts.cpu()  # the one host synchronisation of the step
         K = int(counts_h.sum())
-        dev = cand_boxes.device
+        dev = kept_boxes.device
         counts64 = counts.to(torch.int64)
         image_idx = torch.repeat_interleave(torch.arange(B, device=dev), counts64, output_size=K)
         first = torch.cumsum(counts64, 0) - counts64
-        pos = seg_offsets[:-1].to(torch.int64)[image_idx] + (torch.arange(K, device=dev) - first[image_idx])
+        pos = seg_begin[image_idx] + (torch.arange(K, device=dev) - first[image_idx])
         boxes = kept_boxes[pos]
         table = ops.make_image_table(images)
         S = self.size

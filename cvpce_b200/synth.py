@@ -241,3 +241,48 @@ def head_case(name):
         logits.append(lg)
         regression.append(rg)
     return logits, regression, anchors, sizes, C, topk
+
+
+GLN_FRAME = (800, 1066)  # tv GeneralizedRCNNTransform(min_size=800, max_size=1333) applied to a 1536 x 2048 shelf
+
+
+def head_from_candidates(boxes, scores, image_hw, seed, frame=GLN_FRAME, background=(-6.0, 1.0)):
+    """Head outputs of a 'trained' detector whose decoded, thresholded candidates are (up to fp32 rounding) the given scored
+    boxes: every candidate is encoded (BoxCoder.encode_single, weights 1) against the best-shaped free anchor at its
+    centre cell of the FPN level matching its size, with logit = logit(score); every other anchor gets a background logit
+    N(background).  boxes are in original-image pixels (image_hw); the head works in the resized `frame`.
+    Returns (logits f32 [A,1], regression f32 [A,4], anchors per level, box_scale (x ratio, y ratio) back to the image)."""
+    H, W = image_hw
+    fh, fw = frame
+    sx, sy = fw / W, fh / H
+    anchors = fpn_anchors(fh, fw)
+    n_per = [a.shape[0] for a in anchors]
+    off = np.concatenate([[0], np.cumsum(n_per)])
+    rs = np.random.RandomState(seed)
+    A = int(off[-1])
+    logits = (background[0] + background[1] * rs.standard_normal(A)).astype(np.float32)
+    regression = (0.1 * rs.standard_normal((A, 4))).astype(np.float32)
+    used = set()
+    b = np.asarray(boxes, dtype=np.float64) * [sx, sy, sx, sy]
+    for (x1, y1, x2, y2), s in zip(b, np.asarray(scores, dtype=np.float64)):
+        w, h = max(x2 - x1, 1e-3), max(y2 - y1, 1e-3)
+        cx, cy = x1 + 0.5 * w, y1 + 0.5 * h
+        lvl = int(np.argmin([abs(np.log(np.sqrt(w * h) / (sz * 2 ** (1 / 3)))) for sz in FPN_SIZES]))
+        stride = FPN_STRIDES[lvl]
+        gw = -(-fw // stride)
+        gh = -(-fh // stride)
+        ix, iy = min(gw - 1, max(0, int(round(cx / stride)))), min(gh - 1, max(0, int(round(cy / stride))))
+        base = int(off[lvl]) + (iy * gw + ix) * 9
+        cand = anchors[lvl][(iy * gw + ix) * 9:(iy * gw + ix) * 9 + 9].astype(np.float64)
+        aw, ah = cand[:, 2] - cand[:, 0], cand[:, 3] - cand[:, 1]
+        order = np.argsort(np.abs(np.log(w / aw)) + np.abs(np.log(h / ah)))
+        slot = next((int(o) for o in order if base + int(o) not in used), None)
+        if slot is None:
+            continue  # all 9 anchors of the cell taken: drop this duplicate
+        used.add(base + slot)
+        ax1, ay1 = cand[slot, 0], cand[slot, 1]
+        acx, acy = ax1 + 0.5 * aw[slot], ay1 + 0.5 * ah[slot]
+        regression[base + slot] = [(cx - acx) / aw[slot], (cy - acy) / ah[slot], np.log(w / aw[slot]), np.log(h / ah[slot])]
+        s = min(max(s, 1e-6), 1 - 1e-6)
+        logits[base + slot] = np.log(s / (1 - s))
+    return logits.reshape(A, 1), regression, anchors, (np.float32(W / fw), np.float32(H / fh))

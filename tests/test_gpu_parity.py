@@ -525,3 +525,35 @@ def test_nms_grid_window_adversarial_geometry(ops, thr):
     want = oracle.nms(boxes, scores, thr)
     got = ops.nms(dev(boxes), dev(scores), thr).cpu().numpy()
     assert np.array_equal(got, want), (thr, len(got), len(want))
+
+
+def test_hot_path_from_head_matches_hot_path_from_boxes(ops):
+    """HotPath.step_from_head (f1 -> a1 -> ...) on head outputs that encode a shelf's scored candidates gives the same kept
+    boxes (to fp32 box-coder rounding) and the same matches as HotPath.step on the candidates themselves."""
+    from cvpce_b200 import classification, pipeline
+    torch.backends.cudnn.allow_tf32 = False
+    H, W = 384, 512
+    frame = (300, 400)
+    img = dev(synth.shelf_image(3, H, W))
+    boxes, scores = synth.shelf_candidates(3, H, W, n_products=12)
+    boxes = np.clip(boxes, 0, [W, H, W, H]).astype(np.float32)
+    lg, rg, anc, scale = synth.head_from_candidates(boxes, scores, (H, W), 5, frame=frame)
+    n_per = [a.shape[0] for a in anc]
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda()
+    gallery = dev(synth.unit_rows(np.random.RandomState(2), 300, 1024))
+    hp = pipeline.HotPath(enc, gallery, k=1, size=64, trunk_batch=8, detections_per_img=200, min_score=0.3)
+    seg = dev(np.array([0, len(scores)], dtype=np.int32))
+    a = hp.step([img], dev(boxes), dev(scores), seg, len(scores))
+    b = hp.step_from_head([img], list(dev(lg)[None].split(n_per, 1)), list(dev(rg)[None].split(n_per, 1)), [dev(x) for x in anc],
+                          [frame], dev(np.array([scale], dtype=np.float32)))
+    assert int(a["counts"][0]) == int(b["counts"][0]) > 0
+    np.testing.assert_allclose(b["boxes"].cpu().numpy(), a["boxes"].cpu().numpy(), atol=2e-2)
+    # oracle for the head path itself: selection + NMS + rescale
+    L = [lg[None, o:o + n] for o, n in zip(np.cumsum([0] + n_per[:-1]), n_per)]
+    R = [rg[None, o:o + n] for o, n in zip(np.cumsum([0] + n_per[:-1]), n_per)]
+    wb, ws, _ = oracle.postprocess_detections(L, R, anc, [frame], 0.05, 1000, 0.5, 200)[0]
+    wb = wb[ws > np.float32(0.3)] * np.array([scale[0], scale[1], scale[0], scale[1]], dtype=np.float32)
+    assert np.array_equal(b["boxes"].cpu().numpy(), wb)
+    agree = (a["topk_idx"] == b["topk_idx"]).float().mean().item()
+    assert agree >= 0.9, agree
