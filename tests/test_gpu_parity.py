@@ -557,3 +557,21 @@ def test_hot_path_from_head_matches_hot_path_from_boxes(ops):
     assert np.array_equal(b["boxes"].cpu().numpy(), wb)
     agree = (a["topk_idx"] == b["topk_idx"]).float().mean().item()
     assert agree >= 0.9, agree
+
+
+def test_macresnet_mirror_matches_reference_embeddings(ops, golden):
+    """f4: MACResNet (classification.py:53-85) over a seeded random-init resnet50, descriptor layers (2, 3) -> 1536-d."""
+    from torchvision.models import resnet
+    from cvpce_b200 import classification
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(synth.WEIGHT_SEED + 1)
+    enc = classification.MACResNet(resnet.resnet50(weights=None), (2, 3)).eval().requires_grad_(False)
+    probe = enc.blocks[0][0][0].weight.reshape(-1)[:8].numpy()
+    if not np.allclose(probe, golden["mac"]["macresnet_weight_probe"], atol=1e-7):
+        pytest.skip("seeded resnet50 init differs from the authoring container's torch build")
+    enc = enc.cuda()
+    with torch.no_grad():
+        emb = enc(dev(synth.encoder_inputs())).cpu().numpy()
+    assert emb.shape == (4, 1536)
+    np.testing.assert_allclose(emb, golden["mac"]["macresnet_embeddings"], rtol=1e-3, atol=1e-5)
