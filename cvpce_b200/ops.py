@@ -177,6 +177,27 @@ def batched_nms(boxes, scores, idxs, iou_threshold):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# 2x2 max pooling between the trunk's convolutions  (tv:models/vgg.py make_layers 'M'; classification.py:31-37)
+# ---------------------------------------------------------------------------------------------------------------------
+def maxpool2x2_supported(x):
+    per16 = 4 if x.dtype == torch.float32 else 8
+    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16) and x.shape[1] % per16 == 0
+            and x.shape[2] >= 2 and x.shape[3] >= 2 and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def maxpool2x2(x):
+    """nn.MaxPool2d(kernel_size=2, stride=2) on a channels_last CUDA tensor [B,C,H,W] -> channels_last [B,C,H//2,W//2]."""
+    _need_cuda("maxpool2x2", x)
+    if not maxpool2x2_supported(x):
+        raise RuntimeError("maxpool2x2: needs a channels_last float32/bfloat16 CUDA tensor with 16-byte channel groups")
+    B, C, H, W = x.shape
+    out = torch.empty((B, C, H // 2, W // 2), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    rc = _lib.load().cvpce_maxpool2x2_nhwc(_ptr(x), F32 if x.dtype == torch.float32 else BF16, B, H, W, C, _ptr(out), _stream())
+    _lib.check(rc, "cvpce_maxpool2x2_nhwc")
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # crop + pad + resize  (cvpce/production.py:20, cvpce/datautils.py:234-239, utils.py:280-281, classification.py:41-44)
 # ---------------------------------------------------------------------------------------------------------------------
 def make_image_table(images):

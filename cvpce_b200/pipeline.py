@@ -121,6 +121,9 @@ class HotPath:
         D = self.encoder.embedding_size
         emb = torch.empty((K, D), dtype=torch.float32, device=dev)
         regions = None
+        own0 = getattr(self.encoder, "own_launches", 0)
+        if hasattr(self.encoder, "stage_timer"):
+            self.encoder.stage_timer = None if isinstance(self.timer, _NoTimer) else self.timer
         for i in range(0, K, self.trunk_batch):
             f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True)
             if self.rmac_levels and regions is None:
@@ -130,6 +133,7 @@ class HotPath:
             with self.timer.span("region_pool_embed", nb):
                 ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=bool(self.rmac_levels), out=emb[i:i + self.trunk_batch])
             self.launches += 1
+        self.launches += getattr(self.encoder, "own_launches", 0) - own0  # the library's max-pool launches inside the trunk
         G = self.gallery.G
         k = min(self.k, G)
         with self.timer.span("rows_prepare", 6.0 * K * D):

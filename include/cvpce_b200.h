@@ -183,6 +183,16 @@ CVPCE_API int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, int
 CVPCE_API int cvpce_l2norm_rows(float* x, int B, int D, int64_t stride, float eps, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * a7 (driving the torch trunk)  2x2 / stride-2 max pooling of a channels-last feature map.
+ * Replaces: nn.MaxPool2d(kernel_size=2, stride=2) between the convolutions of the VGG16 trunk (tv:models/vgg.py make_layers,
+ *           cfg 'D' entries 'M'; reached from cvpce/models/classification.py:31-37 MACVGG.block1 / block2).  The convolutions
+ *           themselves stay torch/cuDNN; at::max_pool_forward_nhwc was 28 % of the step's GPU time.
+ * in  [B,H,W,C] dense NHWC (a torch channels_last tensor's memory), f32 or bf16, 16-byte aligned, C*elemsize % 16 == 0;
+ * out [B,H/2,W/2,C] dense NHWC, floor mode, no padding.  Bit-exact max; a NaN in the window propagates (as at::max_pool2d).
+ */
+CVPCE_API int cvpce_maxpool2x2_nhwc(const void* in, int dtype, int B, int H, int W, int C, void* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * a10 + a11  Cosine similarity + per-row top-k.
  * Replaces: cvpce/models/classification.py:87-95  distance() = 1 - cosine_similarity and nearest_neighbors()
  *           (gather [Q,G,D] x2, reduce, full argsort, [:, :k]).

@@ -575,3 +575,37 @@ def test_macresnet_mirror_matches_reference_embeddings(ops, golden):
         emb = enc(dev(synth.encoder_inputs())).cpu().numpy()
     assert emb.shape == (4, 1536)
     np.testing.assert_allclose(emb, golden["mac"]["macresnet_embeddings"], rtol=1e-3, atol=1e-5)
+
+
+@pytest.mark.parametrize("shape", [(3, 64, 32, 32), (2, 128, 17, 23), (1, 512, 2, 2), (5, 8, 6, 4)])
+def test_maxpool2x2_nhwc_equals_torch(ops, shape):
+    """a7 driving: the trunk's nn.MaxPool2d(2, 2) on channels-last maps -- bit-exact, NaN propagating, f32 and bf16."""
+    g = torch.Generator(device="cuda").manual_seed(shape[1])
+    x = torch.randn(shape, device="cuda", generator=g)
+    x[0, 1, 0, 1] = float("nan")
+    x[-1, -1, -1, -1] = float("-inf")
+    for dt in (torch.float32, torch.bfloat16):
+        xc = x.to(dt).contiguous(memory_format=torch.channels_last)
+        if not ops.maxpool2x2_supported(xc):
+            assert dt == torch.float32 or shape[1] % 8
+            continue
+        got = ops.maxpool2x2(xc)
+        want = torch.nn.functional.max_pool2d(xc, 2, 2)
+        assert got.shape == want.shape and got.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(torch.nan_to_num(got.float(), nan=12345.0), torch.nan_to_num(want.float(), nan=12345.0))
+    with pytest.raises(RuntimeError):
+        ops.maxpool2x2(x)  # NCHW-contiguous input is rejected (the caller keeps torch's module for it)
+
+
+def test_fast_trunk_features_equal_plain_trunk(ops):
+    from cvpce_b200 import classification
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda()
+    x = dev(synth.encoder_inputs())
+    with torch.no_grad():
+        p4, p5 = enc.features(x)
+        enc.enable_fast_trunk()
+        f4, f5 = enc.features(x)
+    np.testing.assert_allclose(f4.cpu().numpy(), p4.cpu().numpy(), rtol=1e-3, atol=1e-5)
+    np.testing.assert_allclose(f5.cpu().numpy(), p5.cpu().numpy(), rtol=1e-3, atol=1e-5)

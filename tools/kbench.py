@@ -124,6 +124,19 @@ def bench_select(args):
             report("postprocess (select+nms) B=%d %s" % (B, tag), ms, best, nbytes + 20.0 * ncand)
 
 
+def bench_maxpool(args):
+    """The four 2x2 max-pools of the VGG16 trunk for one 128-crop trunk batch, ours vs at::max_pool2d (channels-last)."""
+    dev = "cuda"
+    B = 128
+    for C, S in ((64, 256), (128, 128), (256, 64), (512, 32)):
+        x = torch.randn((B, C, S, S), device=dev).contiguous(memory_format=torch.channels_last)
+        nb = 1.25 * x.numel() * 4
+        ms, best = timeit(lambda: ops.maxpool2x2(x), args.iters)
+        report("maxpool2x2 nhwc f32 B=%d C=%d %dx%d" % (B, C, S, S), ms, best, nb)
+        ms, best = timeit(lambda: torch.nn.functional.max_pool2d(x, 2, 2), args.iters)
+        report("  torch max_pool2d (at::max_pool_forward_nhwc) same shape", ms, best, nb)
+
+
 def bench_crop(args):
     dev = "cuda"
     H, W = synth.SHELF_HW
@@ -206,7 +219,7 @@ def main():
     args = ap.parse_args()
     torch.cuda.set_device(0)
     for w in args.which:
-        {"nms": bench_nms, "select": bench_select, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
+        {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
 
 
 if __name__ == "__main__":

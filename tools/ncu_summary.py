@@ -3,6 +3,7 @@
 
     python tools/ncu_summary.py launches gpurun_out/<tag>/launches.csv  > profiles/<name>_launches.txt
     python tools/ncu_summary.py full     gpurun_out/<tag>/prof.ncu-rep  > profiles/<name>_ncu_full.txt
+    python tools/ncu_summary.py traffic  gpurun_out/<tag>/prof.ncu-rep gpurun_out/<tag>/plain.log > profiles/ncu_traffic.json
 """
 import collections
 import csv
@@ -73,5 +74,41 @@ def full(path):
     print("\n# launches captured per kernel: " + ", ".join("%s x%d" % kv for kv in seen.items()))
 
 
+STAGE_OF = {"region_pool_kernel": "region_pool_embed", "crop_resize_sep_kernel": "crop_resize", "crop_resize_kernel": "crop_resize",
+            "nms_batched_kernel": "nms", "select_candidates_kernel": "select_candidates", "rows_prepare_kernel": "rows_prepare",
+            "sim_topk_tc_kernel": "sim_topk"}
+
+
+def traffic(path, bench_log):
+    """profiles/ncu_traffic.json: DRAM bytes per launch (median over the captured launches) of each of our kernels, next to
+    the algorithmic bytes per launch the profiled bench.py run itself reported (bench.py matches on those)."""
+    import json
+    import statistics
+    line = [ln for ln in open(bench_log) if ln.startswith("{")][-1]
+    kernels = json.loads(line)["kernels"]
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = collections.defaultdict(list)
+    for d in data:
+        short = re.sub(r"[(<].*", "", re.sub(r"^void ", "", d[idx["Kernel Name"]])).replace("cvpce::", "")
+        stage = STAGE_OF.get(short)
+        if not stage:
+            continue
+        b = 0.0
+        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            b += float(d[idx[m]].replace(",", "")) * scale[units[idx[m]]]
+        per[stage].append(b)
+    res = {}
+    for stage, v in per.items():
+        if stage in kernels and "algorithmic_bytes_per_launch" in kernels[stage]:
+            res[stage] = {"dram_bytes_per_launch": statistics.median(v), "launches_captured": len(v),
+                          "algorithmic_bytes_per_launch": kernels[stage]["algorithmic_bytes_per_launch"],
+                          "source": "ncu --set full --clock-control none, %s" % path}
+    print(json.dumps(res, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
