@@ -49,6 +49,8 @@ def parse():
                     "instead of channels-last + torch.cudnn_convolution_relu")
     ap.add_argument("--trunk-batch", type=int, default=128)
     ap.add_argument("--cudnn-benchmark", action="store_true")
+    ap.add_argument("--strict-fp32", action="store_true", help="torch.backends.cudnn.allow_tf32 = False for the torch trunk (the default "
+                    "is torch's own GPU default, TF32 convolutions: tools/tf32_check.py measures what that costs in accuracy)")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
@@ -484,6 +486,9 @@ def main():
         sys.exit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     world, rank, local = dist_setup(args)
     torch.backends.cudnn.benchmark = bool(args.cudnn_benchmark)
+    if args.strict_fp32:
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
     if args.workload == "c5":
         line = run_ours_c5(args, world, rank, local)
     else:

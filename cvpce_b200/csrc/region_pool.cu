@@ -446,6 +446,116 @@ __global__ void __launch_bounds__(kPoolThreads, GENERAL ? (NHWC_ONLY ? 3 : 2) : 
   cluster.sync();
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// MAC over dense channels-last maps (what the fast trunk produces; the reference's mode): PIXEL-split across the cluster.
+// The channel-split kernel above reads, per CTA, a 256-byte channel slab of every pixel (2 KB apart): 65-70 % of HBM.
+// Here CTA r of the 8-CTA cluster streams the r-th eighth of each map's pixels -- one contiguous block of memory, 128-bit
+// loads, 8 in flight per thread, a thread always sees the same 16-byte channel group so its running maxima stay in
+// registers (no shared-memory atomics) -- and the per-CTA maxima are max-reduced across the cluster through distributed
+// shared memory; the channel slab r of the descriptor is then finished (sum of squares all-reduce, scale, store) by CTA r.
+// Requirements (host-checked): whole-map regions, no per-region L2, sc == 1, sw == C, sh == W*C, 16-byte aligned images,
+// C*elemsize/16 divides 256.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kMacMaxCols = 4096;  // sum of C over the maps
+
+template <bool BF16>
+__global__ void __launch_bounds__(kPoolThreads) mac_nhwc_pixelsplit_kernel(const PoolParams p) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned crank = cluster.block_rank(), csize = cluster.num_blocks();
+  const int n = blockIdx.x / kPoolCluster;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int E = BF16 ? 8 : 4;  // elements per 16-byte vector
+  __shared__ float pmax[kMacMaxCols];          // this CTA's maxima over its pixels, every channel of every map
+  __shared__ float red[kPoolThreads * E];
+  __shared__ float own[kMacMaxCols / kPoolCluster];  // finished maxima of this CTA's channel slab
+  __shared__ float wsum[kPoolWarps];
+  __shared__ float fpart;
+
+  int col = 0;
+  for (int m = 0; m < p.n_maps; ++m) {
+    const PoolMap& mp = p.maps[m];
+    const int V = mp.C / E;
+    const int npix = mp.H * mp.W;
+    const int lo = (int)((long long)npix * crank / csize), hi = (int)((long long)npix * (crank + 1) / csize);
+    const uint4* base = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(mp.data) + (size_t)n * mp.sn * (BF16 ? 2 : 4)) +
+                        (size_t)lo * V;
+    const int total = (hi - lo) * V;
+    float acc[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) acc[e] = -INFINITY;
+#pragma unroll 8
+    for (int i = tid; i < total; i += kPoolThreads) {
+      const uint4 x = ldg_stream_u4(base + i);
+      if (BF16) {
+        acc[0] = fmaxf(acc[0], bf16lo(x.x)); acc[1] = fmaxf(acc[1], bf16hi(x.x));
+        acc[2] = fmaxf(acc[2], bf16lo(x.y)); acc[3] = fmaxf(acc[3], bf16hi(x.y));
+        acc[4 % E] = fmaxf(acc[4 % E], bf16lo(x.z)); acc[5 % E] = fmaxf(acc[5 % E], bf16hi(x.z));
+        acc[6 % E] = fmaxf(acc[6 % E], bf16lo(x.w)); acc[7 % E] = fmaxf(acc[7 % E], bf16hi(x.w));
+      } else {
+        acc[0] = fmaxf(acc[0], __uint_as_float(x.x)); acc[1] = fmaxf(acc[1], __uint_as_float(x.y));
+        acc[2] = fmaxf(acc[2], __uint_as_float(x.z)); acc[3] = fmaxf(acc[3], __uint_as_float(x.w));
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) red[tid * E + e] = acc[e];
+    __syncthreads();
+    if (tid < V) {  // threads tid, tid+V, tid+2V, .. saw the same channel group (V divides the block size)
+      for (int g = tid + V; g < kPoolThreads; g += V) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] = fmaxf(acc[e], red[g * E + e]);
+      }
+#pragma unroll
+      for (int e = 0; e < E; ++e) pmax[col + tid * E + e] = acc[e];
+    }
+    __syncthreads();
+    col += mp.C;
+  }
+  cluster.sync();
+  // channel slab `crank` of every map: max over the cluster, then the descriptor's L2 norm over all channels
+  float sq = 0.f;
+  int ocol = 0, mcol = 0;
+  for (int m = 0; m < p.n_maps; ++m) {
+    const PoolMap& mp = p.maps[m];
+    const int c_lo = (int)crank * mp.slab;
+    const int nch = max(0, min(mp.slab, mp.C - c_lo));
+    for (int c = tid; c < nch; c += kPoolThreads) {
+      float v = -INFINITY;
+      for (unsigned rk = 0; rk < csize; ++rk) v = fmaxf(v, cluster.map_shared_rank(pmax, rk)[mcol + c_lo + c]);
+      own[ocol + c] = v;
+      sq = fmaf(v, v, sq);
+    }
+    ocol += mp.slab;
+    mcol += mp.C;
+  }
+  float denom = 1.f;
+  if (p.final_l2) {
+    sq = warp_sum(sq);
+    if (lane == 0) wsum[warp] = sq;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int w = 0; w < kPoolWarps; ++w) t += wsum[w];
+      fpart = t;
+    }
+    cluster.sync();
+    float tot = 0.f;
+    for (unsigned rk = 0; rk < csize; ++rk) tot += *cluster.map_shared_rank(&fpart, rk);
+    denom = fmaxf(sqrtf(tot), p.eps);
+  } else {
+    __syncthreads();
+  }
+  ocol = 0;
+  for (int m = 0; m < p.n_maps; ++m) {
+    const PoolMap& mp = p.maps[m];
+    const int c_lo = (int)crank * mp.slab;
+    const int nch = max(0, min(mp.slab, mp.C - c_lo));
+    float* orow = p.out + (long long)n * p.out_stride + mp.out_offset + c_lo;
+    for (int c = tid; c < nch; c += kPoolThreads) orow[c] = p.final_l2 ? own[ocol + c] / denom : own[ocol + c];
+    ocol += mp.slab;
+  }
+  cluster.sync();  // peers may still be reading pmax / fpart
+}
+
 __global__ void __launch_bounds__(256) l2norm_rows_kernel(float* x, int B, int D, long long stride, float eps) {
   __shared__ float wsum[8];
   __shared__ float s_denom;
@@ -612,8 +722,22 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   const bool general = !all_whole || per_region_l2;
   bool all_nhwc = true;
   for (int m = 0; m < n_maps; ++m) all_nhwc = all_nhwc && p.maps[m].nhwc;
+  // dense channels-last MAC: the pixel-split streaming kernel
+  bool pixsplit = !general && col <= kMacMaxCols;
+  for (int m = 0; m < n_maps && pixsplit; ++m) {
+    const cvpce_feature_map& fm = maps[m];
+    const int E = dtype == CVPCE_F32 ? 4 : 8;
+    const int V = fm.C / E;
+    pixsplit = fm.C % E == 0 && V >= 1 && V <= kPoolThreads && kPoolThreads % V == 0 && fm.stride_c == 1 && fm.stride_w == fm.C &&
+               fm.stride_h == (int64_t)fm.W * fm.C && fm.stride_n % E == 0 && (reinterpret_cast<uintptr_t>(fm.data) & 15u) == 0 &&
+               p.maps[m].slab * kPoolCluster == fm.C;
+  }
   void (*kern)(PoolParams);
-  if (dtype == CVPCE_F32) {
+  size_t smem_launch = smem;
+  if (pixsplit) {
+    kern = dtype == CVPCE_F32 ? mac_nhwc_pixelsplit_kernel<false> : mac_nhwc_pixelsplit_kernel<true>;
+    smem_launch = 0;
+  } else if (dtype == CVPCE_F32) {
     kern = all_nhwc ? (general ? region_pool_kernel<CVPCE_F32, true, true> : region_pool_kernel<CVPCE_F32, false, true>)
                     : (general ? region_pool_kernel<CVPCE_F32, true, false> : region_pool_kernel<CVPCE_F32, false, false>);
   } else {
@@ -621,11 +745,11 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
                     : (general ? region_pool_kernel<CVPCE_BF16, true, false> : region_pool_kernel<CVPCE_BF16, false, false>);
   }
   // the default 48 KB limit covers static + dynamic shared memory: opt in with a margin for the static part
-  if (smem > 40 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem_launch > 40 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_launch));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(B * kPoolCluster));
   cfg.blockDim = dim3(kPoolThreads);
-  cfg.dynamicSmemBytes = smem;
+  cfg.dynamicSmemBytes = smem_launch;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;

@@ -609,3 +609,24 @@ def test_fast_trunk_features_equal_plain_trunk(ops):
         f4, f5 = enc.features(x)
     np.testing.assert_allclose(f4.cpu().numpy(), p4.cpu().numpy(), rtol=1e-3, atol=1e-5)
     np.testing.assert_allclose(f5.cpu().numpy(), p5.cpu().numpy(), rtol=1e-3, atol=1e-5)
+
+
+@pytest.mark.parametrize("shapes", [[(512, 32, 32), (512, 16, 16)], [(512, 7, 5), (1024, 4, 3)], [(64, 9, 9), (128, 3, 3), (256, 1, 2)],
+                                    [(4, 2, 2)], [(1024, 16, 16)]])
+def test_mac_channels_last_pixel_split_kernel(ops, shapes):
+    """Dense channels-last MAC (the fast trunk's layout) goes through the pixel-split cluster kernel: odd pixel counts, 1..3
+    maps, VGG / ResNet channel counts, f32 and bf16, with and without the final L2."""
+    rs = np.random.RandomState(len(shapes) * 7 + shapes[0][0])
+    B = 5
+    feats = [rs.randn(B, c, h, w).astype(np.float32) for c, h, w in shapes]
+    for final in (True, False):
+        want = oracle.region_pool_embed(feats, final_l2=final)
+        dv = [dev(f).contiguous(memory_format=torch.channels_last) for f in feats]
+        got = ops.region_pool_embed(dv, final_l2=final).cpu().numpy()
+        if final:
+            np.testing.assert_allclose(got, want, rtol=2e-6, atol=1e-7)
+        else:
+            assert np.array_equal(got, want)
+        bf = [d.bfloat16() for d in dv]
+        want_bf = oracle.region_pool_embed([b.float().cpu().numpy() for b in bf], final_l2=final)
+        np.testing.assert_allclose(ops.region_pool_embed(bf, final_l2=final).cpu().numpy(), want_bf, rtol=2e-6, atol=1e-7)
