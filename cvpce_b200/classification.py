@@ -80,20 +80,28 @@ class MACVGG(nn.Module):
                 i += 1
         return x
 
-    def features(self, x, normalized=False):
+    def features(self, x, normalized=False, pooled_f4=False):
+        """(relu4_3, relu5_3) maps.  pooled_f4=True (fast trunk only): return pool4(relu4_3) in place of relu4_3 when the map
+        has even sides -- the 2x2 windows then tile it exactly, so the max over the pooled map IS the max over the map
+        (bit for bit) and the MAC kernel reads a quarter of the bytes of a tensor the trunk produces anyway."""
         if not normalized:
             x = (x - self._mean.to(x.dtype)) / self._std.to(x.dtype)
         if self.fast_trunk and x.is_cuda:
             x = x.contiguous(memory_format=torch.channels_last)
             f4 = self._run_fused(self.block1, x)
-            f5 = self._run_fused(self.block2, f4)
+            b2 = list(self.block2)
+            if (pooled_f4 and isinstance(b2[0], nn.MaxPool2d) and b2[0].kernel_size in (2, (2, 2)) and b2[0].stride in (2, (2, 2))
+                    and b2[0].padding in (0, (0, 0)) and not b2[0].ceil_mode and f4.shape[2] % 2 == 0 and f4.shape[3] % 2 == 0):
+                p4 = self._run_fused(b2[:1], f4)
+                return p4, self._run_fused(b2[1:], p4)
+            f5 = self._run_fused(b2, f4)
             return f4, f5
         f4 = self.block1(x)
         f5 = self.block2(f4)
         return f4, f5
 
     def forward(self, x, eps=1e-8, normalized=False):
-        f4, f5 = self.features(x, normalized)
+        f4, f5 = self.features(x, normalized, pooled_f4=self.regions_levels == 0)
         if f4.dtype not in (torch.float32, torch.bfloat16):
             f4, f5 = f4.float(), f5.float()
         if self.regions_levels > 0:

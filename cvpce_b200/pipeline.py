@@ -125,7 +125,7 @@ class HotPath:
         if hasattr(self.encoder, "stage_timer"):
             self.encoder.stage_timer = None if isinstance(self.timer, _NoTimer) else self.timer
         for i in range(0, K, self.trunk_batch):
-            f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True)
+            f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True, pooled_f4=not self.rmac_levels)
             if self.rmac_levels and regions is None:
                 regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.rmac_levels) for f in (f4, f5)]
             esz = f4.element_size()

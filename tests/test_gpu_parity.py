@@ -630,3 +630,18 @@ def test_mac_channels_last_pixel_split_kernel(ops, shapes):
         bf = [d.bfloat16() for d in dv]
         want_bf = oracle.region_pool_embed([b.float().cpu().numpy() for b in bf], final_l2=final)
         np.testing.assert_allclose(ops.region_pool_embed(bf, final_l2=final).cpu().numpy(), want_bf, rtol=2e-6, atol=1e-7)
+
+
+def test_mac_of_pooled_relu4_3_is_bit_identical(ops):
+    """MACVGG.features(pooled_f4=True): max over pool4(relu4_3) == max over relu4_3 when the map has even sides."""
+    from cvpce_b200 import classification
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda().enable_fast_trunk()
+    x = dev(synth.encoder_inputs())
+    with torch.no_grad():
+        f4, f5 = enc.features(x)
+        p4, q5 = enc.features(x, pooled_f4=True)
+        assert p4.shape[2] * 2 == f4.shape[2] and torch.equal(f5, q5)
+        assert torch.equal(ops.region_pool_embed([f4, f5]), ops.region_pool_embed([p4, q5]))
+        odd = enc.features(x[:, :, :40, :40], pooled_f4=True)[0]      # relu4_3 is 5x5: not tiled by 2x2 windows -> unchanged
+        assert odd.shape[2] == 5
