@@ -47,7 +47,8 @@ def parse():
     ap.add_argument("--channels-last", action="store_true")
     ap.add_argument("--plain-trunk", action="store_true", help="call the torch trunk module by module in NCHW (the reference's way) "
                     "instead of channels-last + torch.cudnn_convolution_relu")
-    ap.add_argument("--trunk-batch", type=int, default=128)
+    ap.add_argument("--trunk-batch", type=int, default=256)
+    ap.add_argument("--streams", type=int, default=1, help="CUDA streams the trunk batches alternate between")
     ap.add_argument("--cudnn-benchmark", action="store_true")
     ap.add_argument("--strict-fp32", action="store_true", help="torch.backends.cudnn.allow_tf32 = False for the torch trunk (the default "
                     "is torch's own GPU default, TF32 convolutions: tools/tf32_check.py measures what that costs in accuracy)")
@@ -221,7 +222,8 @@ def run_ours_shelves(args, world, rank, local):
     gallery = build_gallery(G, enc.embedding_size, device)
     images, boxes_h, scores_h, seg_h, max_n = build_shelves(args, rank, n_shelves, device)
     hp = pipeline.HotPath(enc, gallery, k=args.k, trunk_batch=args.trunk_batch,
-                          trunk_dtype=torch.float32 if args.trunk == "f32" else torch.bfloat16, channels_last=args.channels_last)
+                          trunk_dtype=torch.float32 if args.trunk == "f32" else torch.bfloat16, channels_last=args.channels_last,
+                          n_streams=args.streams)
     if args.sim == "f32":  # CUDA-core similarity instead of the tcgen05 kernel (debug / cross-check)
         from cvpce_b200 import ops
         ops_sim = ops.sim_topk

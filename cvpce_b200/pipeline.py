@@ -51,7 +51,8 @@ class _NoTimer:
 
 class HotPath:
     def __init__(self, encoder, gallery_embedding, k=1, size=256, antialias=True, iou_threshold=0.5, detections_per_img=200,
-                 min_score=None, trunk_batch=128, trunk_dtype=torch.float32, channels_last=False, exact=True, rmac_levels=0):
+                 min_score=None, trunk_batch=128, trunk_dtype=torch.float32, channels_last=False, exact=True, rmac_levels=0,
+                 n_streams=1):
         self.encoder = encoder
         self.gallery = classification.PreparedGallery(gallery_embedding)
         self.k = k
@@ -65,9 +66,16 @@ class HotPath:
         self.channels_last = channels_last
         self.exact = exact
         self.rmac_levels = rmac_levels
+        self.n_streams = n_streams
+        self._streams = None
         self.affine = classification.tanh_normalize_affine()  # scale_to_tanh + MACVGG normalisation folded into the crop kernel
         self.launches = 0  # launches of OUR kernels (library calls), counted per call site
         self.timer = _NoTimer()
+
+    def _side_streams(self, dev):
+        if self._streams is None:
+            self._streams = [torch.cuda.Stream(device=dev) for _ in range(self.n_streams)]
+        return self._streams
 
     @torch.no_grad()
     def step(self, images, cand_boxes, cand_scores, seg_offsets, max_n):
@@ -124,15 +132,31 @@ class HotPath:
         own0 = getattr(self.encoder, "own_launches", 0)
         if hasattr(self.encoder, "stage_timer"):
             self.encoder.stage_timer = None if isinstance(self.timer, _NoTimer) else self.timer
-        for i in range(0, K, self.trunk_batch):
-            f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True, pooled_f4=not self.rmac_levels)
-            if self.rmac_levels and regions is None:
-                regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.rmac_levels) for f in (f4, f5)]
-            esz = f4.element_size()
-            nb = float(f4.numel() + f5.numel()) * esz + 4.0 * D * f4.shape[0]
-            with self.timer.span("region_pool_embed", nb):
-                ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=bool(self.rmac_levels), out=emb[i:i + self.trunk_batch])
+        # trunk batches are independent: with n_streams > 1 they alternate between CUDA streams, so that the HBM-bound
+        # kernels of one batch (max-pools, MAC) can overlap the tensor-bound convolutions of another
+        main = torch.cuda.current_stream()
+        side = self._side_streams(dev) if self.n_streams > 1 else None
+        if side:
+            ready = torch.cuda.Event()
+            ready.record(main)
+        for j, i in enumerate(range(0, K, self.trunk_batch)):
+            st = side[j % len(side)] if side else main
+            if side:
+                st.wait_event(ready)
+            with torch.cuda.stream(st):
+                f4, f5 = self.encoder.features(crops[i:i + self.trunk_batch], normalized=True, pooled_f4=not self.rmac_levels)
+                if self.rmac_levels and regions is None:
+                    regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.rmac_levels) for f in (f4, f5)]
+                esz = f4.element_size()
+                nb = float(f4.numel() + f5.numel()) * esz + 4.0 * D * f4.shape[0]
+                with self.timer.span("region_pool_embed", nb):
+                    ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=bool(self.rmac_levels), out=emb[i:i + self.trunk_batch])
             self.launches += 1
+        if side:
+            for st in side:
+                crops.record_stream(st)
+                emb.record_stream(st)
+                main.wait_stream(st)
         self.launches += getattr(self.encoder, "own_launches", 0) - own0  # the library's max-pool launches inside the trunk
         G = self.gallery.G
         k = min(self.k, G)
