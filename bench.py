@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- proposal crops classified / second through the B200-native hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c4|c5]
 
 A "step" is one pass of the whole hot path over one batch of synthetic shelf images:
 scored candidate boxes -> NMS -> crop/pad/resize -> VGG16 trunk (torch, not rebuilt: SURVEY §8 a7) -> MAC pool + L2 ->
@@ -38,8 +38,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c5"])
-    ap.add_argument("--shelves", type=int, default=None, help="shelf images per GPU per step (c3: 32, c2: 1)")
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--shelves", type=int, default=None, help="shelf images per GPU per step (c3: 32, c2: 1, c4: 512 / n_gpus)")
     ap.add_argument("--products", type=int, default=200)
     ap.add_argument("--gallery", type=int, default=None)
     ap.add_argument("--k", type=int, default=5)
@@ -216,8 +216,15 @@ def run_ours_shelves(args, world, rank, local):
     device = torch.device("cuda", local)
     _lib.load()
     peaks = measured_peaks()
-    n_shelves = args.shelves or (32 if args.workload == "c3" else 1)
-    G = args.gallery or (8192 if args.workload == "c3" else 180)
+    if args.workload == "c4":
+        # BASELINE.json configs[3]: 512 SKU-110K-density shelves (~150 boxes each) split data-parallel over the GPUs
+        # (strong scaling: the 512 images are fixed); gallery as in c3 (BASELINE leaves it open)
+        n_shelves = args.shelves or max(1, 512 // world)
+        if args.products == 200:
+            args.products = 150
+    else:
+        n_shelves = args.shelves or (32 if args.workload == "c3" else 1)
+    G = args.gallery or (8192 if args.workload in ("c3", "c4") else 180)
     enc = build_encoder(args, device)
     gallery = build_gallery(G, enc.embedding_size, device)
     images, boxes_h, scores_h, seg_h, max_n = build_shelves(args, rank, n_shelves, device)
@@ -345,7 +352,8 @@ def run_ours_shelves(args, world, rank, local):
 
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True,
+        "scaling": "strong" if args.workload == "c4" and not args.shelves else "weak", "vs_baseline": None,
         "dtype": "f32" if args.trunk == "f32" else "bf16", "data": "synthetic",
         "config": {"workload": ("%s: %d shelves 2048x1536 x ~%d products per GPU -> " + ("GLN head outputs (800x1066, 160956 anchors) -> "
                                 "sigmoid/top-1000/decode -> " if args.from_head else "") + "NMS(0.5, top200) -> 256x256 crops -> "
@@ -407,7 +415,7 @@ def cpu_reference_rate(args, G, sample_crops, repeats, warmup=0):
 def run_reference(args, world, rank):
     if rank != 0:
         return None
-    G = args.gallery or (8192 if args.workload == "c3" else 180)
+    G = args.gallery or (8192 if args.workload in ("c3", "c4") else 180)
     base = cpu_reference_rate(args, G, sample_crops=args.cpu_sample_crops, repeats=args.steps, warmup=args.warmup)
     secs = base.pop("seconds_per_step")
     n = args.cpu_sample_crops
