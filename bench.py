@@ -54,6 +54,8 @@ def parse():
                     "is torch's own GPU default, TF32 convolutions: tools/tf32_check.py measures what that costs in accuracy)")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="c5, N > 1: how the per-rank top-k blocks reach the other "
+                    "ranks: stored by the selection kernel into every peer's gather buffer over NVLink, or an NCCL all-gather")
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
                     "(800x1066 frame, 5 FPN levels) -> candidate selection -> NMS -> ... instead of scored candidate boxes")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -438,7 +440,7 @@ def run_ours_c5(args, world, rank, local):
     peaks = measured_peaks()
     G = args.gallery or 1_000_000
     Q, D, k = args.queries, 512, args.k
-    searcher = cdist.ShardedGallery.synthetic(G, D, world, rank, device, seed=5)
+    searcher = cdist.ShardedGallery.synthetic(G, D, world, rank, device, seed=5, exchange=args.exchange)
     q = cdist.synthetic_queries(Q, D, device, seed=6)
     # the timed region is tens of milliseconds: start sampling clocks before the warm-up so that the sampler (200 ms period)
     # has readings taken under the same load
@@ -474,7 +476,9 @@ def run_ours_c5(args, world, rank, local):
     return {"metric": "gallery queries matched/sec (cosine top-%d)" % k, "value": round(Q * args.steps / (ms / 1e3), 1), "unit": "queries/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 operands, f32 accumulate + exact f32 re-score",
-            "data": "synthetic", "config": {"workload": "c5: %d x %d gallery sharded over %d GPU(s), %d queries, top-%d, all-gather merge" % (G, D, world, Q, k)},
+            "data": "synthetic", "config": {"workload": "c5: %d x %d gallery sharded over %d GPU(s), %d queries, top-%d, all-gather merge" % (G, D, world, Q, k),
+                               "exchange": "none (1 GPU)" if world == 1 else ("selection-kernel stores into peer gather buffers over NVLink (symmetric memory) + barrier"
+                                                                           if args.exchange == "p2p" else "NCCL all-gather")},
             "roofline": {"kernel": "sim_topk", "bound": "tensor", "achieved": round(tf, 1), "peak": peaks["tensor_sustained"], "unit": "TFLOP/s",
                          "frac": round(tf / peaks["tensor_sustained"], 4), "traffic": None,
                          "peak_source": peaks["source"] + " (bf16_tflops_sustained); includes prepare + re-score + merge time"},

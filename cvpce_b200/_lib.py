@@ -57,6 +57,8 @@ SIGNATURES = {
     "cvpce_sim_topk_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "cvpce_sim_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "cvpce_sim_topk_scatter": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
     "cvpce_sim_topk_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_float, c_void_p, c_void_p,
                                    c_void_p]),
     "cvpce_topk_merge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),

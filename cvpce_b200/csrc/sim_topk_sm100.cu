@@ -369,12 +369,22 @@ __device__ __forceinline__ bool before(float sa, int ia, float sb, int ib) {
   return sa > sb || (sa == sb && ia < ib);
 }
 
+// Where the final [Q,k] block goes: one local buffer, or -- gallery-sharded search -- the same slot of a [W,Q,k] gather
+// buffer on EVERY rank of the node (peer pointers over NVLink): the all-gather is the epilogue's store, row by row,
+// overlapped with the re-scoring of the other rows, instead of a collective after the kernel.
+constexpr int kMaxOutTargets = 16;
+struct OutTargets {
+  int n;
+  float* s[kMaxOutTargets];
+  long long* i[kMaxOutTargets];
+};
+
 template <int KP>
 __global__ void __launch_bounds__(128) sim_select_kernel(const float* __restrict__ cand_s, const int* __restrict__ cand_i, int Q,
                                                          int n_split, int k, long long idx_base, int D,
                                                          const float* __restrict__ q32, const float* __restrict__ g32,
                                                          const float* __restrict__ q_inv, const float* __restrict__ g_inv,
-                                                         float* __restrict__ out_s, long long* __restrict__ out_i) {
+                                                         const OutTargets out) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= Q) return;
@@ -468,15 +478,19 @@ __global__ void __launch_bounds__(128) sim_select_kernel(const float* __restrict
     const int oi = __shfl_sync(0xffffffffu, my_i, c);
     if (c != lane && before(os, oi, my_s, my_i)) ++rank;
   }
-  if (lane < KP && my_i >= 0 && rank < k) {
-    out_s[(size_t)row * k + rank] = my_s;
-    out_i[(size_t)row * k + rank] = idx_base + my_i;
-  }
-  // rows with fewer than k valid candidates: pad
   const int n_valid = __popc(__ballot_sync(0xffffffffu, lane < KP && my_i >= 0));
-  for (int j = n_valid + lane; j < k; j += 32) {
-    out_s[(size_t)row * k + j] = -INFINITY;
-    out_i[(size_t)row * k + j] = -1;
+  for (int t = 0; t < out.n; ++t) {
+    float* out_s = out.s[t];
+    long long* out_i = out.i[t];
+    if (lane < KP && my_i >= 0 && rank < k) {
+      out_s[(size_t)row * k + rank] = my_s;
+      out_i[(size_t)row * k + rank] = idx_base + my_i;
+    }
+    // rows with fewer than k valid candidates: pad
+    for (int j = n_valid + lane; j < k; j += 32) {
+      out_s[(size_t)row * k + j] = -INFINITY;
+      out_i[(size_t)row * k + j] = -1;
+    }
   }
 }
 
@@ -618,10 +632,12 @@ extern "C" size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k) {
   return (size_t)Q * pl.n_split * 32 * 8 + 256;  // sized for KP = 32 so that both modes fit
 }
 
-extern "C" int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
-                              const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
-                              float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream) {
-  using namespace cvpce;
+namespace cvpce {
+static int sim_topk_impl(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                         const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                         const OutTargets& targets, void* workspace, size_t workspace_bytes, void* stream) {
+  float* out_scores = targets.s[0];
+  long long* out_idx = targets.i[0];
   CVPCE_REQUIRE(Q >= 0 && G >= 0, CVPCE_ERR_INVALID_ARG, "sim_topk: negative size Q=%d G=%d", Q, G);
   CVPCE_REQUIRE(D >= 64 && D <= 4096 && D % 64 == 0, CVPCE_ERR_UNSUPPORTED, "sim_topk: D=%d must be a multiple of 64 in [64,4096] (use cvpce_sim_topk_f32)", D);
   CVPCE_REQUIRE(k >= 1 && k <= 32, CVPCE_ERR_UNSUPPORTED, "sim_topk: k=%d outside [1,32] (use cvpce_sim_topk_f32)", k);
@@ -660,10 +676,40 @@ extern "C" int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int
   const int grid = (Q + warps - 1) / warps;
   if (pl.kp == 16)
     sim_select_kernel<16><<<grid, warps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm,
-                                                       g_inv_norm, out_scores, reinterpret_cast<long long*>(out_idx));
+                                                       g_inv_norm, targets);
   else
     sim_select_kernel<32><<<grid, warps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm,
-                                                       g_inv_norm, out_scores, reinterpret_cast<long long*>(out_idx));
+                                                       g_inv_norm, targets);
   CVPCE_LAUNCH_OK("sim_select_kernel");
   return CVPCE_OK;
+}
+}  // namespace cvpce
+
+extern "C" int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                              const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                              float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream) {
+  cvpce::OutTargets t;
+  t.n = 1;
+  t.s[0] = out_scores;
+  t.i[0] = reinterpret_cast<long long*>(out_idx);
+  return cvpce::sim_topk_impl(q_bf16, g_bf16, Q, G, D, k, idx_base, q_f32, g_f32, q_inv_norm, g_inv_norm, t, workspace,
+                              workspace_bytes, stream);
+}
+
+extern "C" int cvpce_sim_topk_scatter(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                                      const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                                      float* const* peer_scores, int64_t* const* peer_idx, int n_peers, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(n_peers >= 1 && n_peers <= kMaxOutTargets && peer_scores && peer_idx, CVPCE_ERR_INVALID_ARG,
+                "sim_topk_scatter: n_peers=%d outside [1,%d] or null pointer table", n_peers, kMaxOutTargets);
+  OutTargets t;
+  t.n = n_peers;
+  for (int p = 0; p < n_peers; ++p) {
+    CVPCE_REQUIRE(peer_scores[p] && peer_idx[p], CVPCE_ERR_INVALID_ARG, "sim_topk_scatter: peer %d has a null buffer", p);
+    t.s[p] = peer_scores[p];
+    t.i[p] = reinterpret_cast<long long*>(peer_idx[p]);
+  }
+  return sim_topk_impl(q_bf16, g_bf16, Q, G, D, k, idx_base, q_f32, g_f32, q_inv_norm, g_inv_norm, t, workspace, workspace_bytes,
+                       stream);
 }

@@ -64,8 +64,59 @@ def all_gather_topk(scores, idx, group=None):
     return s_all, i_all
 
 
+class PeerGather:
+    """Double-buffered [W,Q,k] score / index gather buffers in symmetric memory (torch.distributed._symmetric_memory: every
+    rank's buffer is mapped into every other rank's address space over NVLink).  Plumbing only: it hands raw peer
+    addresses to cvpce_sim_topk_scatter and provides the cross-rank barrier; the bytes are moved by the kernel's stores."""
+
+    def __init__(self, world, rank, Q, k, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.world, self.rank, self.Q, self.k = world, rank, Q, k
+        self.s_bytes = world * Q * k * 4
+        self.i_bytes = world * Q * k * 8
+        self.half = (self.s_bytes + self.i_bytes + 255) // 256 * 256
+        pg = group if group is not None else dist.group.WORLD
+        try:  # needed by older torch builds, deprecated no-op in newer ones
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                if not symm_mem.is_symm_mem_enabled_for_group(pg.group_name):
+                    symm_mem.enable_symm_mem_for_group(pg.group_name)
+        except Exception:
+            pass
+        self.buf = symm_mem.empty((2 * self.half,), dtype=torch.uint8, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, pg)
+        self.flip = 0
+        self.hdl.barrier()
+
+    def targets(self):
+        """(score slot addresses, index slot addresses) of THIS rank's [Q,k] block in every rank's current half."""
+        base = self.flip * self.half
+        slot_s = base + self.rank * self.Q * self.k * 4
+        slot_i = base + self.s_bytes + self.rank * self.Q * self.k * 8
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        return [p + slot_s for p in ptrs], [p + slot_i for p in ptrs]
+
+    def gathered(self):
+        base = self.flip * self.half
+        s = self.buf[base: base + self.s_bytes].view(torch.float32).view(self.world, self.Q, self.k)
+        i = self.buf[base + self.s_bytes: base + self.s_bytes + self.i_bytes].view(torch.int64).view(self.world, self.Q, self.k)
+        return s, i
+
+    def barrier_and_flip(self):
+        # every rank's stores of this step are complete (kernel boundary) before its barrier signal; after the barrier all
+        # W blocks of the current half are in place.  The other half is only rewritten after the NEXT barrier, by which time
+        # every rank's merge of this half has been issued before that barrier on its stream.
+        self.hdl.barrier()
+        self.flip ^= 1
+
+
 class ShardedGallery:
-    def __init__(self, shard_f32, idx_base, world=1, rank=0, group=None, merge=None):
+    def __init__(self, shard_f32, idx_base, world=1, rank=0, group=None, merge=None, exchange="nccl"):
+        """exchange: "nccl" = all-gather of the per-rank [Q,k] blocks after the search (the reference formulation, SURVEY §8 e);
+        "p2p" = the selection kernel stores its block straight into every rank's gather buffer over NVLink peer memory."""
+        self.exchange = exchange
+        self._peer = None
         self.world, self.rank, self.group = world, rank, group
         self.idx_base = int(idx_base)
         self.g32 = shard_f32.contiguous().float()
@@ -75,9 +126,9 @@ class ShardedGallery:
         self._ws = None
 
     @classmethod
-    def synthetic(cls, G, D, world, rank, device, seed=5, group=None):
+    def synthetic(cls, G, D, world, rank, device, seed=5, group=None, exchange="nccl"):
         lo, hi = shard_range(G, world, rank)
-        return cls(synthetic_rows(lo, hi, D, device, seed), lo, world, rank, group)
+        return cls(synthetic_rows(lo, hi, D, device, seed), lo, world, rank, group, exchange=exchange)
 
     def search(self, queries_f32, k, exact=True):
         """queries f32[Q,D] (present on every rank) -> (similarity f32[Q,k], GLOBAL gallery index i64[Q,k]) on every rank."""
@@ -87,6 +138,22 @@ class ShardedGallery:
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(max(need, 16), dtype=torch.uint8, device=q.device)
         qb, qinv = ops.rows_prepare(q, normalize=True)
+        if self.world > 1 and self.exchange == "p2p":
+            if self._peer is None or self._peer.Q != Q or self._peer.k != k:
+                try:
+                    self._peer = PeerGather(self.world, self.rank, Q, k, q.device, self.group)
+                except Exception as e:  # no peer mapping on this box (plumbing, not compute): use the NCCL exchange instead
+                    import sys
+                    sys.stderr.write("cvpce_b200.dist: symmetric memory unavailable (%r); using the NCCL all-gather\n" % (e,))
+                    self.exchange = "nccl"
+                    return self.search(queries_f32, k, exact)
+            ps, pi = self._peer.targets()
+            ops.sim_topk_scatter(qb, self.gb, k, self.idx_base, ps, pi, q if exact else None, self.g32 if exact else None,
+                                 qinv if exact else None, self.ginv if exact else None, workspace=self._ws)
+            s_all, i_all = self._peer.gathered()
+            self._peer.barrier_and_flip()
+            self.launches += 4
+            return self.merge(s_all, i_all)
         s, i = ops.sim_topk(qb, self.gb, k, self.idx_base, q if exact else None, self.g32 if exact else None,
                             qinv if exact else None, self.ginv if exact else None, workspace=self._ws)
         self.launches += 3

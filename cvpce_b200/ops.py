@@ -348,6 +348,31 @@ def sim_topk(q_bf16, g_bf16, k=1, idx_base=0, q_f32=None, g_f32=None, q_inv_norm
     return s, i
 
 
+def sim_topk_scatter(q_bf16, g_bf16, k, idx_base, peer_score_ptrs, peer_idx_ptrs, q_f32=None, g_f32=None, q_inv_norm=None,
+                     g_inv_norm=None, workspace=None):
+    """sim_topk whose [Q,k] result block is stored by the kernel into every peer's gather buffer: peer_*_ptrs are raw device
+    addresses (ints) of THIS rank's [Q,k] slot inside each rank's [W,Q,k] score / index buffers (peer memory over NVLink).
+    The caller synchronises the ranks (symmetric-memory barrier) before merging."""
+    _need_cuda("sim_topk_scatter", q_bf16, g_bf16, q_f32, g_f32, q_inv_norm, g_inv_norm, workspace)
+    if q_bf16.dtype != torch.bfloat16 or g_bf16.dtype != torch.bfloat16 or not q_bf16.is_contiguous() or not g_bf16.is_contiguous():
+        raise RuntimeError("sim_topk_scatter: operands must be contiguous bfloat16 [rows, D]")
+    Q, D = q_bf16.shape
+    G = g_bf16.shape[0]
+    n = len(peer_score_ptrs)
+    if n != len(peer_idx_ptrs) or n < 1:
+        raise RuntimeError("sim_topk_scatter: need one score and one index pointer per peer")
+    need = sim_topk_workspace_bytes(Q, G, D, k)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty(max(need, 16), dtype=torch.uint8, device=q_bf16.device)
+    ps = (ctypes.c_void_p * n)(*[int(p) for p in peer_score_ptrs])
+    pi = (ctypes.c_void_p * n)(*[int(p) for p in peer_idx_ptrs])
+    rc = _lib.load().cvpce_sim_topk_scatter(_ptr(q_bf16), _ptr(g_bf16), Q, G, D, int(k), int(idx_base), _ptr(q_f32), _ptr(g_f32),
+                                            _ptr(q_inv_norm), _ptr(g_inv_norm), ctypes.cast(ps, ctypes.c_void_p),
+                                            ctypes.cast(pi, ctypes.c_void_p), n, _ptr(workspace),
+                                            workspace.numel() * workspace.element_size(), _stream())
+    _lib.check(rc, "cvpce_sim_topk_scatter")
+
+
 def topk_merge(scores, idx):
     """scores f32[W,Q,k], idx i64[W,Q,k] (global indices) -> merged (f32[Q,k], i64[Q,k])."""
     _need_cuda("topk_merge", scores, idx)

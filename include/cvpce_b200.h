@@ -215,6 +215,16 @@ CVPCE_API size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k);
 CVPCE_API int cvpce_sim_topk(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
                    const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
                    float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream);
+/* Gallery-sharded search (e: one process per GPU, each holding a shard): the same computation, but the final [Q,k] block of
+ * this rank is stored by the selection kernel's epilogue DIRECTLY into every peer's gather buffer -- peer_scores[p] /
+ * peer_idx[p] [host arrays of n_peers <= 16 device pointers] address this rank's [Q,k] slot inside rank p's [W,Q,k] buffers
+ * (peer memory mapped over NVLink, e.g. torch symmetric memory / cudaIpc; the own buffer is one of the n_peers).  The
+ * all-gather that follows the search in the reference formulation (SURVEY §8 e) thus happens row by row while other rows
+ * are still being re-scored; the caller only needs a cross-rank barrier before cvpce_topk_merge reads the gather buffers. */
+CVPCE_API int cvpce_sim_topk_scatter(const void* q_bf16, const void* g_bf16, int Q, int G, int D, int k, int64_t idx_base,
+                           const float* q_f32, const float* g_f32, const float* q_inv_norm, const float* g_inv_norm,
+                           float* const* peer_scores, int64_t* const* peer_idx, int n_peers,
+                           void* workspace, size_t workspace_bytes, void* stream);
 /* CUDA-core fp32 path (any D >= 1, k <= 64): exact fp32 dot products, same ordering contract; used for tiny shapes and
  * as the on-device cross-check of the tensor-core path.  normalize=1 divides by max(norm,eps) of both rows (distance()). */
 CVPCE_API int cvpce_sim_topk_f32(const float* q, const float* g, int Q, int G, int D, int k, int64_t idx_base,

@@ -645,3 +645,23 @@ def test_mac_of_pooled_relu4_3_is_bit_identical(ops):
         assert torch.equal(ops.region_pool_embed([f4, f5]), ops.region_pool_embed([p4, q5]))
         odd = enc.features(x[:, :, :40, :40], pooled_f4=True)[0]      # relu4_3 is 5x5: not tiled by 2x2 windows -> unchanged
         assert odd.shape[2] == 5
+
+
+def test_sim_topk_scatter_writes_every_target(ops):
+    """The gallery-sharded search's kernel-side scatter: the [Q,k] block lands in every target buffer (here two local
+    buffers standing in for two ranks' gather slots) and equals the plain sim_topk result."""
+    rs = np.random.RandomState(5)
+    Q, G, D, k = 300, 5000, 512, 5
+    q, g = dev(synth.unit_rows(rs, Q, D, nonneg=False)), dev(synth.unit_rows(rs, G, D, nonneg=False))
+    qb, qi = ops.rows_prepare(q, True)
+    gb, gi = ops.rows_prepare(g, True)
+    s, i = ops.sim_topk(qb, gb, k, 1000, q, g, qi, gi)
+    W = 3
+    gs = torch.full((2, W, Q, k), -7.0, device="cuda")
+    gidx = torch.full((2, W, Q, k), -7, dtype=torch.int64, device="cuda")
+    slot = 1
+    ops.sim_topk_scatter(qb, gb, k, 1000, [gs[r, slot].data_ptr() for r in range(2)], [gidx[r, slot].data_ptr() for r in range(2)],
+                         q, g, qi, gi)
+    for r in range(2):
+        assert torch.equal(gs[r, slot], s) and torch.equal(gidx[r, slot], i)
+        assert bool((gs[r, 0] == -7).all()) and bool((gidx[r, 2] == -7).all())   # other slots untouched
