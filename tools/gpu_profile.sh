@@ -15,6 +15,6 @@ $PROF > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $OUT/launches.csv $PROF > $OUT/ncu_launch.log 2>&1
 echo "ncu launches exit $?"
 $PROF > $OUT/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k 'regex:select_candidates_kernel|nms_batched_kernel|crop_resize_sep_kernel|crop_resize_kernel|region_pool_kernel|rows_prepare_kernel|sim_topk_tc_kernel|sim_select_kernel' -c 16 -o $OUT/prof_own $PROF > $OUT/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:select_candidates_kernel|nms_batched_kernel|crop_resize_sep_kernel|crop_resize_kernel|region_pool_kernel|mac_nhwc_pixelsplit_kernel|maxpool2x2_nhwc_kernel|rows_prepare_kernel|sim_topk_tc_kernel|sim_select_kernel' -c 40 -o $OUT/prof_own $PROF > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT

@@ -74,39 +74,42 @@ def full(path):
     print("\n# launches captured per kernel: " + ", ".join("%s x%d" % kv for kv in seen.items()))
 
 
-STAGE_OF = {"region_pool_kernel": "region_pool_embed", "crop_resize_sep_kernel": "crop_resize", "crop_resize_kernel": "crop_resize",
+STAGE_OF = {"region_pool_kernel": "region_pool_embed", "mac_nhwc_pixelsplit_kernel": "region_pool_embed", "maxpool2x2_nhwc_kernel": "maxpool2x2", "crop_resize_sep_kernel": "crop_resize", "crop_resize_kernel": "crop_resize",
             "nms_batched_kernel": "nms", "select_candidates_kernel": "select_candidates", "rows_prepare_kernel": "rows_prepare",
             "sim_topk_tc_kernel": "sim_topk"}
 
 
-def traffic(path, bench_log):
+def traffic(path, bench_log, *more_paths):
     """profiles/ncu_traffic.json: DRAM bytes per launch (median over the captured launches) of each of our kernels, next to
     the algorithmic bytes per launch the profiled bench.py run itself reported (bench.py matches on those)."""
     import json
     import statistics
     line = [ln for ln in open(bench_log) if ln.startswith("{")][-1]
     kernels = json.loads(line)["kernels"]
-    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-    rows = list(csv.reader(io.StringIO(out)))
-    hdr, units, data = rows[0], rows[1], rows[2:]
-    idx = {h: i for i, h in enumerate(hdr)}
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     per = collections.defaultdict(list)
-    for d in data:
+    src = {}
+    for pth in (path,) + tuple(more_paths):
+      out = subprocess.run(["ncu", "-i", pth, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+      rows = list(csv.reader(io.StringIO(out)))
+      hdr, units, data = rows[0], rows[1], rows[2:]
+      idx = {h: i for i, h in enumerate(hdr)}
+      for d in data:
         short = re.sub(r"[(<].*", "", re.sub(r"^void ", "", d[idx["Kernel Name"]])).replace("cvpce::", "")
         stage = STAGE_OF.get(short)
-        if not stage:
+        if not stage or src.get(stage, pth) != pth:  # a stage is taken from the first report that has it
             continue
         b = 0.0
         for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
             b += float(d[idx[m]].replace(",", "")) * scale[units[idx[m]]]
         per[stage].append(b)
+        src[stage] = pth
     res = {}
     for stage, v in per.items():
         if stage in kernels and "algorithmic_bytes_per_launch" in kernels[stage]:
-            res[stage] = {"dram_bytes_per_launch": statistics.median(v), "launches_captured": len(v),
+            res[stage] = {"dram_bytes_per_launch": statistics.mean(v), "launches_captured": len(v),
                           "algorithmic_bytes_per_launch": kernels[stage]["algorithmic_bytes_per_launch"],
-                          "source": "ncu --set full --clock-control none, %s" % path}
+                          "source": "ncu --set full --clock-control none, %s (mean over the captured launches)" % src[stage]}
     print(json.dumps(res, indent=1))
 
 
