@@ -3,7 +3,7 @@
 
     python tools/ncu_summary.py launches gpurun_out/<tag>/launches.csv  > profiles/<name>_launches.txt
     python tools/ncu_summary.py full     gpurun_out/<tag>/prof.ncu-rep  > profiles/<name>_ncu_full.txt
-    python tools/ncu_summary.py traffic  gpurun_out/<tag>/prof.ncu-rep gpurun_out/<tag>/plain.log > profiles/ncu_traffic.json
+    python tools/ncu_summary.py traffic  <rep> <plain log of the same command> [<rep2> <log2> ...] > profiles/ncu_traffic.json
 """
 import collections
 import csv
@@ -79,17 +79,21 @@ STAGE_OF = {"region_pool_kernel": "region_pool_embed", "mac_nhwc_pixelsplit_kern
             "sim_topk_tc_kernel": "sim_topk"}
 
 
-def traffic(path, bench_log, *more_paths):
+def traffic(path, bench_log, *more):
     """profiles/ncu_traffic.json: DRAM bytes per launch (median over the captured launches) of each of our kernels, next to
     the algorithmic bytes per launch the profiled bench.py run itself reported (bench.py matches on those)."""
     import json
     import statistics
-    line = [ln for ln in open(bench_log) if ln.startswith("{")][-1]
-    kernels = json.loads(line)["kernels"]
+    # arguments: report, the plain log of the same command [, report2, log2 ...]; a stage is taken from the first pair that has it
+    pairs = [(path, bench_log)] + [(more[i], more[i + 1]) for i in range(0, len(more) - 1, 2)]
+    kernels_of = {}
+    for pth, log in pairs:
+        line = [ln for ln in open(log) if ln.startswith("{")][-1]
+        kernels_of[pth] = json.loads(line)["kernels"]
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     per = collections.defaultdict(list)
     src = {}
-    for pth in (path,) + tuple(more_paths):
+    for pth, _ in pairs:
       out = subprocess.run(["ncu", "-i", pth, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
       rows = list(csv.reader(io.StringIO(out)))
       hdr, units, data = rows[0], rows[1], rows[2:]
@@ -106,6 +110,7 @@ def traffic(path, bench_log, *more_paths):
         src[stage] = pth
     res = {}
     for stage, v in per.items():
+        kernels = kernels_of[src[stage]]
         if stage in kernels and "algorithmic_bytes_per_launch" in kernels[stage]:
             res[stage] = {"dram_bytes_per_launch": statistics.mean(v), "launches_captured": len(v),
                           "algorithmic_bytes_per_launch": kernels[stage]["algorithmic_bytes_per_launch"],
