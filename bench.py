@@ -360,9 +360,11 @@ def run_ours_shelves(args, world, rank, local):
         "config": {"workload": ("%s: %d shelves 2048x1536 x ~%d products per GPU -> " + ("GLN head outputs (800x1066, 160956 anchors) -> "
                                 "sigmoid/top-1000/decode -> " if args.from_head else "") + "NMS(0.5, top200) -> 256x256 crops -> "
                                 "VGG16(random init)+MAC -> cosine top-%d vs %d x 1024 gallery") % (args.workload, n_shelves, args.products, args.k, G),
-                   "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16, not rebuilt (%s%s%s, tf32 convs %s)" % (
+                   "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16 convolutions, not rebuilt (%s%s%s, tf32 convs %s)%s" % (
                        args.trunk, ", channels_last" if args.channels_last else "",
-                       "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32),
+                       "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32,
+                       "" if args.plain_trunk else "; the 2x2 max-pools between them run in the library (cvpce_maxpool2x2_nhwc)"),
+                   "trunk_batch": args.trunk_batch,
                    "similarity": "tcgen05 bf16 + exact fp32 re-score" if args.sim == "tc" else "cuda-core fp32",
                    "l2": "inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9),
                    "parallelism": "dp%d (independent images, no data-path collective)" % world},
