@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libcvpce_b200.so")
 
-F32, BF16 = 0, 1
+F32, BF16, F16 = 0, 1, 2
 NCHW, NHWC = 0, 1
 NMS_MAX_N = 8192
 POOL_MAX_MAPS = 4

@@ -102,7 +102,7 @@ class MACVGG(nn.Module):
 
     def forward(self, x, eps=1e-8, normalized=False):
         f4, f5 = self.features(x, normalized, pooled_f4=self.regions_levels == 0)
-        if f4.dtype not in (torch.float32, torch.bfloat16):
+        if f4.dtype not in (torch.float32, torch.bfloat16, torch.float16):
             f4, f5 = f4.float(), f5.float()
         if self.regions_levels > 0:
             regions = [ops.rmac_regions(f.shape[2], f.shape[3], self.regions_levels) for f in (f4, f5)]

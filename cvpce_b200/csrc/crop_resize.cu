@@ -18,6 +18,7 @@
 //  * crop_resize_kernel (direct form: one thread per output pixel, all taps): plain bilinear (antialias=0, 4 taps),
 //    odd S, and the fallback for extreme down-sampling whose tap table does not fit the shared-memory budget.
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 namespace cvpce {
@@ -158,6 +159,22 @@ __device__ __forceinline__ void direct_pixel(const float* __restrict__ base, lon
   }
 }
 
+// two fp32 values -> one 32-bit word of 16-bit outputs (bf16 or IEEE half, round to nearest even)
+template <int DTYPE>
+__device__ __forceinline__ uint32_t pack16x2(float lo, float hi) {
+  if (DTYPE == CVPCE_F16) {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+  }
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+template <int DTYPE>
+__device__ __forceinline__ unsigned short to16(float x) {
+  if (DTYPE == CVPCE_F16) return __half_as_ushort(__float2half_rn(x));
+  return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
+
 template <int DTYPE, int LAYOUT>
 __device__ __forceinline__ void store_pixel(void* outp, size_t k, int npix, int pix, float a0, float a1, float a2) {
   if (LAYOUT == CVPCE_NCHW) {
@@ -168,10 +185,10 @@ __device__ __forceinline__ void store_pixel(void* outp, size_t k, int npix, int 
       __stcs(out + o + npix, a1);
       __stcs(out + o + 2 * (size_t)npix, a2);
     } else {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(outp);
-      out[o] = __float2bfloat16_rn(a0);
-      out[o + npix] = __float2bfloat16_rn(a1);
-      out[o + 2 * (size_t)npix] = __float2bfloat16_rn(a2);
+      unsigned short* out = reinterpret_cast<unsigned short*>(outp);
+      out[o] = to16<DTYPE>(a0);
+      out[o + npix] = to16<DTYPE>(a1);
+      out[o + 2 * (size_t)npix] = to16<DTYPE>(a2);
     }
   } else {
     const size_t o = (k * (size_t)npix + pix) * 3;
@@ -181,17 +198,12 @@ __device__ __forceinline__ void store_pixel(void* outp, size_t k, int npix, int 
       out[o + 1] = a1;
       out[o + 2] = a2;
     } else {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(outp);
-      out[o] = __float2bfloat16_rn(a0);
-      out[o + 1] = __float2bfloat16_rn(a1);
-      out[o + 2] = __float2bfloat16_rn(a2);
+      unsigned short* out = reinterpret_cast<unsigned short*>(outp);
+      out[o] = to16<DTYPE>(a0);
+      out[o + 1] = to16<DTYPE>(a1);
+      out[o + 2] = to16<DTYPE>(a2);
     }
   }
-}
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<const uint32_t*>(&v);
 }
 
 // 4 consecutive output pixels (ox4 .. ox4+3) of row oy, 3 channels
@@ -208,10 +220,10 @@ __device__ __forceinline__ void store_quad(void* outp, size_t k, int S, int oy, 
       __stcs(reinterpret_cast<float4*>(out + o + npix), c1);
       __stcs(reinterpret_cast<float4*>(out + o + 2 * npix), c2);
     } else {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(outp);
-      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack_bf16x2(c0.x, c0.y), pack_bf16x2(c0.z, c0.w)));
-      __stcs(reinterpret_cast<uint2*>(out + o + npix), make_uint2(pack_bf16x2(c1.x, c1.y), pack_bf16x2(c1.z, c1.w)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 2 * npix), make_uint2(pack_bf16x2(c2.x, c2.y), pack_bf16x2(c2.z, c2.w)));
+      unsigned short* out = reinterpret_cast<unsigned short*>(outp);
+      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack16x2<DTYPE>(c0.x, c0.y), pack16x2<DTYPE>(c0.z, c0.w)));
+      __stcs(reinterpret_cast<uint2*>(out + o + npix), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
+      __stcs(reinterpret_cast<uint2*>(out + o + 2 * npix), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
     }
   } else {
     const size_t o = (k * npix + pix) * 3;  // 12 consecutive values: c0.x c1.x c2.x c0.y ...
@@ -221,10 +233,10 @@ __device__ __forceinline__ void store_quad(void* outp, size_t k, int S, int oy, 
       __stcs(reinterpret_cast<float4*>(out + o + 4), make_float4(c1.y, c2.y, c0.z, c1.z));
       __stcs(reinterpret_cast<float4*>(out + o + 8), make_float4(c2.z, c0.w, c1.w, c2.w));
     } else {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(outp);  // 24 bytes, 8-byte aligned (S % 4 == 0)
-      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack_bf16x2(c0.x, c1.x), pack_bf16x2(c2.x, c0.y)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 4), make_uint2(pack_bf16x2(c1.y, c2.y), pack_bf16x2(c0.z, c1.z)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 8), make_uint2(pack_bf16x2(c2.z, c0.w), pack_bf16x2(c1.w, c2.w)));
+      unsigned short* out = reinterpret_cast<unsigned short*>(outp);  // 24 bytes, 8-byte aligned (S % 4 == 0)
+      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, c0.y)));
+      __stcs(reinterpret_cast<uint2*>(out + o + 4), make_uint2(pack16x2<DTYPE>(c1.y, c2.y), pack16x2<DTYPE>(c0.z, c1.z)));
+      __stcs(reinterpret_cast<uint2*>(out + o + 8), make_uint2(pack16x2<DTYPE>(c2.z, c0.w), pack16x2<DTYPE>(c1.w, c2.w)));
     }
   }
 }
@@ -240,9 +252,9 @@ __device__ __forceinline__ void store_quad_at(unsigned char* at, size_t plane_by
       __stcs(reinterpret_cast<float4*>(at + plane_bytes), c1);
       __stcs(reinterpret_cast<float4*>(at + 2 * plane_bytes), c2);
     } else {
-      __stcs(reinterpret_cast<uint2*>(at), make_uint2(pack_bf16x2(c0.x, c0.y), pack_bf16x2(c0.z, c0.w)));
-      __stcs(reinterpret_cast<uint2*>(at + plane_bytes), make_uint2(pack_bf16x2(c1.x, c1.y), pack_bf16x2(c1.z, c1.w)));
-      __stcs(reinterpret_cast<uint2*>(at + 2 * plane_bytes), make_uint2(pack_bf16x2(c2.x, c2.y), pack_bf16x2(c2.z, c2.w)));
+      __stcs(reinterpret_cast<uint2*>(at), make_uint2(pack16x2<DTYPE>(c0.x, c0.y), pack16x2<DTYPE>(c0.z, c0.w)));
+      __stcs(reinterpret_cast<uint2*>(at + plane_bytes), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
+      __stcs(reinterpret_cast<uint2*>(at + 2 * plane_bytes), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
     }
   } else {
     if (DTYPE == CVPCE_F32) {
@@ -252,9 +264,9 @@ __device__ __forceinline__ void store_quad_at(unsigned char* at, size_t plane_by
       __stcs(o + 2, make_float4(c2.z, c0.w, c1.w, c2.w));
     } else {
       uint2* o = reinterpret_cast<uint2*>(at);  // 24 bytes, 8-byte aligned (S % 4 == 0)
-      __stcs(o, make_uint2(pack_bf16x2(c0.x, c1.x), pack_bf16x2(c2.x, c0.y)));
-      __stcs(o + 1, make_uint2(pack_bf16x2(c1.y, c2.y), pack_bf16x2(c0.z, c1.z)));
-      __stcs(o + 2, make_uint2(pack_bf16x2(c2.z, c0.w), pack_bf16x2(c1.w, c2.w)));
+      __stcs(o, make_uint2(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, c0.y)));
+      __stcs(o + 1, make_uint2(pack16x2<DTYPE>(c1.y, c2.y), pack16x2<DTYPE>(c0.z, c1.z)));
+      __stcs(o + 2, make_uint2(pack16x2<DTYPE>(c2.z, c0.w), pack16x2<DTYPE>(c1.w, c2.w)));
     }
   }
 }
@@ -628,6 +640,9 @@ static int launch_sep(const CropParams& p, int out_dtype, int out_layout, cudaSt
   if (smem > 200 * 1024) return -1;
   if (out_dtype == CVPCE_F32 && out_layout == CVPCE_NCHW) return launch_sep_one<CVPCE_F32, CVPCE_NCHW>(p, lay, smem, st);
   if (out_dtype == CVPCE_F32) return launch_sep_one<CVPCE_F32, CVPCE_NHWC>(p, lay, smem, st);
+  if (out_dtype == CVPCE_F16)
+    return out_layout == CVPCE_NCHW ? launch_sep_one<CVPCE_F16, CVPCE_NCHW>(p, lay, smem, st)
+                                    : launch_sep_one<CVPCE_F16, CVPCE_NHWC>(p, lay, smem, st);
   if (out_layout == CVPCE_NCHW) return launch_sep_one<CVPCE_BF16, CVPCE_NCHW>(p, lay, smem, st);
   return launch_sep_one<CVPCE_BF16, CVPCE_NHWC>(p, lay, smem, st);
 }
@@ -684,6 +699,10 @@ static int launch_crop(const CropParams& p, int out_dtype, int out_layout, cudaS
     crop_resize_kernel<AA, CVPCE_F32, CVPCE_NCHW><<<grid, kCropThreads, 0, st>>>(p);
   else if (out_dtype == CVPCE_F32)
     crop_resize_kernel<AA, CVPCE_F32, CVPCE_NHWC><<<grid, kCropThreads, 0, st>>>(p);
+  else if (out_dtype == CVPCE_F16 && out_layout == CVPCE_NCHW)
+    crop_resize_kernel<AA, CVPCE_F16, CVPCE_NCHW><<<grid, kCropThreads, 0, st>>>(p);
+  else if (out_dtype == CVPCE_F16)
+    crop_resize_kernel<AA, CVPCE_F16, CVPCE_NHWC><<<grid, kCropThreads, 0, st>>>(p);
   else if (out_layout == CVPCE_NCHW)
     crop_resize_kernel<AA, CVPCE_BF16, CVPCE_NCHW><<<grid, kCropThreads, 0, st>>>(p);
   else
@@ -703,7 +722,8 @@ extern "C" int cvpce_crop_resize(const int64_t* image_table, int n_images, const
                                  void* stream) {
   using namespace cvpce;
   CVPCE_REQUIRE(K >= 0 && S > 0 && S <= 4096, CVPCE_ERR_INVALID_ARG, "crop_resize: bad K=%d or S=%d", K, S);
-  CVPCE_REQUIRE(out_dtype == CVPCE_F32 || out_dtype == CVPCE_BF16, CVPCE_ERR_INVALID_ARG, "crop_resize: bad out_dtype %d", out_dtype);
+  CVPCE_REQUIRE(out_dtype == CVPCE_F32 || out_dtype == CVPCE_BF16 || out_dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG,
+                "crop_resize: bad out_dtype %d", out_dtype);
   CVPCE_REQUIRE(out_layout == CVPCE_NCHW || out_layout == CVPCE_NHWC, CVPCE_ERR_INVALID_ARG, "crop_resize: bad out_layout %d", out_layout);
   if (K == 0) return CVPCE_OK;
   CVPCE_REQUIRE(image_table && boxes && out && n_images > 0, CVPCE_ERR_INVALID_ARG, "crop_resize: null pointer or n_images<=0");

@@ -10,6 +10,7 @@
 // consecutive addresses of both input rows), one 128-bit store.  blockIdx.x = output row (b, yo): no integer division
 // except one per thread to split (xo, channel group).
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace cvpce {
 
@@ -37,6 +38,23 @@ __device__ __forceinline__ uint32_t max2_bf16(uint32_t a, uint32_t b) {
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
+__device__ __forceinline__ uint32_t max2_f16(uint32_t a, uint32_t b) {
+  const __half2 x = *reinterpret_cast<const __half2*>(&a), y = *reinterpret_cast<const __half2*>(&b);
+  const float2 xf = __half22float2(x), yf = __half22float2(y);
+  const __half2 r = __floats2half2_rn(max_nan(xf.x, yf.x), max_nan(xf.y, yf.y));  // exact: both are half values
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+
+__device__ __forceinline__ float4 max4_f16(float4 a, float4 b, float4 c, float4 d) {
+  float4 r;
+  uint32_t* ro = reinterpret_cast<uint32_t*>(&r);
+  const uint32_t *pa = reinterpret_cast<const uint32_t*>(&a), *pb = reinterpret_cast<const uint32_t*>(&b),
+                 *pc = reinterpret_cast<const uint32_t*>(&c), *pd = reinterpret_cast<const uint32_t*>(&d);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ro[i] = max2_f16(max2_f16(pa[i], pb[i]), max2_f16(pc[i], pd[i]));
+  return r;
+}
+
 __device__ __forceinline__ float4 max4_bf16(float4 a, float4 b, float4 c, float4 d) {
   float4 r;
   uint32_t* ro = reinterpret_cast<uint32_t*>(&r);
@@ -48,7 +66,7 @@ __device__ __forceinline__ float4 max4_bf16(float4 a, float4 b, float4 c, float4
 }
 
 // vec = 16-byte groups per pixel (C*esize/16); row_vecs = Wo * vec
-template <bool BF16>
+template <int DT>
 __global__ void __launch_bounds__(256) maxpool2x2_nhwc_kernel(const float4* __restrict__ in, float4* __restrict__ out, int H, int W,
                                                                int Ho, int Wo, int vec, int row_vecs) {
   const int row = blockIdx.x;  // b * Ho + yo
@@ -60,7 +78,7 @@ __global__ void __launch_bounds__(256) maxpool2x2_nhwc_kernel(const float4* __re
     const int xo = j / vec, c = j - xo * vec;
     const int i0 = 2 * xo * vec + c;
     const float4 a = ld_stream(r0 + i0), bq = ld_stream(r0 + i0 + vec), cq = ld_stream(r1 + i0), d = ld_stream(r1 + i0 + vec);
-    o[j] = BF16 ? max4_bf16(a, bq, cq, d) : max4_f32(a, bq, cq, d);
+    o[j] = DT == CVPCE_BF16 ? max4_bf16(a, bq, cq, d) : (DT == CVPCE_F16 ? max4_f16(a, bq, cq, d) : max4_f32(a, bq, cq, d));
   }
 }
 
@@ -69,7 +87,7 @@ __global__ void __launch_bounds__(256) maxpool2x2_nhwc_kernel(const float4* __re
 extern "C" int cvpce_maxpool2x2_nhwc(const void* in, int dtype, int B, int H, int W, int C, void* out, void* stream) {
   using namespace cvpce;
   CVPCE_REQUIRE(B >= 0 && H >= 0 && W >= 0 && C >= 1, CVPCE_ERR_INVALID_ARG, "maxpool2x2: bad shape B=%d H=%d W=%d C=%d", B, H, W, C);
-  CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16, CVPCE_ERR_INVALID_ARG, "maxpool2x2: dtype %d", dtype);
+  CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16 || dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG, "maxpool2x2: dtype %d", dtype);
   const int Ho = H / 2, Wo = W / 2;  // floor mode, no padding (nn.MaxPool2d defaults)
   if (B == 0 || Ho == 0 || Wo == 0) return CVPCE_OK;
   const int per16 = dtype == CVPCE_F32 ? 4 : 8;
@@ -86,9 +104,11 @@ extern "C" int cvpce_maxpool2x2_nhwc(const void* in, int dtype, int B, int H, in
   const float4* i4 = reinterpret_cast<const float4*>(in);
   float4* o4 = reinterpret_cast<float4*>(out);
   if (dtype == CVPCE_F32)
-    maxpool2x2_nhwc_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(i4, o4, H, W, Ho, Wo, vec, (int)row_vecs);
+    maxpool2x2_nhwc_kernel<CVPCE_F32><<<grid, 256, 0, (cudaStream_t)stream>>>(i4, o4, H, W, Ho, Wo, vec, (int)row_vecs);
+  else if (dtype == CVPCE_BF16)
+    maxpool2x2_nhwc_kernel<CVPCE_BF16><<<grid, 256, 0, (cudaStream_t)stream>>>(i4, o4, H, W, Ho, Wo, vec, (int)row_vecs);
   else
-    maxpool2x2_nhwc_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(i4, o4, H, W, Ho, Wo, vec, (int)row_vecs);
+    maxpool2x2_nhwc_kernel<CVPCE_F16><<<grid, 256, 0, (cudaStream_t)stream>>>(i4, o4, H, W, Ho, Wo, vec, (int)row_vecs);
   CVPCE_LAUNCH_OK("maxpool2x2_nhwc_kernel");
   return CVPCE_OK;
 }

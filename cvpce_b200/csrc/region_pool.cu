@@ -18,6 +18,7 @@
 //    maxima of every COLUMN segment of the row go to shared memory, then one thread per (region, channel) reduces the
 //    region's rows x column segments.
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include <cooperative_groups.h>
 #include <math.h>
 #include <algorithm>
@@ -458,12 +459,13 @@ __global__ void __launch_bounds__(kPoolThreads, GENERAL ? (NHWC_ONLY ? 3 : 2) : 
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kMacMaxCols = 4096;  // sum of C over the maps
 
-template <bool BF16>
+template <int DT>
 __global__ void __launch_bounds__(kPoolThreads) mac_nhwc_pixelsplit_kernel(const PoolParams p) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned crank = cluster.block_rank(), csize = cluster.num_blocks();
   const int n = blockIdx.x / kPoolCluster;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr bool BF16 = DT != CVPCE_F32;  // any 16-bit element type
   constexpr int E = BF16 ? 8 : 4;  // elements per 16-byte vector
   __shared__ float pmax[kMacMaxCols];          // this CTA's maxima over its pixels, every channel of every map
   __shared__ float red[kPoolThreads * E];
@@ -486,7 +488,14 @@ __global__ void __launch_bounds__(kPoolThreads) mac_nhwc_pixelsplit_kernel(const
 #pragma unroll 8
     for (int i = tid; i < total; i += kPoolThreads) {
       const uint4 x = ldg_stream_u4(base + i);
-      if (BF16) {
+      if (DT == CVPCE_F16) {
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&x.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&x.y));
+        const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&x.z)), d = __half22float2(*reinterpret_cast<const __half2*>(&x.w));
+        acc[0] = fmaxf(acc[0], a.x); acc[1] = fmaxf(acc[1], a.y);
+        acc[2] = fmaxf(acc[2], b.x); acc[3] = fmaxf(acc[3], b.y);
+        acc[4 % E] = fmaxf(acc[4 % E], c.x); acc[5 % E] = fmaxf(acc[5 % E], c.y);
+        acc[6 % E] = fmaxf(acc[6 % E], d.x); acc[7 % E] = fmaxf(acc[7 % E], d.y);
+      } else if (BF16) {
         acc[0] = fmaxf(acc[0], bf16lo(x.x)); acc[1] = fmaxf(acc[1], bf16hi(x.x));
         acc[2] = fmaxf(acc[2], bf16lo(x.y)); acc[3] = fmaxf(acc[3], bf16hi(x.y));
         acc[4 % E] = fmaxf(acc[4 % E], bf16lo(x.z)); acc[5 % E] = fmaxf(acc[5 % E], bf16hi(x.z));
@@ -640,7 +649,7 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
                                        int final_l2, float eps, float* out, int64_t out_stride, void* stream) {
   using namespace cvpce;
   CVPCE_REQUIRE(maps && n_maps >= 1 && n_maps <= CVPCE_POOL_MAX_MAPS, CVPCE_ERR_INVALID_ARG, "region_pool: n_maps=%d out of [1,%d]", n_maps, CVPCE_POOL_MAX_MAPS);
-  CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16, CVPCE_ERR_INVALID_ARG, "region_pool: bad dtype %d", dtype);
+  CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16 || dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG, "region_pool: bad dtype %d", dtype);
   CVPCE_REQUIRE(B >= 0, CVPCE_ERR_INVALID_ARG, "region_pool: B=%d", B);
   CVPCE_REQUIRE((regions == nullptr) == (n_regions == nullptr), CVPCE_ERR_INVALID_ARG, "region_pool: regions and n_regions must both be given or both null");
   if (B == 0) return CVPCE_OK;
@@ -735,8 +744,12 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   void (*kern)(PoolParams);
   size_t smem_launch = smem;
   if (pixsplit) {
-    kern = dtype == CVPCE_F32 ? mac_nhwc_pixelsplit_kernel<false> : mac_nhwc_pixelsplit_kernel<true>;
+    kern = dtype == CVPCE_F32 ? mac_nhwc_pixelsplit_kernel<CVPCE_F32>
+                              : (dtype == CVPCE_BF16 ? mac_nhwc_pixelsplit_kernel<CVPCE_BF16> : mac_nhwc_pixelsplit_kernel<CVPCE_F16>);
     smem_launch = 0;
+  } else if (dtype == CVPCE_F16) {
+    return set_err(CVPCE_ERR_UNSUPPORTED, "region_pool: float16 maps are supported for dense channels-last MAC only (whole-map regions, "
+                                          "no per-region L2, C*2/16 dividing 256)");
   } else if (dtype == CVPCE_F32) {
     kern = all_nhwc ? (general ? region_pool_kernel<CVPCE_F32, true, true> : region_pool_kernel<CVPCE_F32, false, true>)
                     : (general ? region_pool_kernel<CVPCE_F32, true, false> : region_pool_kernel<CVPCE_F32, false, false>);

@@ -10,7 +10,9 @@ import struct
 import torch
 
 from . import _lib
-from ._lib import BF16, F32, NCHW, NHWC  # noqa: F401
+from ._lib import BF16, F16, F32, NCHW, NHWC  # noqa: F401
+
+_DTYPE_CODE = {torch.float32: F32, torch.bfloat16: BF16, torch.float16: F16}
 
 
 def _stream():
@@ -181,7 +183,7 @@ def batched_nms(boxes, scores, idxs, iou_threshold):
 # ---------------------------------------------------------------------------------------------------------------------
 def maxpool2x2_supported(x):
     per16 = 4 if x.dtype == torch.float32 else 8
-    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16) and x.shape[1] % per16 == 0
+    return (x.is_cuda and x.dim() == 4 and x.dtype in _DTYPE_CODE and x.shape[1] % per16 == 0
             and x.shape[2] >= 2 and x.shape[3] >= 2 and x.is_contiguous(memory_format=torch.channels_last))
 
 
@@ -189,10 +191,10 @@ def maxpool2x2(x):
     """nn.MaxPool2d(kernel_size=2, stride=2) on a channels_last CUDA tensor [B,C,H,W] -> channels_last [B,C,H//2,W//2]."""
     _need_cuda("maxpool2x2", x)
     if not maxpool2x2_supported(x):
-        raise RuntimeError("maxpool2x2: needs a channels_last float32/bfloat16 CUDA tensor with 16-byte channel groups")
+        raise RuntimeError("maxpool2x2: needs a channels_last float32 / bfloat16 / float16 CUDA tensor with 16-byte channel groups")
     B, C, H, W = x.shape
     out = torch.empty((B, C, H // 2, W // 2), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
-    rc = _lib.load().cvpce_maxpool2x2_nhwc(_ptr(x), F32 if x.dtype == torch.float32 else BF16, B, H, W, C, _ptr(out), _stream())
+    rc = _lib.load().cvpce_maxpool2x2_nhwc(_ptr(x), _DTYPE_CODE[x.dtype], B, H, W, C, _ptr(out), _stream())
     _lib.check(rc, "cvpce_maxpool2x2_nhwc")
     return out
 
@@ -221,9 +223,9 @@ def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, anti
     boxes = boxes.contiguous().float()
     K = boxes.shape[0]
     S = int(size)
-    dt = F32 if out_dtype == torch.float32 else BF16
-    if out_dtype not in (torch.float32, torch.bfloat16):
-        raise RuntimeError("crop_resize: out_dtype must be float32 or bfloat16")
+    if out_dtype not in _DTYPE_CODE:
+        raise RuntimeError("crop_resize: out_dtype must be float32, bfloat16 or float16")
+    dt = _DTYPE_CODE[out_dtype]
     if channels_last:
         out = torch.empty((K, S, S, 3), dtype=out_dtype, device=boxes.device)
     else:
@@ -260,8 +262,8 @@ def region_pool_embed(feats, regions=None, per_region_l2=False, final_l2=True, e
     _need_cuda("region_pool_embed", *feats)
     B = feats[0].shape[0]
     dtype = feats[0].dtype
-    if dtype not in (torch.float32, torch.bfloat16) or any(f.dtype != dtype or f.shape[0] != B or f.dim() != 4 for f in feats):
-        raise RuntimeError("region_pool_embed: maps must be 4-d, share batch size and dtype (float32 or bfloat16)")
+    if dtype not in _DTYPE_CODE or any(f.dtype != dtype or f.shape[0] != B or f.dim() != 4 for f in feats):
+        raise RuntimeError("region_pool_embed: maps must be 4-d, share batch size and dtype (float32, bfloat16; float16 for dense channels-last MAC)")
     D = sum(f.shape[1] for f in feats)
     if out is None:
         out = torch.empty((B, D), dtype=torch.float32, device=feats[0].device)
@@ -273,7 +275,7 @@ def region_pool_embed(feats, regions=None, per_region_l2=False, final_l2=True, e
         flat = [int(v) for per_map in regions for r in per_map for v in r]
         rg = (ctypes.c_int32 * len(flat))(*flat)
         nr = (ctypes.c_int32 * len(regions))(*[len(r) for r in regions])
-    rc = _lib.load().cvpce_region_pool_embed(maps, len(feats), F32 if dtype == torch.float32 else BF16, B,
+    rc = _lib.load().cvpce_region_pool_embed(maps, len(feats), _DTYPE_CODE[dtype], B,
                                              ctypes.cast(rg, ctypes.c_void_p) if rg is not None else None,
                                              ctypes.cast(nr, ctypes.c_void_p) if nr is not None else None,
                                              1 if per_region_l2 else 0, 1 if final_l2 else 0, float(eps), _ptr(out),

@@ -37,7 +37,7 @@ typedef enum cvpce_status {
   CVPCE_ERR_WORKSPACE = 5      /* workspace pointer null or smaller than *_workspace_bytes() */
 } cvpce_status;
 
-typedef enum cvpce_dtype { CVPCE_F32 = 0, CVPCE_BF16 = 1 } cvpce_dtype;
+typedef enum cvpce_dtype { CVPCE_F32 = 0, CVPCE_BF16 = 1, CVPCE_F16 = 2 } cvpce_dtype; /* F16: crop output, max-pool, dense NHWC MAC */
 typedef enum cvpce_layout { CVPCE_NCHW = 0, CVPCE_NHWC = 1 } cvpce_layout;
 
 /* Thread-local message of the last failing call on this thread ("" if none). */

@@ -665,3 +665,27 @@ def test_sim_topk_scatter_writes_every_target(ops):
     for r in range(2):
         assert torch.equal(gs[r, slot], s) and torch.equal(gidx[r, slot], i)
         assert bool((gs[r, 0] == -7).all()) and bool((gidx[r, 2] == -7).all())   # other slots untouched
+
+
+def test_float16_hand_off_kernels(ops):
+    """Extension mode (--trunk f16): the crop kernel writes IEEE half directly, the max-pool and the dense channels-last MAC
+    read it.  Crops: the fp32 result of the oracle rounded to half; pools / MAC: exact on the half inputs."""
+    img = synth.shelf_image(synth.CROP_IMAGE_SEED, *synth.CROP_IMAGE_HW)
+    boxes = synth.crop_boxes()[:6]
+    want, _ = oracle.crop_resize(img, boxes, 64, True)
+    table = ops.make_image_table([dev(img)])
+    for cl in (False, True):
+        got = ops.crop_resize(table, 1, dev(boxes), None, 64, True, 0.5, None, torch.float16, cl)
+        assert got.dtype == torch.float16 and got.is_contiguous(memory_format=torch.channels_last if cl else torch.contiguous_format)
+        ref16 = torch.from_numpy(want).half()
+        diff = (got.cpu().float() - ref16.float()).abs().max().item()
+        assert diff <= 2 ** -11, diff     # at most one half ulp apart where the fp32 values differ in the last bits
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn((3, 64, 10, 12), device="cuda", generator=g).half().contiguous(memory_format=torch.channels_last)
+    assert torch.equal(ops.maxpool2x2(x), torch.nn.functional.max_pool2d(x, 2, 2))
+    feats = [torch.randn((4, 512, 6, 6), device="cuda", generator=g).half().contiguous(memory_format=torch.channels_last),
+             torch.randn((4, 512, 3, 3), device="cuda", generator=g).half().contiguous(memory_format=torch.channels_last)]
+    want = oracle.region_pool_embed([f.float().cpu().numpy() for f in feats])
+    np.testing.assert_allclose(ops.region_pool_embed(feats).cpu().numpy(), want, rtol=2e-6, atol=1e-7)
+    with pytest.raises(RuntimeError):
+        ops.region_pool_embed([f.contiguous() for f in feats])   # float16 NCHW maps: unsupported, fails loudly

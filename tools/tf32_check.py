@@ -20,12 +20,22 @@ with torch.no_grad():
         if not tf32:
             # gallery: embeddings of other random crops (strict fp32), so that neighbours are as close as random-init allows
             G = torch.cat([enc(torch.nn.functional.interpolate(gal[i:i + 256], size=(256, 256))) for i in range(0, 2048, 256)])
+    # --trunk f16: half weights / activations (10-bit mantissa like TF32), fp32 accumulation, library kernels reading half
+    e16 = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    e16.load_state_dict(enc.state_dict())
+    e16 = e16.to(dev).half().enable_fast_trunk()
+    with torch.no_grad():
+        out["f16"] = e16(x.half())
 a, b = out[False], out[True]
 rel = ((a - b).abs() / a.abs().clamp(min=1e-6))
 print("embedding tf32 vs fp32: max rel %.3e  mean rel %.3e  max abs %.3e  min cosine %.8f" % (
     rel.max().item(), rel.mean().item(), (a - b).abs().max().item(), torch.nn.functional.cosine_similarity(a, b).min().item()))
 sa, ia = classification.similarity_topk(G, a, 5)
-sb, ib = classification.similarity_topk(G, b, 5)
-print("similarity: max abs diff %.3e (rel %.3e); top-1 agreement %.4f, top-5 list agreement %.4f" % (
-    (sa - sb).abs().max().item(), ((sa - sb).abs() / sa.abs()).max().item(), (ia[:, 0] == ib[:, 0]).float().mean().item(),
-    (ia == ib).all(dim=1).float().mean().item()))
+for name, b in (("tf32", out[True]), ("f16", out["f16"])):
+    rel = ((a - b).abs() / a.abs().clamp(min=1e-6))
+    sb, ib = classification.similarity_topk(G, b, 5)
+    print("%s vs fp32: ||d||/||e|| max %.3e, mean elementwise rel %.3e, max abs %.3e, min cosine %.8f | similarity max rel diff %.3e, "
+          "top-1 agreement %.4f, top-5 list agreement %.4f" % (
+              name, ((a - b).norm(dim=1) / a.norm(dim=1)).max().item(), rel.mean().item(), (a - b).abs().max().item(),
+              torch.nn.functional.cosine_similarity(a, b).min().item(), ((sa - sb).abs() / sa.abs()).max().item(),
+              (ia[:, 0] == ib[:, 0]).float().mean().item(), (ia == ib).all(dim=1).float().mean().item()))
