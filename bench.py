@@ -62,6 +62,8 @@ def parse():
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
                     "(800x1066 frame, 5 FPN levels) -> candidate selection -> NMS -> ... instead of scored candidate boxes")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extension-modes", action="store_true", help="skip the short extra pass that also reports the f16-trunk "
+                    "extension mode next to the headline (N = 1, default trunk only)")
     ap.add_argument("--cpu-sample-crops", type=int, default=32)
     return ap.parse_args()
 
@@ -514,6 +516,17 @@ def main():
         line = run_ours_c5(args, world, rank, local)
     else:
         line = run_ours_shelves(args, world, rank, local)
+        if world == 1 and args.trunk == "f32" and not args.strict_fp32 and not args.no_extension_modes and not args.plain_trunk:
+            # reported next to the headline, never instead of it: the same step with the half-precision trunk hand-off
+            # (same 10-bit mantissa as the TF32 convolutions of the headline, same measured deviation)
+            import copy
+            a16 = copy.copy(args)
+            a16.trunk, a16.no_cpu_baseline, a16.steps = "f16", True, max(1, min(args.steps, 2))
+            torch.cuda.empty_cache()
+            l16 = run_ours_shelves(a16, world, rank, local)
+            line["extension_modes"] = {"trunk_f16": {"value": l16["value"], "unit": l16["unit"], "ms_per_step": l16["ms_per_step"],
+                                                     "e2e": l16["e2e"]["value"], "steps": a16.steps,
+                                                     "note": "half weights/activations, fp32 accumulation; not the headline"}}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
