@@ -50,6 +50,9 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p]),
     "cvpce_region_pool_embed": (c_int, [ctypes.POINTER(FeatureMap), c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                         c_float, c_void_p, c_int64, c_void_p]),
+    "cvpce_box_iou": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "cvpce_iou_match": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p,
+                                c_void_p, c_void_p]),
     "cvpce_maxpool2x2_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cvpce_rmac_regions": (c_int, [c_int, c_int, c_int, c_void_p, c_int]),
     "cvpce_l2norm_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_float, c_void_p]),

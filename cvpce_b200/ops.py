@@ -98,6 +98,65 @@ def nms_segments(boxes, scores, seg_stride, seg_counts, iou_threshold=0.5, min_s
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# box IoU + greedy IoU claim  (tv:ops/boxes.py box_iou; cvpce/metrics.py:11-34; cvpce/planograms.py:214-232)
+# ---------------------------------------------------------------------------------------------------------------------
+MATCH_MAX_COLS = 16384
+
+
+def _boxes_f32(name, b):
+    if b.dim() != 2 or b.shape[1] != 4:
+        raise RuntimeError("%s: boxes must be [N,4], got %s" % (name, tuple(b.shape)))
+    return b.contiguous().float()
+
+
+def box_iou(boxes_a, boxes_b):
+    """torchvision.ops.box_iou(boxes_a [Na,4], boxes_b [Nb,4]) -> f32 [Na,Nb], bit-equal to torchvision's fp32 result."""
+    _need_cuda("box_iou", boxes_a, boxes_b)
+    a, b = _boxes_f32("box_iou", boxes_a), _boxes_f32("box_iou", boxes_b)
+    out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
+    rc = _lib.load().cvpce_box_iou(_ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _stream())
+    _lib.check(rc, "cvpce_box_iou")
+    return out
+
+
+def iou_match(row_boxes, col_boxes, iou_threshold=0.5, row_labels=None, col_labels=None, row_offsets=None, col_offsets=None,
+              max_cols=None):
+    """The reference's greedy claim pass (metrics.check_matches / the matching loop of planograms.finalize_via_ransac) without
+    the IoU matrix or its sort: rows in index order mark every still-unmarked column with !(iou < thr) (and equal label).
+
+    One problem by default; pass i32 CSR `row_offsets` / `col_offsets` (device) plus the host bound `max_cols` for a batch of
+    images in one launch.  Returns (row_matched bool [R], col_matched bool [C]).  No host synchronisation."""
+    _need_cuda("iou_match", row_boxes, col_boxes, row_labels, col_labels, row_offsets, col_offsets)
+    r, c = _boxes_f32("iou_match", row_boxes), _boxes_f32("iou_match", col_boxes)
+    dev = r.device
+    if (row_labels is None) != (col_labels is None):
+        raise RuntimeError("iou_match: give both label tensors or neither")
+    if row_labels is not None:
+        row_labels, col_labels = row_labels.contiguous().to(torch.int64), col_labels.contiguous().to(torch.int64)
+        if row_labels.numel() != r.shape[0] or col_labels.numel() != c.shape[0]:
+            raise RuntimeError("iou_match: one label per box expected")
+    if (row_offsets is None) != (col_offsets is None):
+        raise RuntimeError("iou_match: give both offset tensors or neither")
+    if row_offsets is None:
+        row_offsets = torch.tensor([0, r.shape[0]], dtype=torch.int32, device=dev)
+        col_offsets = torch.tensor([0, c.shape[0]], dtype=torch.int32, device=dev)
+        max_cols = c.shape[0]
+    elif max_cols is None:
+        raise RuntimeError("iou_match: max_cols (host upper bound of columns per problem) is required with offsets")
+    row_offsets, col_offsets = row_offsets.contiguous().to(torch.int32), col_offsets.contiguous().to(torch.int32)
+    n_problems = row_offsets.numel() - 1
+    if col_offsets.numel() - 1 != n_problems:
+        raise RuntimeError("iou_match: row_offsets and col_offsets describe different numbers of problems")
+    row_m = torch.zeros(r.shape[0], dtype=torch.uint8, device=dev)
+    col_m = torch.zeros(c.shape[0], dtype=torch.uint8, device=dev)
+    if r.shape[0] and c.shape[0]:
+        rc = _lib.load().cvpce_iou_match(_ptr(r), _ptr(row_labels), _ptr(row_offsets), _ptr(c), _ptr(col_labels), _ptr(col_offsets),
+                                         n_problems, int(max_cols), float(iou_threshold), _ptr(row_m), _ptr(col_m), _stream())
+        _lib.check(rc, "cvpce_iou_match")
+    return row_m.bool(), col_m.bool()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # pre-NMS candidate selection  (tv:models/detection/retinanet.py:527-557, tv:models/detection/_utils.py:183-224)
 # ---------------------------------------------------------------------------------------------------------------------
 BBOX_XFORM_CLIP = math.log(1000.0 / 16)

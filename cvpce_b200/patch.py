@@ -8,7 +8,7 @@ import sys
 
 import torch
 
-from . import classification, datautils, detection, ops, production
+from . import classification, datautils, detection, metrics, ops, planograms, production
 
 _saved = []
 
@@ -86,6 +86,19 @@ def apply(ref=None):
     _swap(rc.MACResNet, "forward", _macresnet_forward)                          # classification.py:78-85
     _swap(rd, "resize_for_classification", _resize_for_classification)          # datautils.py:234
     _swap(rp.ProposalGenerator, "generate_proposals_and_images", _generate_proposals_and_images)  # production.py:16
+    # f3: detection-evaluation matching and the planogram box_iou call site
+    rm = getattr(ref, "metrics", None)
+    if rm is not None:
+        do_calc = rm._do_calculate
+
+        def _calculate_metrics(targets, predictions, confidences, iou_thresholds=(0.5,)):
+            return metrics.calculate_metrics(targets, predictions, confidences, iou_thresholds, do_calculate=do_calc)
+        _swap(rm, "iou_matrices", metrics.iou_matrices)                         # metrics.py:11
+        _swap(rm, "_process_one", metrics.process_one)                          # metrics.py:80 (sync path; the async workers
+        _swap(rm, "calculate_metrics", _calculate_metrics)                      # metrics.py:126  are forked CPU processes)
+    rg = getattr(ref, "planograms", None)
+    if rg is not None and hasattr(rg, "tvops"):
+        _swap(rg, "tvops", planograms.TvopsProxy())                             # planograms.py:224
     # Classifier.classify keeps its signature; the patched version embeds all crops, searches once, syncs once
     rp.Classifier.embed = production.Classifier.embed
     rp.Classifier.prepared_gallery = production.Classifier.prepared_gallery

@@ -286,3 +286,86 @@ def head_from_candidates(boxes, scores, image_hw, seed, frame=GLN_FRAME, backgro
         s = min(max(s, 1e-6), 1 - 1e-6)
         logits[base + slot] = np.log(s / (1 - s))
     return logits.reshape(A, 1), regression, anchors, (np.float32(W / fw), np.float32(H / fh))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# box IoU / greedy matching: detection evaluation (cvpce/metrics.py) and planogram matching (cvpce/planograms.py)
+# ---------------------------------------------------------------------------------------------------------------------
+# the reference's own test data, test/metrics_test.py:5-21 (targets, predictions already in confidence order)
+METRICS_KAT_TARGETS = [
+    [[0, 0, 1, 1], [1, 0, 2, 1], [1, 1, 2, 2]],
+    [[1, 1, 2, 2], [3, 1, 4, 2], [5, 1, 6, 2], [7, 1, 8, 2]],
+    [[0, 0, 5, 5], [5, 5, 10, 10]],
+]
+METRICS_KAT_PREDICTIONS = [
+    [[0, 0, .9, .9], [1.1, 0.1, 1.9, 0.9], [0, 0, 1, 1], [0.9, 0.9, 2.1, 2.1], [3, 3, 4, 4]],
+    [[1, 0, 2, 1], [1, 1, 2, 2], [5, 1, 6, 2], [7, 1.1, 8, 1.9], [9, 9, 10, 10]],
+    [[0, 0, 1, 1], [1, 1, 3, 3], [0.5, 0.5, 4.5, 4.5], [0, 0, 6, 6], [6, 6, 9, 9]],
+]
+MATCH_THRESHOLDS = (0.5, 0.65, 0.75)
+
+
+def detection_eval_case(seed, n_targets, n_extra, duplicates=3, extent=1500.0):
+    """(targets f32 [T,4], predictions f32 [P,4] in descending-confidence order): every target gets `duplicates` jittered
+    predictions of varying quality plus `n_extra` unrelated boxes, shuffled by a random confidence."""
+    rs = np.random.RandomState(seed)
+    xy = rs.uniform(0, extent, size=(n_targets, 2))
+    wh = rs.uniform(40, 220, size=(n_targets, 2))
+    targets = np.concatenate([xy, xy + wh], axis=1).astype(np.float32)
+    preds = []
+    for d in range(duplicates):
+        jit = rs.normal(0, 4.0 + 14.0 * d, size=(n_targets, 4))
+        preds.append(targets + jit)
+    xy = rs.uniform(0, extent, size=(n_extra, 2))
+    wh = rs.uniform(40, 220, size=(n_extra, 2))
+    preds.append(np.concatenate([xy, xy + wh], axis=1))
+    preds = np.concatenate(preds).astype(np.float32)
+    preds[:, 2:] = np.maximum(preds[:, 2:], preds[:, :2])  # keep x2 >= x1, y2 >= y1
+    order = np.argsort(-rs.uniform(size=len(preds)), kind="stable")
+    return targets, np.ascontiguousarray(preds[order])
+
+
+def match_cases():
+    """name -> (targets, predictions): the reference's three test cases, two random images and the empty-ish corners."""
+    cases = {}
+    for i, (t, p) in enumerate(zip(METRICS_KAT_TARGETS, METRICS_KAT_PREDICTIONS)):
+        cases["kat%d" % i] = (np.array(t, dtype=np.float32), np.array(p, dtype=np.float32))
+    cases["image150"] = detection_eval_case(41, 150, 300)
+    cases["image40_dense"] = detection_eval_case(42, 40, 60, duplicates=5, extent=400.0)
+    cases["one_target"] = detection_eval_case(43, 1, 6)
+    return cases
+
+
+def planogram_case(seed, n=60, n_labels=12, missing=9, extra=7):
+    """A planogram (b1, l1) and a detection result (b2, l2) of the same shelf under a mild projective map: `missing` products
+    are absent from the detections, `extra` detections have no planogram counterpart, a few detections carry a wrong label.
+    Returns b1, l1, b2, l2 (labels as strings, like the reference's annotations) and the list of true (i, j) pairs."""
+    rs = np.random.RandomState(seed)
+    cols = 10
+    b1 = []
+    for i in range(n):
+        r, c = divmod(i, cols)
+        x, y = 40 + c * 130 + rs.uniform(-6, 6), 30 + r * 190 + rs.uniform(-6, 6)
+        b1.append([x, y, x + rs.uniform(90, 120), y + rs.uniform(140, 175)])
+    b1 = np.array(b1, dtype=np.float32)
+    l1 = ["sku%02d" % rs.randint(n_labels) for _ in range(n)]
+    Hm = np.array([[1.9, 0.03, 55.0], [-0.02, 1.85, 20.0], [1e-5, 2e-5, 1.0]])
+
+    def proj(x, y):
+        v = Hm @ np.array([x, y, 1.0])
+        return v[:2] / v[2]
+    present = np.sort(rs.permutation(n)[:n - missing])
+    b2, l2, pairs = [], [], []
+    for j, i in enumerate(present):
+        p1, p2 = proj(*b1[i, :2]), proj(*b1[i, 2:])
+        b2.append(np.concatenate([p1, p2]) + rs.normal(0, 3.0, size=4))
+        l2.append(l1[i] if rs.uniform() > 0.08 else "sku%02d" % rs.randint(n_labels))
+        pairs.append((int(i), j))
+    for _ in range(extra):
+        i = rs.randint(n)
+        p1, p2 = proj(*b1[i, :2]), proj(*b1[i, 2:])
+        b2.append(np.concatenate([p1, p2]) + rs.normal(0, 25.0, size=4))   # overlapping double detections
+        l2.append(l1[i])
+    b2 = np.array(b2, dtype=np.float32)
+    solution = [pairs[t] for t in rs.permutation(len(pairs))[:14] if l2[pairs[t][1]] == l1[pairs[t][0]]]
+    return b1, l1, b2, l2, solution

@@ -183,6 +183,35 @@ CVPCE_API int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, int
 CVPCE_API int cvpce_l2norm_rows(float* x, int B, int D, int64_t stride, float eps, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * f3  Pairwise box IoU and the greedy IoU claim pass (detection evaluation; planogram expected-vs-detected matching).
+ * Replaces: tv:ops/boxes.py box_iou called from cvpce/metrics.py:11-13 (iou_matrices) and cvpce/planograms.py:224;
+ *           the Python loops over the sorted matrix at cvpce/metrics.py:15-34 (check_matches) and
+ *           cvpce/planograms.py:214-232 (inside finalize_via_ransac, feeding the second-round re-classification of
+ *           cvpce/production.py:101-115).
+ *
+ * cvpce_box_iou: iou f32 [n_a, n_b] row-major = inter / ((area_a + area_b) - inter), area = (x2-x1)*(y2-y1),
+ * inter = max(w,0)*max(h,0), IEEE fp32 without contraction: bit-equal to torchvision's matrix (0/0 = NaN).
+ * Boxes f32 [n,4] xyxy, 16-byte aligned.
+ *
+ * cvpce_iou_match: problem b (one image) owns rows [row_offsets[b], row_offsets[b+1]) and columns
+ * [col_offsets[b], col_offsets[b+1]) (i32 CSR, device).  Rows are visited in index order; row i marks EVERY column j of
+ * its problem that is not marked yet, has the row's label (when labels are given: i64, both arrays or neither) and has
+ * !(iou_ij < iou_threshold) in fp32 (so a NaN IoU claims, as in the reference where NaN sorts first and never breaks the
+ * walk); row_matched[i] = 1 iff it marked at least one, col_matched[j] = 1 iff some row marked it.  This is exactly what
+ * the reference's loops compute: they `continue` past used columns and never stop after the first hit, so the descending
+ * walk order inside a row is immaterial.  check_matches: rows = predictions in confidence order, columns = targets,
+ * true_positive = row_matched, false_positive = 1 - row_matched.  finalize_via_ransac: rows = projected planogram boxes,
+ * columns = detections, labels = the integer label ids, matched_expected = row_matched, matched_actual = col_matched.
+ * max_cols [host]: upper bound of the columns of any one problem (<= CVPCE_MATCH_MAX_COLS); the IoU matrix is never
+ * written to memory.  row_matched u8 [total rows], col_matched u8 [total cols].
+ */
+#define CVPCE_MATCH_MAX_COLS 16384
+CVPCE_API int cvpce_box_iou(const float* boxes_a, int n_a, const float* boxes_b, int n_b, float* iou, void* stream);
+CVPCE_API int cvpce_iou_match(const float* row_boxes, const int64_t* row_labels, const int32_t* row_offsets,
+                    const float* col_boxes, const int64_t* col_labels, const int32_t* col_offsets, int n_problems,
+                    int max_cols, float iou_threshold, uint8_t* row_matched, uint8_t* col_matched, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * a7 (driving the torch trunk)  2x2 / stride-2 max pooling of a channels-last feature map.
  * Replaces: nn.MaxPool2d(kernel_size=2, stride=2) between the convolutions of the VGG16 trunk (tv:models/vgg.py make_layers,
  *           cfg 'D' entries 'M'; reached from cvpce/models/classification.py:31-37 MACVGG.block1 / block2).  The convolutions

@@ -212,3 +212,25 @@ def postprocess_detections(logits, regression, anchors, image_sizes, score_thres
         keep = nms(boxes, scores, nms_thresh)[:detections_per_img]
         res.append((boxes[keep], scores[keep], labels[keep]))
     return res
+
+
+def box_iou(a, b):
+    """tv:ops/boxes.py box_iou (cvpce/metrics.py:11-13, cvpce/planograms.py:224): f32 [Na,Nb]."""
+    a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 4)
+    b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 4)
+    out = np.empty((a.shape[0], b.shape[0]), dtype=np.float32)
+    lib().oracle_box_iou(_p(a), ctypes.c_int(a.shape[0]), _p(b), ctypes.c_int(b.shape[0]), _p(out))
+    return out
+
+
+def iou_match(rows, cols, iou_threshold=0.5, row_labels=None, col_labels=None):
+    """The reference's sorted greedy walk (cvpce/metrics.py:15-34; cvpce/planograms.py:214-232) -> (row_matched, col_matched) bool."""
+    rows = np.ascontiguousarray(rows, dtype=np.float32).reshape(-1, 4)
+    cols = np.ascontiguousarray(cols, dtype=np.float32).reshape(-1, 4)
+    rl = None if row_labels is None else np.ascontiguousarray(row_labels, dtype=np.int64)
+    cl = None if col_labels is None else np.ascontiguousarray(col_labels, dtype=np.int64)
+    rm = np.zeros(rows.shape[0], dtype=np.uint8)
+    cm = np.zeros(cols.shape[0], dtype=np.uint8)
+    lib().oracle_iou_match(_p(rows), None if rl is None else _p(rl), ctypes.c_int(rows.shape[0]), _p(cols),
+                           None if cl is None else _p(cl), ctypes.c_int(cols.shape[0]), ctypes.c_float(iou_threshold), _p(rm), _p(cm))
+    return rm.astype(bool), cm.astype(bool)

@@ -178,6 +178,37 @@ def golden_head(ref):
     print("head:", {k: v.shape for k, v in out.items() if k.endswith(("cand_scores", "det_scores", "cand_count"))})
 
 
+def golden_match(ref):
+    """the reference's detection-evaluation matching (metrics.iou_matrices + check_matches) and the
+    expected-vs-detected matching inside planograms.finalize_via_ransac (run for real, cv2 RANSAC included; the projected
+    positions it matches on are stored because they come out of cv2)."""
+    import cvpce.metrics as metrics
+    import cvpce.planograms as planograms
+    out = {}
+    for name, (targets, preds) in synth.match_cases().items():
+        t, p = torch.from_numpy(targets), torch.from_numpy(preds)
+        ious, idx = metrics.iou_matrices(t, p)                         # metrics.py:11-13
+        out[name + "/iou"] = torchvision.ops.box_iou(p, t).numpy()
+        out[name + "/sorted_iou"] = ious.numpy()
+        for thr in synth.MATCH_THRESHOLDS:
+            tp, fp = metrics.check_matches(ious, idx, thr)             # metrics.py:15-34
+            assert torch.equal(tp + fp, torch.ones_like(tp))
+            out[name + "/tp_%g" % thr] = tp.numpy().astype(np.uint8)
+    for seed in (51, 52):
+        b1, l1, b2, l2, solution = synth.planogram_case(seed)
+        for thr in (0.5, 0.8):
+            res = planograms.finalize_via_ransac(solution, torch.from_numpy(b1), torch.from_numpy(b2), l1, l2, iou_threshold=thr,
+                                                 return_matched_actual=True, return_expected_positions=True)
+            matched_expected, matched_actual, expected_positions, missing_expected = res[0], res[1], res[2], res[3]
+            key = "planogram%d_%g" % (seed, thr)
+            out[key + "/expected_positions"] = expected_positions.numpy()
+            out[key + "/matched_expected"] = matched_expected.numpy().astype(np.uint8)
+            out[key + "/matched_actual"] = matched_actual.numpy().astype(np.uint8)
+            out[key + "/missing_expected"] = missing_expected.numpy()
+    np.savez_compressed(os.path.join(OUT, "match.npz"), **out)
+    print("match:", {k: int(v.sum()) for k, v in out.items() if "/tp_" in k or "/matched_" in k})
+
+
 def main():
     if not shim.available():
         sys.exit("reference tree not present; golden vectors can only be regenerated in the authoring container")
@@ -191,6 +222,7 @@ def main():
     golden_nn(ref)
     golden_classify(ref)
     golden_head(ref)
+    golden_match(ref)
     with open(os.path.join(OUT, "VERSIONS.txt"), "w") as f:
         f.write("torch %s\ntorchvision %s\nnumpy %s\nreference commit 7509e7d (laitalaj/cvpce)\n" %
                 (torch.__version__, torchvision.__version__, np.__version__))

@@ -442,3 +442,69 @@ API int64_t oracle_select_level(const float* logits, const float* regression, co
   free(cand);
   return k;
 }
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Box IoU and the greedy claim walk over its sorted rows.
+ * tv:ops/boxes.py box_iou / _box_inter_union: area = (x2-x1)*(y2-y1); lt = max, rb = min, wh = (rb-lt).clamp(min=0);
+ * inter = w*h; union = area_a[:,None] + area_b - inter; iou = inter/union (fp32).  Called from cvpce/metrics.py:11-13
+ * and cvpce/planograms.py:224.
+ * --------------------------------------------------------------------------------------------------------------- */
+static float tv_iou(const float* a, const float* b) {
+  const float area_a = (a[2] - a[0]) * (a[3] - a[1]);
+  const float area_b = (b[2] - b[0]) * (b[3] - b[1]);
+  const float ltx = a[0] > b[0] ? a[0] : b[0], lty = a[1] > b[1] ? a[1] : b[1];
+  const float rbx = a[2] < b[2] ? a[2] : b[2], rby = a[3] < b[3] ? a[3] : b[3];
+  float w = rbx - ltx, h = rby - lty;
+  if (w < 0.f) w = 0.f;
+  if (h < 0.f) h = 0.f;
+  const float inter = w * h;
+  const float uni = (area_a + area_b) - inter;
+  return inter / uni;
+}
+
+API void oracle_box_iou(const float* a, int n_a, const float* b, int n_b, float* out) {
+  for (int i = 0; i < n_a; ++i)
+    for (int j = 0; j < n_b; ++j) out[(size_t)i * n_b + j] = tv_iou(a + 4 * i, b + 4 * j);
+}
+
+typedef struct { float v; int32_t j; } ioukey;
+
+/* torch.sort(descending=True): NaN counts as the largest value; order among equal values is irrelevant to the walk */
+static int cmp_iou_desc(const void* x, const void* y) {
+  const ioukey* p = (const ioukey*)x;
+  const ioukey* q = (const ioukey*)y;
+  const int pn = p->v != p->v, qn = q->v != q->v;
+  if (pn || qn) return qn - pn;
+  if (p->v > q->v) return -1;
+  if (p->v < q->v) return 1;
+  return (p->j > q->j) - (p->j < q->j);
+}
+
+/* cvpce/metrics.py:15-34 (check_matches) and cvpce/planograms.py:214-232, restated literally: for each row, the IoUs
+ * against its eligible columns are sorted descending, the walk stops at the first iou < thr (fp32 comparison: a 0-dim
+ * fp32 tensor against a Python float), skips used columns and marks every other one -- it does NOT stop at the first
+ * hit.  Labels (nullable): planograms.py:214-223 restricts row i to the columns with its label; visiting label by label
+ * equals visiting the rows in index order because columns of different labels are disjoint. */
+API void oracle_iou_match(const float* rows, const int64_t* row_labels, int n_rows, const float* cols, const int64_t* col_labels,
+                          int n_cols, float thr, uint8_t* row_matched, uint8_t* col_matched) {
+  ioukey* keys = (ioukey*)malloc(sizeof(ioukey) * (size_t)(n_cols > 0 ? n_cols : 1));
+  memset(row_matched, 0, (size_t)n_rows);
+  memset(col_matched, 0, (size_t)n_cols);
+  for (int i = 0; i < n_rows; ++i) {
+    int m = 0;
+    for (int j = 0; j < n_cols; ++j) {
+      if (row_labels && col_labels && row_labels[i] != col_labels[j]) continue;
+      keys[m].v = tv_iou(rows + 4 * i, cols + 4 * j);
+      keys[m].j = j;
+      ++m;
+    }
+    qsort(keys, (size_t)m, sizeof(ioukey), cmp_iou_desc);
+    for (int t = 0; t < m; ++t) {
+      if (keys[t].v < thr) break;
+      if (col_matched[keys[t].j]) continue;
+      col_matched[keys[t].j] = 1;
+      row_matched[i] = 1;
+    }
+  }
+  free(keys);
+}

@@ -16,7 +16,7 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def golden():
-    return {name: np.load(os.path.join(GOLDEN, name + ".npz")) for name in ("nms", "crops", "mac", "nn", "classify", "head")}
+    return {name: np.load(os.path.join(GOLDEN, name + ".npz")) for name in ("nms", "crops", "mac", "nn", "classify", "head", "match")}
 
 
 @pytest.fixture(scope="session")

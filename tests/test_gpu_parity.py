@@ -689,3 +689,127 @@ def test_float16_hand_off_kernels(ops):
     np.testing.assert_allclose(ops.region_pool_embed(feats).cpu().numpy(), want, rtol=2e-6, atol=1e-7)
     with pytest.raises(RuntimeError):
         ops.region_pool_embed([f.contiguous() for f in feats])   # float16 NCHW maps: unsupported, fails loudly
+
+
+# ------------------------------------------------------------------------------ f3: box IoU + greedy IoU claim (matching)
+def test_box_iou_bit_equal_to_torchvision_golden_and_oracle(ops, golden):
+    g = golden["match"]
+    for name, (targets, preds) in synth.match_cases().items():
+        got = ops.box_iou(dev(preds), dev(targets)).cpu().numpy()
+        assert np.array_equal(got.view(np.uint32), g[name + "/iou"].view(np.uint32)), name
+    rs = np.random.RandomState(5)
+    for na, nb in ((1, 1), (3, 5), (257, 1023), (1000, 1024), (64, 4099)):   # unaligned and vector-store row pitches
+        a, _ = synth.random_boxes(rs.randint(1 << 30), na, extent=400.0)
+        b, _ = synth.random_boxes(rs.randint(1 << 30), nb, extent=400.0)
+        b[::7, 2:] = b[::7, :2]                                               # zero-area boxes
+        a[0] = b[0]
+        got = ops.box_iou(dev(a), dev(b)).cpu().numpy()
+        want = oracle.box_iou(a, b)
+        nan = np.isnan(want)                                                   # 0/0: NaN on both sides (payload bits differ by ISA)
+        assert nan.any() and np.array_equal(np.isnan(got), nan), (na, nb)
+        assert np.array_equal(got.view(np.uint32)[~nan], want.view(np.uint32)[~nan]), (na, nb)
+    assert ops.box_iou(dev(np.zeros((0, 4), np.float32)), dev(b)).shape == (0, 4099)
+    assert ops.box_iou(dev(a), dev(np.zeros((0, 4), np.float32))).shape == (64, 0)
+
+
+def test_iou_match_equals_reference_golden(ops, golden):
+    g = golden["match"]
+    cases = synth.match_cases()
+    for name, (targets, preds) in cases.items():
+        for thr in synth.MATCH_THRESHOLDS:
+            tp, used = ops.iou_match(dev(preds), dev(targets), thr)
+            assert np.array_equal(tp.cpu().numpy().astype(np.uint8), g[name + "/tp_%g" % thr]), (name, thr)
+            assert np.array_equal(used.cpu().numpy(), oracle.iou_match(preds, targets, thr)[1]), (name, thr)
+    # the reference test's own known answer (test/metrics_test.py:61-68)
+    tp, _ = ops.iou_match(dev(cases["kat0"][1]), dev(cases["kat0"][0]), 0.65)
+    assert tp.int().tolist() == [1, 0, 0, 1, 0]
+    # all images in ONE launch (CSR offsets), plus an image without predictions and one without targets
+    names = list(cases)
+    rows = [cases[n][1] for n in names] + [np.zeros((0, 4), np.float32), cases["kat1"][1]]
+    cols = [cases[n][0] for n in names] + [cases["kat1"][0], np.zeros((0, 4), np.float32)]
+    ro = np.cumsum([0] + [len(r) for r in rows]).astype(np.int32)
+    co = np.cumsum([0] + [len(c) for c in cols]).astype(np.int32)
+    for thr in synth.MATCH_THRESHOLDS:
+        tp, used = ops.iou_match(dev(np.concatenate(rows)), dev(np.concatenate(cols)), thr, row_offsets=dev(ro), col_offsets=dev(co),
+                                 max_cols=max(len(c) for c in cols))
+        tp, used = tp.cpu().numpy(), used.cpu().numpy()
+        for i, n in enumerate(names):
+            assert np.array_equal(tp[ro[i]:ro[i + 1]].astype(np.uint8), g[n + "/tp_%g" % thr]), (n, thr)
+        assert not tp[ro[-2]:].any() and not used[co[-3]:].any()
+
+
+def test_iou_match_planogram_labels_equal_reference_golden(ops, golden):
+    from cvpce_b200 import planograms
+    g = golden["match"]
+    for seed in (51, 52):
+        b1, l1, b2, l2, _ = synth.planogram_case(seed)
+        for thr in (0.5, 0.8):
+            key = "planogram%d_%g" % (seed, thr)
+            exp = torch.from_numpy(g[key + "/expected_positions"])
+            me, ma, missing = planograms.match_expected(exp, torch.from_numpy(b2), l1, l2, thr)   # host tensors, like the reference
+            assert not me.is_cuda
+            assert np.array_equal(me.numpy().astype(np.uint8), g[key + "/matched_expected"]), key
+            assert np.array_equal(ma.numpy().astype(np.uint8), g[key + "/matched_actual"]), key
+            assert np.array_equal(missing.numpy(), g[key + "/missing_expected"]), key
+
+
+def test_iou_match_edges_and_large_problem(ops):
+    # fp32 threshold comparison, NaN claims, no stop after the first hit (see tests/test_match_golden.py for the reference facts)
+    tp, _ = ops.iou_match(dev(np.array([[0, 0, 10, 10]], np.float32)), dev(np.array([[0, 0, 7, 10]], np.float32)), 0.7)
+    assert tp.tolist() == [True]
+    z = dev(np.array([[5, 5, 5, 5]], np.float32))
+    tp, used = ops.iou_match(z, z, 0.5)
+    assert tp.tolist() == [True] and used.tolist() == [True]
+    rows = dev(np.array([[0, 0, 10, 10], [0, 0, 10, 10]], np.float32))
+    cols = dev(np.array([[0, 0, 10, 10], [0, 0, 10, 9]], np.float32))
+    tp, used = ops.iou_match(rows, cols, 0.5)
+    assert tp.tolist() == [True, False] and used.tolist() == [True, True]
+    tp, used = ops.iou_match(dev(np.zeros((0, 4), np.float32)), cols, 0.5)
+    assert tp.numel() == 0 and used.tolist() == [False, False]
+    tp, used = ops.iou_match(rows, dev(np.zeros((0, 4), np.float32)), 0.5)
+    assert tp.tolist() == [False, False] and used.numel() == 0
+    # several panels of rows, several words of columns, labels, dense overlaps
+    rs = np.random.RandomState(9)
+    for n_rows, n_cols, n_labels, thr in ((5000, 3000, 0, 0.3), (777, 5001, 6, 0.2), (33, 16384, 0, 0.1), (2000, 31, 3, 0.5)):
+        r, _ = synth.random_boxes(rs.randint(1 << 30), n_rows, extent=600.0)
+        c, _ = synth.random_boxes(rs.randint(1 << 30), n_cols, extent=600.0)
+        rl = cl = None
+        if n_labels:
+            rl, cl = rs.randint(n_labels, size=n_rows).astype(np.int64), rs.randint(n_labels, size=n_cols).astype(np.int64)
+        tp, used = ops.iou_match(dev(r), dev(c), thr, None if rl is None else dev(rl), None if cl is None else dev(cl))
+        want_tp, want_used = oracle.iou_match(r, c, thr, rl, cl)
+        assert np.array_equal(tp.cpu().numpy(), want_tp) and np.array_equal(used.cpu().numpy(), want_used), (n_rows, n_cols)
+        assert 0 < want_tp.sum() and 0 < want_used.sum() < n_cols
+    with pytest.raises(RuntimeError):
+        ops.iou_match(rows, dev(np.zeros((16385, 4), np.float32)), 0.5)
+    with pytest.raises(RuntimeError):
+        ops.iou_match(rows.cpu(), cols, 0.5)
+
+
+def test_metrics_mirror_process_batch(ops, golden):
+    from cvpce_b200 import metrics
+    g = golden["match"]
+    cases = synth.match_cases()
+    names = list(cases)
+    rs = np.random.RandomState(3)
+    targets, preds, confs, perms = [], [], [], []
+    for n in names:                      # hand the predictions over UNSORTED with their confidences, like detection_eval.py does
+        t, p = cases[n]
+        conf = np.sort(rs.uniform(size=len(p)).astype(np.float32))[::-1].copy()
+        perm = rs.permutation(len(p))
+        targets.append(torch.from_numpy(t))
+        preds.append(torch.from_numpy(p[perm]))
+        confs.append(torch.from_numpy(conf[perm]))
+    res = metrics.process_batch(targets, preds, confs, synth.MATCH_THRESHOLDS)
+    for n, (m, conf, n_t), t in zip(names, res, targets):
+        assert n_t == len(t) and bool((conf[:-1] >= conf[1:]).all())
+        for thr in synth.MATCH_THRESHOLDS:
+            tp = m[thr]["true_positives"]
+            assert tp.dtype == torch.float32 and not tp.is_cuda
+            assert np.array_equal(tp.numpy().astype(np.uint8), g[n + "/tp_%g" % thr]), (n, thr)
+            assert torch.equal(tp + m[thr]["false_positives"], torch.ones_like(tp))
+            assert float(m[thr]["recall_300"]) == pytest.approx(float(tp[:300].sum()) / len(t))
+    s, i = metrics.iou_matrices(targets[0], torch.from_numpy(cases[names[0]][1]))
+    assert np.array_equal(s.numpy(), g[names[0] + "/sorted_iou"])
+    one = metrics.process_one(targets[3], preds[3], confs[3], (0.5,))
+    assert torch.equal(one[0][0.5]["true_positives"], res[3][0][0.5]["true_positives"])

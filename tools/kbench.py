@@ -11,6 +11,7 @@ import sys
 
 import numpy as np
 import torch
+import torchvision
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -208,6 +209,38 @@ def bench_sim(args):
         report("sim_topk bf16-only Q=%d G=%d D=%d k=%d" % (Q, G, D, k), ms, best, flops=fl)
 
 
+def bench_match(args):
+    """f3: torchvision-exact box IoU matrix and the greedy claim pass of detection evaluation (C4 density: 512 images x
+    (1000 detections vs 150 targets)); the oracle's literal sort-and-walk restatement on one host core beside it."""
+    import time
+    import oracle
+    dev = "cuda"
+    for na, nb in ((1000, 150), (8192, 8192), (20000, 16384)):
+        a, _ = synth.random_boxes(1, na, extent=1500.0)
+        b, _ = synth.random_boxes(2, nb, extent=1500.0)
+        ad, bd = torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev)
+        ms, best = timeit(lambda: ops.box_iou(ad, bd), args.iters)
+        report("box_iou %d x %d" % (na, nb), ms, best, 16.0 * (na + nb) + 4.0 * na * nb)
+        ms, best = timeit(lambda: torchvision.ops.box_iou(ad, bd), args.iters)
+        report("  torchvision.ops.box_iou (CUDA, eager) same shape", ms, best, 16.0 * (na + nb) + 4.0 * na * nb)
+    n_img = args.stress_images
+    rows, cols = [], []
+    for i in range(n_img):
+        t, p = synth.detection_eval_case(700 + i, 150, 1000 - 150 * 3)
+        rows.append(p)
+        cols.append(t)
+    ro = torch.from_numpy(np.cumsum([0] + [len(r) for r in rows]).astype(np.int32)).to(dev)
+    co = torch.from_numpy(np.cumsum([0] + [len(c) for c in cols]).astype(np.int32)).to(dev)
+    rd, cd = torch.from_numpy(np.concatenate(rows)).to(dev), torch.from_numpy(np.concatenate(cols)).to(dev)
+    ms, best = timeit(lambda: ops.iou_match(rd, cd, 0.5, row_offsets=ro, col_offsets=co, max_cols=150), args.iters)
+    t0 = time.perf_counter()
+    for i in range(8):
+        oracle.iou_match(rows[i], cols[i], 0.5)
+    cpu_ms = (time.perf_counter() - t0) / 8 * 1e3
+    report("iou_match %d images x (1000 x 150), one launch" % n_img, ms, best, 16.0 * (rd.shape[0] + cd.shape[0]) + rd.shape[0] + cd.shape[0],
+           images_per_s=round(n_img / ms * 1e3, 1), oracle_cpu_ms_per_image=round(cpu_ms, 3))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("which", nargs="*", default=["nms", "select", "crop", "pool", "prep", "sim"])
@@ -219,7 +252,7 @@ def main():
     args = ap.parse_args()
     torch.cuda.set_device(0)
     for w in args.which:
-        {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
+        {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "match": bench_match, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
 
 
 if __name__ == "__main__":
