@@ -54,3 +54,26 @@ def test_reference_own_tests_pass_through_shim(ref, tmp_path):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     mod.test_nearest_neigbors()
+
+
+def test_matching_oracle_equals_reference_on_fresh_inputs(ref):
+    """oracle box_iou / iou_match against the live metrics.iou_matrices + check_matches (metrics.py:11-34) on cases that
+    are not in the golden file, and the reference's own metrics tests run unmodified through the shim."""
+    import importlib.util
+    import sys
+    import cvpce.metrics as metrics
+    for seed, thr in ((91, 0.5), (92, 0.3), (93, 0.9)):
+        t, p = synth.detection_eval_case(seed, 25, 40, duplicates=4, extent=500.0)
+        ious, idx = metrics.iou_matrices(torch.from_numpy(t), torch.from_numpy(p))
+        tp, fp = metrics.check_matches(ious, idx, thr)
+        assert np.array_equal(-np.sort(-oracle.box_iou(p, t), axis=1), ious.numpy())
+        got, _ = oracle.iou_match(p, t, thr)
+        assert np.array_equal(got, tp.numpy().astype(bool)), (seed, thr)
+    sys.modules["thesis"] = ref
+    sys.modules["thesis.metrics"] = metrics
+    spec = importlib.util.spec_from_file_location("ref_metrics_test", shim.REFERENCE_ROOT + "/test/metrics_test.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.test_iou_matrices()
+    mod.test_iou_matrices_2()
+    mod.test_check_matches()
