@@ -61,6 +61,9 @@ def parse():
                     "ranks: stored by the selection kernel into every peer's gather buffer over NVLink, or an NCCL all-gather")
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
                     "(800x1066 frame, 5 FPN levels) -> candidate selection -> NMS -> ... instead of scored candidate boxes")
+    ap.add_argument("--e2e-serial", action="store_true", help="e2e leg: upload all images before the step instead of overlapping "
+                    "the upload with the step's own compute")
+    ap.add_argument("--upload-group", type=int, default=4, help="e2e leg: shelf images per upload group")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extension-modes", action="store_true", help="skip the short extra pass that also reports the f16-trunk "
                     "extension mode next to the headline (N = 1, default trunk only)")
@@ -268,12 +271,13 @@ def run_ours_shelves(args, world, rank, local):
         scale_d = torch.tensor([[float(scale[0]), float(scale[1])]] * n_shelves, dtype=torch.float32, device=device)
         head_d = (head_h[0].to(device), head_h[1].to(device))
 
-    def run_step(imgs, cand=None, head=None):
+    def run_step(imgs, cand=None, head=None, uploads=None):
         if args.from_head:
             lg, rg = head if head is not None else head_d
-            return hp.step_from_head(imgs, list(lg.split(n_per, dim=1)), list(rg.split(n_per, dim=1)), anchors_d, frame_d, scale_d)
+            return hp.step_from_head(imgs, list(lg.split(n_per, dim=1)), list(rg.split(n_per, dim=1)), anchors_d, frame_d, scale_d,
+                                     uploads=uploads)
         b, sc, sg = cand if cand is not None else (boxes_d, scores_d, seg_d)
-        return hp.step(imgs, b, sc, sg, max_n)
+        return hp.step(imgs, b, sc, sg, max_n, uploads=uploads)
 
     # -------- device-resident timing ("value")
     for _ in range(args.warmup):
@@ -305,12 +309,17 @@ def run_ours_shelves(args, world, rank, local):
     del images
 
     def e2e_step():
-        imgs = [im.to(device, non_blocking=True) for im in images_h]
+        # the step's images go up on the library's copy stream in groups (HotPath.upload_images) and are consumed group by
+        # group, so this step's own transfer overlaps this step's convolutions; --e2e-serial uploads everything first
+        if args.e2e_serial:
+            imgs, ups = [im.to(device, non_blocking=True) for im in images_h], None
+        else:
+            imgs, ups = hp.upload_images(images_h, args.upload_group)
         if args.from_head:
-            o = run_step(imgs, head=(head_h[0].to(device, non_blocking=True), head_h[1].to(device, non_blocking=True)))
+            o = run_step(imgs, head=(head_h[0].to(device, non_blocking=True), head_h[1].to(device, non_blocking=True)), uploads=ups)
         else:
             o = run_step(imgs, cand=(boxes_p.to(device, non_blocking=True), scores_p.to(device, non_blocking=True),
-                                     seg_p.to(device, non_blocking=True)))
+                                     seg_p.to(device, non_blocking=True)), uploads=ups)
         idx = o["topk_idx"].cpu()
         bx = o["boxes"].cpu()
         return idx, bx
@@ -376,7 +385,9 @@ def run_ours_shelves(args, world, rank, local):
                    "l2": "inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9),
                    "parallelism": "dp%d (independent images, no data-path collective)" % world},
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": round(ms_e2e / args.steps, 3)},
+                "ms_per_step": round(ms_e2e / args.steps, 3),
+                "upload": "all images before the step" if args.e2e_serial else
+                          "copy stream, groups of %d shelves, overlapped with the step's own compute (HotPath.upload_images)" % args.upload_group},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,

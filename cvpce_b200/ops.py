@@ -63,6 +63,9 @@ def nms_batched(boxes, scores, seg_offsets, max_n, iou_threshold=0.5, min_score=
     if box_scale is not None:
         box_scale = box_scale.contiguous().float()
     lib = _lib.load()
+    if total == 0:  # no candidate in any image: torch hands out null pointers for empty tensors, nothing to launch
+        counts.zero_()
+        return keep, counts, kept_boxes, kept_scores
     rc = lib.cvpce_nms_batched(_ptr(boxes), _ptr(scores), _ptr(seg_offsets), n_images, int(max_n),
                                threshold_as_cpu_op(float(iou_threshold)),
                                float("-inf") if min_score is None else float(min_score), int(max_keep),
@@ -276,19 +279,22 @@ def make_image_table(images):
 
 
 def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, antialias=True, pad_value=0.5, affine=None,
-                out_dtype=torch.float32, channels_last=False, return_valid=False):
-    """All crops of a batch in one launch. boxes f32[K,4] (device) -> [K,3,S,S] (or a channels_last view of [K,S,S,3])."""
-    _need_cuda("crop_resize", image_table, boxes, box_image_idx)
+                out_dtype=torch.float32, channels_last=False, return_valid=False, out=None):
+    """All crops of a batch in one launch. boxes f32[K,4] (device) -> [K,3,S,S] (or a channels_last view of [K,S,S,3]).
+    `out`: optional preallocated PHYSICAL buffer ([K,S,S,3] when channels_last, else [K,3,S,S]; contiguous), e.g. a row slice
+    of a larger crop tensor that is filled group by group."""
+    _need_cuda("crop_resize", image_table, boxes, box_image_idx, out)
     boxes = boxes.contiguous().float()
     K = boxes.shape[0]
     S = int(size)
     if out_dtype not in _DTYPE_CODE:
         raise RuntimeError("crop_resize: out_dtype must be float32, bfloat16 or float16")
     dt = _DTYPE_CODE[out_dtype]
-    if channels_last:
-        out = torch.empty((K, S, S, 3), dtype=out_dtype, device=boxes.device)
-    else:
-        out = torch.empty((K, 3, S, S), dtype=out_dtype, device=boxes.device)
+    shape = (K, S, S, 3) if channels_last else (K, 3, S, S)
+    if out is None:
+        out = torch.empty(shape, dtype=out_dtype, device=boxes.device)
+    elif tuple(out.shape) != shape or out.dtype != out_dtype or not out.is_contiguous():
+        raise RuntimeError("crop_resize: out must be a contiguous %s tensor of shape %s" % (out_dtype, shape))
     valid = torch.empty(K, dtype=torch.int32, device=boxes.device) if return_valid else None
     if box_image_idx is not None:
         box_image_idx = box_image_idx.contiguous().to(torch.int32)

@@ -68,6 +68,7 @@ class HotPath:
         self.rmac_levels = rmac_levels
         self.n_streams = n_streams
         self._streams = None
+        self._copy_stream = self._stage = self._stage_key = self._stage_free = None
         self.affine = classification.tanh_normalize_affine()  # scale_to_tanh + MACVGG normalisation folded into the crop kernel
         self.launches = 0  # launches of OUR kernels (library calls), counted per call site
         self.timer = _NoTimer()
@@ -78,7 +79,7 @@ class HotPath:
         return self._streams
 
     @torch.no_grad()
-    def step(self, images, cand_boxes, cand_scores, seg_offsets, max_n):
+    def step(self, images, cand_boxes, cand_scores, seg_offsets, max_n, uploads=None):
         """images: list of CUDA f32 [3,H,W]; cand_boxes f32[total,4] / cand_scores f32[total] / seg_offsets i32[B+1] on the
         device (original-image pixels); max_n: host upper bound of candidates per image.
         Returns dict(boxes f32[K,4], image_idx i32[K], counts i32[B] (host), topk_idx i64[K,k], topk_sim f32[K,k], embedding)."""
@@ -88,11 +89,11 @@ class HotPath:
             keep, counts, kept_boxes, _ = ops.nms_batched(cand_boxes, cand_scores, seg_offsets, max_n, self.iou_threshold,
                                                           self.min_score, self.detections_per_img, want_boxes=True)
         self.launches += 1
-        return self._classify_kept(images, counts, kept_boxes, seg_offsets[:-1].to(torch.int64))
+        return self._classify_kept(images, counts, kept_boxes, seg_offsets[:-1].to(torch.int64), uploads)
 
     @torch.no_grad()
     def step_from_head(self, images, cls_logits, bbox_regression, anchors, frame_sizes, box_scale, score_thresh=0.05,
-                       topk_candidates=1000):
+                       topk_candidates=1000, uploads=None):
         """The same step starting one stage earlier: the detector head's per-level outputs of the batch
         (tv:retinanet.py:508-571) -> candidate selection -> NMS over its fixed-stride segments, boxes rescaled to the
         original images by box_scale f32[B,2] (tv:transform.py:306-319) -> crops -> ... as in step()."""
@@ -105,9 +106,46 @@ class HotPath:
             _, counts, kept_boxes, _ = ops.nms_segments(cb, cs, stride, seg_counts, self.iou_threshold, self.min_score,
                                                         self.detections_per_img, box_scale=box_scale, want_boxes=True)
         self.launches += 2
-        return self._classify_kept(images, counts, kept_boxes, torch.arange(B, device=cb.device, dtype=torch.int64) * stride)
+        return self._classify_kept(images, counts, kept_boxes, torch.arange(B, device=cb.device, dtype=torch.int64) * stride, uploads)
 
-    def _classify_kept(self, images, counts, kept_boxes, seg_begin):
+    def upload_images(self, images_h, upload_group=4):
+        """Starts the host->device transfer of pinned host images on a copy stream, in groups of `upload_group`, into a
+        persistent staging buffer.  Returns (device images, uploads) for step(..., uploads=uploads) /
+        step_from_head(..., uploads=uploads): the step then cuts the crops of a group as soon as its images have landed
+        and runs the trunk on the crops that exist, so the transfer of the step's own images is hidden behind its
+        convolutions instead of preceding them."""
+        dev = self.gallery.f32.device
+        B = len(images_h)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        shapes = [tuple(im.shape) for im in images_h]
+        if self._stage is None or self._stage_key != shapes:
+            self._stage = [torch.empty(sh, dtype=torch.float32, device=dev) for sh in shapes]
+            self._stage_key = shapes
+        cs = self._copy_stream
+        if self._stage_free is not None:
+            cs.wait_event(self._stage_free)  # the previous step's crop launches have finished reading the staging buffers
+            self._stage_free = None
+        uploads = []
+        with torch.cuda.stream(cs):
+            for lo in range(0, B, upload_group):
+                hi = min(B, lo + upload_group)
+                for i in range(lo, hi):
+                    self._stage[i].copy_(images_h[i], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                uploads.append((ev, lo, hi))
+        return self._stage, uploads
+
+    @torch.no_grad()
+    def step_host(self, images_h, cand_boxes_h, cand_scores_h, seg_offsets_h, max_n, upload_group=4):
+        """step() for inputs in PINNED HOST memory (see upload_images).  Same results as step()."""
+        dev = self.gallery.f32.device
+        images, uploads = self.upload_images(images_h, upload_group)
+        return self.step(images, cand_boxes_h.to(dev, non_blocking=True), cand_scores_h.to(dev, non_blocking=True),
+                         seg_offsets_h.to(dev, non_blocking=True), max_n, uploads=uploads)
+
+    def _classify_kept(self, images, counts, kept_boxes, seg_begin, uploads=None):
         B = len(images)
         counts_h = counts.cpu()  # the one host synchronisation of the step
         K = int(counts_h.sum())
@@ -122,10 +160,37 @@ class HotPath:
         crop_bytes = 12.0 * S * S * K + 12.0 * float(((boxes[:, 2].long() - boxes[:, 0].long()).clamp(min=0) *
                                                       (boxes[:, 3].long() - boxes[:, 1].long()).clamp(min=0)).sum()) \
             if not isinstance(self.timer, _NoTimer) else 0.0
-        with self.timer.span("crop_resize", crop_bytes):
-            crops = ops.crop_resize(table, B, boxes, image_idx.to(torch.int32), S, self.antialias, 0.5, self.affine,
-                                    self.trunk_dtype, self.channels_last)
-        self.launches += 1
+        image_idx32 = image_idx.to(torch.int32)
+        if uploads is None:
+            with self.timer.span("crop_resize", crop_bytes):
+                crops = ops.crop_resize(table, B, boxes, image_idx32, S, self.antialias, 0.5, self.affine,
+                                        self.trunk_dtype, self.channels_last)
+            self.launches += 1
+            ensure_crops = None
+        else:
+            # images arrive group by group (step_host): one crop launch per group, issued right before the first trunk batch
+            # that needs it, after the main stream has waited for the group's upload
+            phys = torch.empty((K, S, S, 3) if self.channels_last else (K, 3, S, S), dtype=self.trunk_dtype, device=dev)
+            crops = phys.permute(0, 3, 1, 2) if self.channels_last else phys
+            first_crop = [0]
+            for c in counts_h.tolist():
+                first_crop.append(first_crop[-1] + int(c))
+            pending = list(uploads)
+            main_stream = torch.cuda.current_stream(dev)
+
+            def ensure_crops(upto):
+                while pending and first_crop[pending[0][1]] < upto:
+                    ev, lo, hi = pending.pop(0)
+                    a, b = first_crop[lo], first_crop[hi]
+                    main_stream.wait_event(ev)
+                    if b > a:
+                        with self.timer.span("crop_resize", crop_bytes * (b - a) / max(K, 1)):
+                            ops.crop_resize(table, B, boxes[a:b], image_idx32[a:b], S, self.antialias, 0.5, self.affine,
+                                            self.trunk_dtype, self.channels_last, out=phys[a:b])
+                        self.launches += 1
+                if not pending and self._stage_free is None:
+                    self._stage_free = torch.cuda.Event()
+                    self._stage_free.record(main_stream)
         D = self.encoder.embedding_size
         emb = torch.empty((K, D), dtype=torch.float32, device=dev)
         regions = None
@@ -141,6 +206,11 @@ class HotPath:
             ready.record(main)
         for j, i in enumerate(range(0, K, self.trunk_batch)):
             st = side[j % len(side)] if side else main
+            if ensure_crops is not None:
+                ensure_crops(min(K, i + self.trunk_batch))
+                if side:
+                    ready = torch.cuda.Event()
+                    ready.record(main)
             if side:
                 st.wait_event(ready)
             with torch.cuda.stream(st):
@@ -152,6 +222,8 @@ class HotPath:
                 with self.timer.span("region_pool_embed", nb):
                     ops.region_pool_embed([f4, f5], regions=regions, per_region_l2=bool(self.rmac_levels), out=emb[i:i + self.trunk_batch])
             self.launches += 1
+        if ensure_crops is not None:
+            ensure_crops(K + 1)  # groups without crops: nothing to launch, but the staging buffers are released
         if side:
             for st in side:
                 crops.record_stream(st)

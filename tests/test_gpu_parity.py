@@ -813,3 +813,48 @@ def test_metrics_mirror_process_batch(ops, golden):
     assert np.array_equal(s.numpy(), g[names[0] + "/sorted_iou"])
     one = metrics.process_one(targets[3], preds[3], confs[3], (0.5,))
     assert torch.equal(one[0][0.5]["true_positives"], res[3][0][0.5]["true_positives"])
+
+
+def test_hot_path_step_host_overlapped_upload_equals_step(ops):
+    """HotPath.step_host (pinned host images uploaded group by group on a copy stream, crops cut per group between trunk
+    batches) returns exactly what HotPath.step returns on device-resident inputs -- repeatedly, with the staging buffers
+    reused, with an image without detections in the middle and at the end, for fp32 and the channels-last half hand-off."""
+    from cvpce_b200 import classification, pipeline
+    torch.backends.cudnn.allow_tf32 = False
+    H, W = 384, 512
+    n_img = 7
+    images, boxes, scores, seg = [], [], [], [0]
+    for i in range(n_img):
+        images.append(torch.from_numpy(synth.shelf_image(20 + i, H, W)))
+        if i in (3, 6):
+            b, s = np.zeros((0, 4), np.float32), np.zeros((0,), np.float32)
+        else:
+            b, s = synth.shelf_candidates(20 + i, H, W, n_products=5 + 2 * i)
+            b = np.clip(b, 0, [W, H, W, H]).astype(np.float32)
+        boxes.append(b)
+        scores.append(s)
+        seg.append(seg[-1] + len(s))
+    boxes, scores, seg = np.concatenate(boxes), np.concatenate(scores), np.array(seg, dtype=np.int32)
+    max_n = int(np.diff(seg).max())
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda()
+    gallery = dev(synth.unit_rows(np.random.RandomState(2), 300, 1024))
+    images_h = [im.pin_memory() for im in images]
+    bh, sh, gh = torch.from_numpy(boxes).pin_memory(), torch.from_numpy(scores).pin_memory(), torch.from_numpy(seg).pin_memory()
+    for kwargs in (dict(), dict(trunk_dtype=torch.float16, channels_last=True)):
+        if kwargs:
+            enc = enc.half().to(memory_format=torch.channels_last)
+            enc.enable_fast_trunk()
+        hp = pipeline.HotPath(enc, gallery, k=3, size=64, trunk_batch=8, detections_per_img=200, **kwargs)
+        want = hp.step([im.cuda() for im in images], dev(boxes), dev(scores), dev(seg), max_n)
+        assert int(want["counts"].sum()) > 20 and int(want["counts"][3]) == 0
+        for group in (1, 2, 4, 16):
+            for _ in range(2):
+                got = hp.step_host(images_h, bh, sh, gh, max_n, upload_group=group)
+                assert torch.equal(got["counts"], want["counts"])
+                assert torch.equal(got["boxes"], want["boxes"])
+                assert torch.equal(got["embedding"], want["embedding"]), (kwargs, group)
+                assert torch.equal(got["topk_idx"], want["topk_idx"]) and torch.equal(got["topk_sim"], want["topk_sim"])
+    # a step with no detections at all releases the staging buffers too
+    empty = hp.step_host(images_h, bh[:0], sh[:0], torch.zeros(n_img + 1, dtype=torch.int32).pin_memory(), 1, upload_group=2)
+    assert int(empty["counts"].sum()) == 0 and hp._stage_free is not None
