@@ -130,6 +130,25 @@ class ShardedGallery:
         lo, hi = shard_range(G, world, rank)
         return cls(synthetic_rows(lo, hi, D, device, seed), lo, world, rank, group, exchange=exchange)
 
+    @staticmethod
+    def load_index_rows(pth, world, rank):
+        """This rank's row range of an index file in the reference's format ({'embedding', 'annotations'}, written by
+        Classifier.save_index, cvpce/production.py:52-56): the file is memory-mapped, so a rank pages in only its own rows.
+        Returns (rows f32 [hi-lo, D] on the host, first global row index, annotations list (whole: it maps global indices))."""
+        try:
+            idx = torch.load(pth, map_location="cpu", mmap=True, weights_only=False)
+        except (RuntimeError, ValueError, TypeError):  # legacy (non-zip) serialisation cannot be mapped
+            idx = torch.load(pth, map_location="cpu", weights_only=False)
+        emb = idx["embedding"]
+        lo, hi = shard_range(int(emb.shape[0]), world, rank)
+        return emb[lo:hi].contiguous().float(), lo, idx["annotations"]
+
+    @classmethod
+    def from_index(cls, pth, world, rank, device, group=None, exchange="nccl"):
+        """(ShardedGallery over this rank's rows of the index file, annotations)."""
+        rows, lo, annotations = cls.load_index_rows(pth, world, rank)
+        return cls(rows.to(device), lo, world, rank, group, exchange=exchange), annotations
+
     def search(self, queries_f32, k, exact=True):
         """queries f32[Q,D] (present on every rank) -> (similarity f32[Q,k], GLOBAL gallery index i64[Q,k]) on every rank."""
         q = queries_f32.contiguous()

@@ -58,6 +58,7 @@ class Classifier:
         else:
             self.embedding, self.annotations = self.load_index(load)
         self._prepared = None
+        self._sharded = None
 
     def build_index(self, sample_set, verbose=False):
         loader = DataLoader(sample_set, batch_size=self.batch_size, num_workers=self.num_workers,
@@ -82,6 +83,15 @@ class Classifier:
         idx = torch.load(pth, map_location=self.emb_device)
         return idx['embedding'], idx['annotations']
 
+    def shard_gallery(self, world, rank, group=None, exchange="nccl"):
+        """Multi-GPU gallery: keep only this rank's row range of the index on the device; classify() then
+        searches the shard, exchanges the per-rank top-k blocks and merges, and every rank maps the same GLOBAL indices to
+        annotations (the annotation list stays whole on every rank).  Returns the ShardedGallery."""
+        from . import dist as cdist
+        lo, hi = cdist.shard_range(int(self.embedding.shape[0]), world, rank)
+        self._sharded = cdist.ShardedGallery(self.embedding[lo:hi].to(self.emb_device), lo, world, rank, group, exchange=exchange)
+        return self._sharded
+
     def prepared_gallery(self):
         if self._prepared is None or self._prepared.f32.data_ptr() != self.embedding.data_ptr():
             self._prepared = classification.PreparedGallery(self.embedding.to(self.emb_device))
@@ -104,7 +114,10 @@ class Classifier:
             emb = torch.empty((0, self.encoder.embedding_size), dtype=torch.float, device=self.emb_device)
             return (res, emb) if return_embedding else res
         emb = self.embed(images)
-        _, nearest = classification.similarity_topk(self.embedding, emb, self.k, prepared=self.prepared_gallery())
+        if getattr(self, "_sharded", None) is not None:
+            _, nearest = self._sharded.search(emb, self.k)
+        else:
+            _, nearest = classification.similarity_topk(self.embedding, emb, self.k, prepared=self.prepared_gallery())
         nearest = nearest.cpu().tolist()
         res = [[self.annotations[j] for j in row] for row in nearest]
         if return_embedding:

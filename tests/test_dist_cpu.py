@@ -69,3 +69,20 @@ def test_gallery_sharded_search_world2_gloo(tmp_path):
     port = 29500 + os.getpid() % 2000
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert [open(tmp_path / ("ok%d" % r)).read() for r in range(2)] == ["1", "1"]
+
+
+def test_index_file_rows_per_rank(tmp_path):
+    """f2: every rank reads only its row range of an index file in the reference's {'embedding','annotations'} format
+    (production.py:52-56); the ranges tile the gallery and the annotation list stays whole."""
+    emb = cdist.synthetic_rows(0, 101, 16, torch.device("cpu"), 9)
+    ann = ["sku%03d" % i for i in range(101)]
+    pth = str(tmp_path / "index.pt")
+    torch.save({"embedding": emb, "annotations": ann}, pth)
+    for world in (1, 2, 3, 8):
+        parts, nxt = [], 0
+        for rank in range(world):
+            rows, lo, a = cdist.ShardedGallery.load_index_rows(pth, world, rank)
+            assert lo == nxt and a == ann and rows.dtype == torch.float32 and rows.is_contiguous()
+            nxt += rows.shape[0]
+            parts.append(rows)
+        assert torch.equal(torch.cat(parts), emb)

@@ -409,6 +409,26 @@ def test_classifier_mirror_matches_reference_labels(ops, golden):
     labels = np.array([[int(a[1:]) for a in row] for row in res])
     assert np.array_equal(labels, golden["classify"]["labels"])
     assert clf.classify(torch.empty((0, 3, 64, 64))) == []
+    # f2: index file round trip in the reference's format, then the same labels through a sharded gallery
+    # (rank 1 of 2 holds only the upper half of the rows; merged with rank 0's block the result is the unsharded one)
+    import os
+    import tempfile
+    from cvpce_b200 import dist as cdist
+    with tempfile.TemporaryDirectory() as tmp:
+        pth = os.path.join(tmp, "index.pt")
+        clf.save_index(pth)
+        clf2 = production.Classifier(enc, None, batch_size=4, num_workers=0, k=3, load=pth)
+        assert torch.equal(clf2.embedding, clf.embedding) and clf2.annotations == clf.annotations
+        clf2.shard_gallery(1, 0)
+        assert clf2.classify(torch.from_numpy(queries)) == res
+        blocks = []
+        for rank in range(2):
+            sg, ann = cdist.ShardedGallery.from_index(pth, 2, rank, torch.device("cuda"))
+            assert ann == clf.annotations and sg.g32.shape[0] in (len(ann) // 2, len(ann) - len(ann) // 2)
+            sg.world = 1                                      # single process: search the shard, merge by hand below
+            blocks.append(sg.search(emb, 3))
+        _, merged = ops.topk_merge(torch.stack([b[0] for b in blocks]), torch.stack([b[1] for b in blocks]))
+        assert [[clf.annotations[j] for j in row] for row in merged.cpu().tolist()] == res
 
 
 # ------------------------------------------------------------------------------ f1: pre-NMS candidate selection (+ a1, a2)
