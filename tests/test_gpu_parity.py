@@ -878,3 +878,81 @@ def test_hot_path_step_host_overlapped_upload_equals_step(ops):
     # a step with no detections at all releases the staging buffers too
     empty = hp.step_host(images_h, bh[:0], sh[:0], torch.zeros(n_img + 1, dtype=torch.int32).pin_memory(), 1, upload_group=2)
     assert int(empty["counts"].sum()) == 0 and hp._stage_free is not None
+
+
+def test_patch_layer_on_a_reference_shaped_package(ops):
+    """The reference itself cannot travel to the GPU box, so the patcher is exercised on a package with the reference's
+    attribute layout (the real reference is patched and reverted in tests/test_reference_pin.py): after patch.apply the
+    swapped call sites run on the GPU and agree with the torch / torchvision functions they replace."""
+    import types
+    import torchvision
+    from torchvision.models.detection import retinanet
+    from cvpce_b200 import patch
+
+    def ref_nn(anchors, queries, k=1):
+        d = 1 - torch.nn.functional.cosine_similarity(anchors[None, :, :], queries[:, None, :], dim=2)
+        return d.argsort(dim=1)[:, :k]
+
+    def ref_resize(img):
+        _, h, w = img.shape
+        L = max(h, w)
+        canvas = torch.full((3, L, L), 0.5, dtype=img.dtype, device=img.device)
+        canvas[:, :h, :w] = img
+        return torch.nn.functional.interpolate(canvas[None], size=(256, 256), mode="bilinear", antialias=True, align_corners=False)[0]
+
+    class _Enc(torch.nn.Module):
+        def forward(self, x, eps=1e-8):
+            return x
+
+    class _PG:
+        def generate_proposals_and_images(self, image):
+            raise NotImplementedError
+
+    class _Clf:
+        def classify(self, images, return_embedding=False):
+            raise NotImplementedError
+
+    seen = {}
+
+    def do_calculate(thresholds, matches, confidences, total_targets):
+        seen.update(thresholds=thresholds, matches=matches, confidences=confidences, total=total_targets)
+        return "bookkeeping result"
+
+    pkg = types.SimpleNamespace(
+        models=types.SimpleNamespace(classification=types.SimpleNamespace(nearest_neighbors=ref_nn, MACVGG=type("MACVGG", (_Enc,), {}),
+                                                                          MACResNet=type("MACResNet", (_Enc,), {}))),
+        production=types.SimpleNamespace(nearest_neighbors=ref_nn, ProposalGenerator=_PG, Classifier=_Clf),
+        datautils=types.SimpleNamespace(resize_for_classification=ref_resize),
+        utils=types.SimpleNamespace(nearest_neighbors=ref_nn),
+        metrics=types.SimpleNamespace(iou_matrices=ref_nn, _process_one=ref_nn, calculate_metrics=ref_nn, _do_calculate=do_calculate),
+        planograms=types.SimpleNamespace(tvops=torchvision.ops))
+    tv_batched_nms = retinanet.box_ops.batched_nms
+    patch.apply(pkg)
+    try:
+        # a11: the reference's own known answer (test/models/classification_test.py:8-25) through every alias
+        anchors, queries, expected = synth.nn_kat()
+        for mod in (pkg.models.classification, pkg.production, pkg.utils):
+            assert mod.nearest_neighbors(dev(anchors), dev(queries)).flatten().tolist() == list(expected)
+        # a1: torchvision's RetinaNet call site
+        b, s = synth.random_boxes(77, 900, extent=300.0)
+        labels = torch.zeros(900, dtype=torch.int64, device="cuda")
+        assert retinanet.box_ops.batched_nms is not tv_batched_nms
+        assert torch.equal(retinanet.box_ops.batched_nms(dev(b), dev(s), labels, 0.5), tv_batched_nms(dev(b), dev(s), labels, 0.5))
+        # a4: same signature, CUDA image in
+        img = dev(synth.shelf_image(8, 150, 90))
+        assert float((pkg.datautils.resize_for_classification(img) - ref_resize(img)).abs().max()) <= 1e-5
+        # f3: matching on the GPU, bookkeeping handed to the package's own _do_calculate; box_iou behind the tvops name
+        cases = synth.match_cases()
+        t = [torch.from_numpy(cases[n][0]) for n in ("kat0", "kat1", "kat2")]
+        p = [torch.from_numpy(cases[n][1]) for n in ("kat0", "kat1", "kat2")]
+        conf = [torch.linspace(1, 0.1, len(x)) for x in p]
+        assert pkg.metrics.calculate_metrics(t, p, conf, (0.5, 0.65)) == "bookkeeping result"
+        assert seen["total"] == 9 and seen["matches"][0.65]["true_positives"][0].tolist() == [1, 0, 0, 1, 0]
+        assert [float(r) for r in seen["matches"][0.5]["recall_300"]] == pytest.approx([1, 3 / 4, 1 / 2])   # test/metrics_test.py:70-78
+        got = pkg.planograms.tvops.box_iou(p[0], t[0])
+        assert not got.is_cuda and torch.equal(got, torchvision.ops.box_iou(p[0], t[0]))
+        assert pkg.planograms.tvops.nms is torchvision.ops.nms
+    finally:
+        patch.revert()
+    assert retinanet.box_ops.batched_nms is tv_batched_nms and pkg.models.classification.nearest_neighbors is ref_nn
+    assert pkg.planograms.tvops is torchvision.ops and pkg.metrics.calculate_metrics is ref_nn

@@ -77,3 +77,49 @@ def test_matching_oracle_equals_reference_on_fresh_inputs(ref):
     mod.test_iou_matrices()
     mod.test_iou_matrices_2()
     mod.test_check_matches()
+
+
+def test_patch_swaps_and_restores_every_call_site(ref):
+    """cvpce_b200.patch on the UNMODIFIED reference: every hot-path call site is swapped, the swapped functions refuse CPU
+    tensors loudly (no CPU fallback), and revert() puts back exactly the original objects."""
+    import cvpce.metrics as rmetrics
+    import cvpce.planograms as rplan
+    import cvpce.models.proposals as rprop
+    from torchvision.models.detection import retinanet
+    from cvpce_b200 import patch
+    rc, rp, rd = ref.models.classification, ref.production, ref.datautils
+    sites = [(rc, "nearest_neighbors"), (rp, "nearest_neighbors"), (ref.utils, "nearest_neighbors"), (rc.MACVGG, "forward"),
+             (rc.MACResNet, "forward"), (rd, "resize_for_classification"), (rp.ProposalGenerator, "generate_proposals_and_images"),
+             (rp.Classifier, "classify"), (rmetrics, "iou_matrices"), (rmetrics, "_process_one"), (rmetrics, "calculate_metrics"),
+             (rplan, "tvops"), (retinanet.box_ops, "batched_nms")]
+    before = [getattr(o, n) for o, n in sites]
+    gln_own = "postprocess_detections" in vars(rprop.GaussianLayerNetwork)
+    patch.apply(ref)
+    try:
+        patch.apply(ref)  # idempotent
+        after = [getattr(o, n) for o, n in sites]
+        assert all(a is not b for a, b in zip(after, before)), [n for (o, n), a, b in zip(sites, after, before) if a is b]
+        assert "postprocess_detections" in vars(rprop.GaussianLayerNetwork)
+        b = torch.tensor([[0., 0., 10., 10.], [1., 1., 11., 11.]])
+        for call in (lambda: retinanet.box_ops.batched_nms(b, torch.tensor([.9, .8]), torch.zeros(2, dtype=torch.int64), 0.5),
+                     lambda: rd.resize_for_classification(torch.rand(3, 20, 30)),
+                     lambda: rc.nearest_neighbors(torch.rand(4, 8), torch.rand(2, 8), 1)):
+            with pytest.raises(RuntimeError):
+                call()
+        if not torch.cuda.is_available():   # the GPU-backed metrics / box_iou replacements say so instead of computing on the host
+            with pytest.raises(RuntimeError):
+                rmetrics.iou_matrices(b, b)
+            with pytest.raises(RuntimeError):
+                rplan.tvops.box_iou(b, b)
+        assert rplan.tvops.clip_boxes_to_image is torchvision_ops().clip_boxes_to_image   # everything else passes through
+    finally:
+        patch.revert()
+    assert all(getattr(o, n) is b for (o, n), b in zip(sites, before))
+    assert ("postprocess_detections" in vars(rprop.GaussianLayerNetwork)) == gln_own
+    # the reference computes again after the revert
+    assert rc.nearest_neighbors(torch.eye(3), torch.eye(3)[[2, 0]], 1).flatten().tolist() == [2, 0]
+
+
+def torchvision_ops():
+    import torchvision
+    return torchvision.ops
