@@ -88,3 +88,52 @@ def test_affine_fold_matches_reference_composition():
     got = x * a[:, 0].view(1, 3, 1, 1) + a[:, 1].view(1, 3, 1, 1)
     want = ((x * 2 - 1) - torch.tensor(classification.NORM_MEAN).view(1, 3, 1, 1)) / torch.tensor(classification.NORM_STD).view(1, 3, 1, 1)
     assert torch.allclose(got, want, atol=1e-6)
+
+
+def test_header_is_plain_c_and_a_c_program_can_bind(lib, tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 (no C++-isms, no torch types) and a C host must be able to
+    dlopen the library and call through it -- here the calls that need no GPU (version, argument validation, last error)."""
+    import os
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "host.c"
+    src.write_text(r'''
+#include <dlfcn.h>
+#include <stdio.h>
+#include <string.h>
+#include "cvpce_b200.h"
+typedef int (*version_fn)(void);
+typedef const char* (*err_fn)(void);
+typedef int (*iou_fn)(const float*, int, const float*, int, float*, void*);
+typedef int (*match_fn)(const float*, const int64_t*, const int32_t*, const float*, const int64_t*, const int32_t*, int, int, float,
+                        uint8_t*, uint8_t*, void*);
+int main(int argc, char** argv) {
+  void* h = dlopen(argv[1], RTLD_NOW | RTLD_LOCAL);
+  if (!h) { fprintf(stderr, "%s\n", dlerror()); return 2; }
+  version_fn version = (version_fn)dlsym(h, "cvpce_version");
+  err_fn last_error = (err_fn)dlsym(h, "cvpce_last_error");
+  iou_fn box_iou = (iou_fn)dlsym(h, "cvpce_box_iou");
+  match_fn iou_match = (match_fn)dlsym(h, "cvpce_iou_match");
+  if (!version || !last_error || !box_iou || !iou_match) return 3;
+  if (version() != CVPCE_B200_VERSION) return 4;
+  if (box_iou(NULL, 0, NULL, 0, NULL, NULL) != CVPCE_OK) return 5;                 /* empty input: valid, nothing launched */
+  if (box_iou(NULL, 3, NULL, 2, NULL, NULL) != CVPCE_ERR_INVALID_ARG) return 6;    /* null pointers: refused on the host */
+  if (strstr(last_error(), "box_iou") == NULL) return 7;
+  if (iou_match(NULL, NULL, NULL, NULL, NULL, NULL, 1, CVPCE_MATCH_MAX_COLS + 1, 0.5f, NULL, NULL, NULL) == CVPCE_OK) return 8;
+  printf("ok %d\n", version());
+  return 0;
+}
+''')
+    exe = tmp_path / "host"
+    hdr = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-x", "c",
+                          os.path.join(root, "include", "cvpce_b200.h")], capture_output=True, text=True)
+    assert hdr.returncode == 0, hdr.stderr
+    # (no -pedantic for the host: ISO C has no object-pointer -> function-pointer conversion, which dlsym needs)
+    cc = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(root, "include"), str(src), "-o", str(exe), "-ldl"],
+                        capture_output=True, text=True)
+    assert cc.returncode == 0, cc.stderr
+    run = subprocess.run([str(exe), _lib.SO_PATH], capture_output=True, text=True)
+    assert run.returncode == 0 and run.stdout.strip() == "ok 100", (run.returncode, run.stdout, run.stderr)
