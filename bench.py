@@ -382,7 +382,10 @@ def run_ours_shelves(args, world, rank, local):
                        "" if args.plain_trunk else "; the 2x2 max-pools between them run in the library (cvpce_maxpool2x2_nhwc)"),
                    "trunk_batch": args.trunk_batch,
                    "similarity": "tcgen05 bf16 + exact fp32 re-score" if args.sim == "tc" else "cuda-core fp32",
-                   "l2": "inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9),
+                   "l2": ("inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9))
+                         if n_shelves * 3 * 1536 * 2048 * 4 > 126e6 else
+                         ("inputs (%.0f MB) fit L2, but every step streams %.1f GB of crops and trunk activations through it before "
+                          "the inputs are read again" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e6, K_crops * (0.79e6 + 60e6) / 1e9)),
                    "parallelism": "dp%d (independent images, no data-path collective)" % world},
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": round(ms_e2e / args.steps, 3),
@@ -535,6 +538,16 @@ def main():
             a16.trunk, a16.no_cpu_baseline, a16.steps = "f16", True, max(1, min(args.steps, 2))
             torch.cuda.empty_cache()
             l16 = run_ours_shelves(a16, world, rank, local)
+            if args.workload == "c3":
+                # BASELINE.json configs[1] (one shelf, ~200 boxes, 180 references) next to the headline: the same step at
+                # batch 1, i.e. the latency case (the headline is configs[2], the largest single-GPU configuration)
+                a2 = copy.copy(args)
+                a2.workload, a2.shelves, a2.gallery, a2.no_cpu_baseline, a2.steps, a2.warmup = "c2", None, None, True, 20, 5
+                torch.cuda.empty_cache()
+                l2 = run_ours_shelves(a2, world, rank, local)
+                line["other_configs"] = {"c2": {"workload": l2["config"]["workload"], "value": l2["value"], "unit": l2["unit"],
+                                                "ms_per_step": l2["ms_per_step"], "e2e": l2["e2e"]["value"],
+                                                "e2e_ms_per_step": l2["e2e"]["ms_per_step"], "steps": a2.steps}}
             line["extension_modes"] = {"trunk_f16": {"value": l16["value"], "unit": l16["unit"], "ms_per_step": l16["ms_per_step"],
                                                      "e2e": l16["e2e"]["value"], "steps": a16.steps,
                                                      "note": "half weights/activations, fp32 accumulation; not the headline"}}
