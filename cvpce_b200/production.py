@@ -6,7 +6,7 @@ out of scope and not mirrored; the reference's own classes accept t
 import torch
 from torch.utils.data import DataLoader
 
-from . import classification, datautils, ops
+from . import classification, datautils
 
 
 def scale_to_tanh(tensor):

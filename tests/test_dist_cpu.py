@@ -3,7 +3,6 @@ The CUDA arithmetic is replaced by the oracle here (tests only); the product pat
 import os
 
 import numpy as np
-import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp

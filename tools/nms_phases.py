@@ -2,7 +2,7 @@
 """Development aid: per-phase cycle counts of nms_batched_kernel (block 0).  Needs a library built with
 CVPCE_NVCC_EXTRA=-DCVPCE_PHASE_TIMERS python -m cvpce_b200.build --force"""
 import ctypes, os, sys
-import numpy as np, torch
+import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cvpce_b200 import _lib, ops, synth, detection
 

@@ -2,7 +2,7 @@
 """How far do the embeddings move when the (torch) trunk's convolutions run in TF32 (torch's default on GPU, what bench.py
 times) instead of strict fp32?  Prints max / mean relative deviation, cosine, and top-1 / top-5 agreement vs a gallery."""
 import os, sys
-import numpy as np, torch
+import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cvpce_b200 import classification, synth
 
