@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libcvpce_b200.so")
+SO_PATH = os.environ.get("CVPCE_B200_SO") or os.path.join(_HERE, "libcvpce_b200.so")  # the override is for A/B builds during development
 
 F32, BF16, F16 = 0, 1, 2
 NCHW, NHWC = 0, 1

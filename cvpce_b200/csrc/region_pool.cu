@@ -459,17 +459,26 @@ __global__ void __launch_bounds__(kPoolThreads, GENERAL ? (NHWC_ONLY ? 3 : 2) : 
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kMacMaxCols = 4096;  // sum of C over the maps
 
+#ifndef CVPCE_MAC_MIN_CTAS
+#define CVPCE_MAC_MIN_CTAS 1
+#endif
+#ifndef CVPCE_MAC_UNROLL
+#define CVPCE_MAC_UNROLL 8
+#endif
+#define CVPCE_PRAGMA(x) _Pragma(#x)
+#define CVPCE_UNROLL(n) CVPCE_PRAGMA(unroll n)
+
 template <int DT>
-__global__ void __launch_bounds__(kPoolThreads) mac_nhwc_pixelsplit_kernel(const PoolParams p) {
+__global__ void __launch_bounds__(kPoolThreads, CVPCE_MAC_MIN_CTAS) mac_nhwc_pixelsplit_kernel(const PoolParams p) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned crank = cluster.block_rank(), csize = cluster.num_blocks();
-  const int n = blockIdx.x / kPoolCluster;
+  const int n = blockIdx.x / csize;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr bool BF16 = DT != CVPCE_F32;  // any 16-bit element type
   constexpr int E = BF16 ? 8 : 4;  // elements per 16-byte vector
   __shared__ float pmax[kMacMaxCols];          // this CTA's maxima over its pixels, every channel of every map
   __shared__ float red[kPoolThreads * E];
-  __shared__ float own[kMacMaxCols / kPoolCluster];  // finished maxima of this CTA's channel slab
+  __shared__ float own[kMacMaxCols / 2];  // finished maxima of this CTA's channel slab (cluster size >= 2)
   __shared__ float wsum[kPoolWarps];
   __shared__ float fpart;
 
@@ -485,7 +494,7 @@ __global__ void __launch_bounds__(kPoolThreads) mac_nhwc_pixelsplit_kernel(const
     float acc[E];
 #pragma unroll
     for (int e = 0; e < E; ++e) acc[e] = -INFINITY;
-#pragma unroll 8
+    CVPCE_UNROLL(CVPCE_MAC_UNROLL)
     for (int i = tid; i < total; i += kPoolThreads) {
       const uint4 x = ldg_stream_u4(base + i);
       if (DT == CVPCE_F16) {
@@ -743,7 +752,22 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   }
   void (*kern)(PoolParams);
   size_t smem_launch = smem;
+  int cluster_size = kPoolCluster;
   if (pixsplit) {
+    // The pixel-split kernel works with any cluster size that divides every C.  Measured on B200 (tools/kbench.py pool,
+    // two 512 x 16 x 16 maps per image): about 512 CTAs -- one resident wave, ~0.5 MB streamed per CTA before its
+    // reduction tail -- is the sweet spot: B = 256: 0.77 of HBM with clusters of 2 against 0.65 with 4 or 8 (a ragged
+    // second wave); B = 128: 0.62 with 4 against 0.52 (8) and 0.50 (2, too few CTAs).  CVPCE_MAC_CLUSTER overrides.
+    const char* e = getenv("CVPCE_MAC_CLUSTER");
+    const int want = e ? atoi(e) : (B >= 256 ? 2 : (B >= 128 ? 4 : kPoolCluster));
+    if (want == 2 || want == 4) {
+      bool ok = true;
+      for (int m = 0; m < n_maps; ++m) ok = ok && maps[m].C % want == 0;
+      if (ok) {
+        cluster_size = want;
+        for (int m = 0; m < n_maps; ++m) p.maps[m].slab = maps[m].C / want;
+      }
+    }
     kern = dtype == CVPCE_F32 ? mac_nhwc_pixelsplit_kernel<CVPCE_F32>
                               : (dtype == CVPCE_BF16 ? mac_nhwc_pixelsplit_kernel<CVPCE_BF16> : mac_nhwc_pixelsplit_kernel<CVPCE_F16>);
     smem_launch = 0;
@@ -760,13 +784,13 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   // the default 48 KB limit covers static + dynamic shared memory: opt in with a margin for the static part
   if (smem_launch > 40 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_launch));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(B * kPoolCluster));
+  cfg.gridDim = dim3((unsigned)(B * cluster_size));
   cfg.blockDim = dim3(kPoolThreads);
   cfg.dynamicSmemBytes = smem_launch;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kPoolCluster;
+  attr[0].val.clusterDim.x = cluster_size;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;

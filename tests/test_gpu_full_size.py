@@ -100,11 +100,12 @@ def test_crop_identity_and_constant_at_shelf_size(ops):
     assert float(many.min()) >= 0.0 and float(many.max()) <= 1.0
 
 
-def test_mac_exact_maxima_at_trunk_batch_size(ops):
+@pytest.mark.parametrize("B", [256, 130])   # the trunk batch of the step (clusters of 2) and a ragged last batch (clusters of 4)
+def test_mac_exact_maxima_at_trunk_batch_size(ops, B):
     g = torch.Generator(device="cuda").manual_seed(3)
     for cl in (False, True):
-        f4 = torch.rand((256, 512, 16, 16), device="cuda", generator=g)     # pool4(relu4_3) and relu5_3 of a 256-crop batch
-        f5 = torch.rand((256, 512, 16, 16), device="cuda", generator=g)
+        f4 = torch.rand((B, 512, 16, 16), device="cuda", generator=g)       # pool4(relu4_3) and relu5_3 of a trunk batch
+        f5 = torch.rand((B, 512, 16, 16), device="cuda", generator=g)
         if cl:
             f4, f5 = f4.contiguous(memory_format=torch.channels_last), f5.contiguous(memory_format=torch.channels_last)
         emb = ops.region_pool_embed([f4, f5])

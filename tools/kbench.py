@@ -176,6 +176,11 @@ def bench_pool(args):
             nb = 4.0 * (f4.numel() + f5.numel()) + 4.0 * 1024 * B
             ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], out=out), args.iters)
             report("region_pool MAC B=%d %s" % (B, "nhwc" if cl else "nchw"), ms, best, nb)
+            if cl:  # the shape inside the step: MAC over pool4(relu4_3) and relu5_3, both 16 x 16
+                p4 = torch.rand((B, 512, 16, 16), device=dev).contiguous(memory_format=torch.channels_last)
+                nb2 = 4.0 * (p4.numel() + f5.numel()) + 4.0 * 1024 * B
+                ms, best = timeit(lambda: ops.region_pool_embed([p4, f5], out=out), args.iters)
+                report("region_pool MAC B=%d nhwc, pooled f4 (in-step shape)" % B, ms, best, nb2)
             regs = [ops.rmac_regions(32, 32, 3), ops.rmac_regions(16, 16, 3)]
             ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
             report("region_pool R-MAC L=3 B=%d %s" % (B, "nhwc" if cl else "nchw"), ms, best, nb)
