@@ -620,7 +620,8 @@ static int launch_sep(const CropParams& p, int out_dtype, int out_layout, cudaSt
   SepLayout lay;
   // band height: 64 output rows when there are enough crops to fill the machine, fewer rows per CTA otherwise
   const long long want_ctas = 4ll * sm_count();
-  int band_rows = 64;
+  int band_rows = env_int("CVPCE_CROP_BAND_ROWS", 64);
+  if (band_rows < 8 || band_rows > 256 || (band_rows & (band_rows - 1))) band_rows = 64;
   while (band_rows > 8 && (long long)p.K * ((S + band_rows - 1) / band_rows) < want_ctas) band_rows >>= 1;
   if (band_rows > S) band_rows = (S + 3) & ~3;
   lay.band_rows = band_rows;
