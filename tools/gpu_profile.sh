@@ -10,7 +10,7 @@ tail -3 $OUT/pytest_gpu.log
 python bench.py --steps 3 --warmup 3 > $OUT/bench_c3.json 2> $OUT/bench_c3.err; echo "bench exit $?"
 tail -c 600 $OUT/bench_c3.json
 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref exit $?"
-PROF="python bench.py --from-head --shelves 4 --steps 1 --warmup 1 --no-cpu-baseline"
+PROF="python bench.py --from-head --shelves 4 --steps 1 --warmup 1 --no-cpu-baseline --no-extension-modes"
 $PROF > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $OUT/launches.csv $PROF > $OUT/ncu_launch.log 2>&1
 echo "ncu launches exit $?"
