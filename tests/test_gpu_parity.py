@@ -956,3 +956,29 @@ def test_patch_layer_on_a_reference_shaped_package(ops):
         patch.revert()
     assert retinanet.box_ops.batched_nms is tv_batched_nms and pkg.models.classification.nearest_neighbors is ref_nn
     assert pkg.planograms.tvops is torchvision.ops and pkg.metrics.calculate_metrics is ref_nn
+
+
+def test_nms_and_box_iou_on_degenerate_integer_grids(ops):
+    """Small integer coordinates: exact score ties, IoUs exactly at the threshold, zero-area and nested boxes -- the same
+    generator on which tests/test_oracle_golden.py pins the oracle to the compiled torchvision ops."""
+    rs = np.random.RandomState(2025)
+    for thr in (0.25, 1 / 3, 0.5, 0.7):
+        boxes, scores, seg = [], [], [0]
+        for case in range(40):
+            n = int(rs.choice([0, 1, 2, 7, 40, 150, 700]))
+            xy = rs.randint(0, 12, size=(n, 2)).astype(np.float32)
+            wh = rs.randint(0, 7, size=(n, 2)).astype(np.float32)
+            boxes.append(np.concatenate([xy, xy + wh], axis=1))
+            scores.append((rs.randint(0, 8, size=n) / 8.0).astype(np.float32))
+            seg.append(seg[-1] + n)
+        b, s = np.concatenate(boxes), np.concatenate(scores)
+        keep, counts, _, _ = ops.nms_batched(dev(b), dev(s), dev(np.array(seg, np.int32)), 700, thr)
+        keep, counts = keep.cpu().numpy(), counts.cpu().numpy()
+        for i in range(40):
+            want = oracle.nms(boxes[i], scores[i], thr)
+            assert counts[i] == len(want) and np.array_equal(keep[seg[i]:seg[i] + counts[i]], want), (thr, i, len(scores[i]))
+        got = ops.box_iou(dev(boxes[5]), dev(boxes[6])).cpu().numpy() if len(boxes[5]) and len(boxes[6]) else None
+        if got is not None:
+            want = oracle.box_iou(boxes[5], boxes[6])
+            nan = np.isnan(want)
+            assert np.array_equal(np.isnan(got), nan) and np.array_equal(got[~nan], want[~nan])

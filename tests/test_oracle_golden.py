@@ -102,3 +102,27 @@ def test_sim_topk_ties_and_padding():
     assert idx.tolist() == [[0, 1, 3]]  # equal similarity: ascending index
     sim, idx = oracle.sim_topk(q, np.zeros((1, 2), dtype=np.float32), 1)
     assert sim[0, 0] == 0.0  # zero vector: norm clamped to eps => similarity 0 (distance 1)
+
+
+def test_oracle_nms_and_box_iou_equal_the_compiled_torchvision_ops_on_random_cases():
+    """The third-party ops the reference calls (torchvision.ops.nms / box_iou, CPU) are available wherever the tests run, so the
+    restatement is also pinned on fresh random inputs: small integer coordinates make exact score ties, IoUs exactly at the
+    threshold, zero-area and fully nested boxes common."""
+    import torch
+    import torchvision
+    rs = np.random.RandomState(2024)
+    for case in range(60):
+        n = int(rs.choice([0, 1, 2, 7, 40, 150]))
+        xy = rs.randint(0, 12, size=(n, 2)).astype(np.float32)
+        wh = rs.randint(0, 7, size=(n, 2)).astype(np.float32)            # zero-width / zero-height boxes included
+        boxes = np.concatenate([xy, xy + wh], axis=1)
+        scores = (rs.randint(0, 8, size=n) / 8.0).astype(np.float32)     # many equal scores
+        thr = float(rs.choice([0.25, 1 / 3, 0.5, 0.7]))
+        want = torchvision.ops.nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
+        assert np.array_equal(oracle.nms(boxes, scores, thr), want), (case, n, thr)
+        m = int(rs.choice([1, 3, 30]))
+        other = np.concatenate([rs.randint(0, 12, size=(m, 2)), rs.randint(6, 16, size=(m, 2))], axis=1).astype(np.float32)
+        want_iou = torchvision.ops.box_iou(torch.from_numpy(boxes), torch.from_numpy(other)).numpy()
+        got_iou = oracle.box_iou(boxes, other)
+        nan = np.isnan(want_iou)
+        assert np.array_equal(np.isnan(got_iou), nan) and np.array_equal(got_iou[~nan], want_iou[~nan]), case
