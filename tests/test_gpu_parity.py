@@ -982,3 +982,26 @@ def test_nms_and_box_iou_on_degenerate_integer_grids(ops):
             want = oracle.box_iou(boxes[5], boxes[6])
             nan = np.isnan(want)
             assert np.array_equal(np.isnan(got), nan) and np.array_equal(got[~nan], want[~nan])
+
+
+def test_crops_equal_the_reference_torch_cpu_ops_on_random_boxes(ops):
+    """The crop kernel against the reference's own torch CPU ops (python slice + pad 0.5 + F.interpolate(antialias=True),
+    oracle/torch_port.py, pinned to the live reference in tests/test_reference_pin.py) on random boxes: up- and down-sampling
+    by up to ~5x, thin strips, boxes touching and crossing the image border, fractional coordinates."""
+    from oracle import torch_port
+    H, W = 700, 900
+    img = synth.shelf_image(12, H, W)
+    rs = np.random.RandomState(77)
+    xy = rs.uniform(-20, [W - 10, H - 10], size=(48, 2))
+    wh = np.exp(rs.uniform(np.log(6), np.log(680), size=(48, 2)))
+    boxes = np.concatenate([np.maximum(xy, 0), xy + wh], axis=1).astype(np.float32)
+    boxes[:, 2] = np.maximum(boxes[:, 2], boxes[:, 0] + 2)
+    boxes[:, 3] = np.maximum(boxes[:, 3], boxes[:, 1] + 2)
+    boxes[:, 0] = np.minimum(boxes[:, 0], W - 3)
+    boxes[:, 1] = np.minimum(boxes[:, 1], H - 3)
+    want = torch_port.crops_for_boxes(torch.from_numpy(img), torch.from_numpy(boxes)).numpy()
+    table = ops.make_image_table([dev(img)])
+    got = ops.crop_resize(table, 1, dev(boxes), torch.zeros(len(boxes), dtype=torch.int32, device="cuda"), 256).cpu().numpy()
+    assert got.shape == want.shape
+    err = np.abs(got - want).reshape(len(boxes), -1).max(axis=1)
+    assert err.max() <= 1e-5, (int(err.argmax()), float(err.max()), boxes[int(err.argmax())])
