@@ -1005,3 +1005,39 @@ def test_crops_equal_the_reference_torch_cpu_ops_on_random_boxes(ops):
     assert got.shape == want.shape
     err = np.abs(got - want).reshape(len(boxes), -1).max(axis=1)
     assert err.max() <= 1e-5, (int(err.argmax()), float(err.max()), boxes[int(err.argmax())])
+
+
+def test_hot_path_end_to_end_equals_the_reference_torch_cpu_path(ops):
+    """One shelf through HotPath.step on the GPU (NMS -> crops -> VGG16 -> MAC -> cosine top-k, S = 256, fp32 convolutions)
+    against the same shelf through the reference's torch CPU ops in the reference's order (oracle/torch_port.hot_path:
+    torchvision nms, python crop loop + F.interpolate, VGG16, amax / cat / norm, the gather-and-argsort nearest_neighbors)."""
+    from oracle import torch_port
+    from cvpce_b200 import classification, pipeline
+    torch.backends.cudnn.allow_tf32 = False
+    H, W = 420, 560
+    img = synth.shelf_image(14, H, W)
+    boxes, scores = synth.shelf_candidates(14, H, W, n_products=9)
+    boxes = np.clip(boxes, 0, [W, H, W, H]).astype(np.float32)
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    port = torch_port.MACVGGPort().eval().requires_grad_(False)
+    port.block1.load_state_dict(enc.block1.state_dict())
+    port.block2.load_state_dict(enc.block2.state_dict())
+    gallery = torch.from_numpy(synth.unit_rows(np.random.RandomState(4), 257, 1024))
+    want_boxes, want_idx = torch_port.hot_path(port, gallery, torch.from_numpy(img), torch.from_numpy(boxes), torch.from_numpy(scores), k=3)
+    hp = pipeline.HotPath(enc.cuda(), gallery.cuda(), k=3, size=256, trunk_batch=4, detections_per_img=200)
+    out = hp.step([dev(img)], dev(boxes), dev(scores), dev(np.array([0, len(scores)], np.int32)), len(scores))
+    assert torch.equal(out["boxes"].cpu(), want_boxes)                                  # NMS: bit-exact keep list, in order
+    K = want_boxes.shape[0]
+    assert K >= 8 and out["topk_idx"].shape == (K, 3)
+    # embeddings of the CPU path for the tolerance check and the tie-aware index comparison
+    crops = torch_port.crops_for_boxes(torch.from_numpy(img), want_boxes)
+    with torch.no_grad():
+        emb = port(crops * 2 - 1)                                                        # utils.scale_to_tanh, production.py:63
+    np.testing.assert_allclose(out["embedding"].cpu().numpy(), emb.numpy(), rtol=1e-3, atol=2e-5)
+    sims = (emb.double() @ gallery.double().T)
+    top = sims.sort(dim=1, descending=True)
+    clear = (top.values[:, :3] - top.values[:, 1:4]) > 1e-5                              # ranks decided by more than rounding
+    got = out["topk_idx"].cpu()
+    assert torch.equal(got[clear], want_idx[clear]) and torch.equal(want_idx[clear], top.indices[:, :3][clear])
+    assert float(clear.float().mean()) > 0.9
