@@ -61,6 +61,8 @@ def parse():
                     "ranks: stored by the selection kernel into every peer's gather buffer over NVLink, or an NCCL all-gather")
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
                     "(800x1066 frame, 5 FPN levels) -> candidate selection -> NMS -> ... instead of scored candidate boxes")
+    ap.add_argument("--no-pad-channel", action="store_true", help="3-channel crops (the fast trunk's default is 4-channel crops with a "
+                    "zero 4th channel so that cuDNN skips its channel-padding pass before conv1_1)")
     ap.add_argument("--e2e-serial", action="store_true", help="e2e leg: upload all images before the step instead of overlapping "
                     "the upload with the step's own compute")
     ap.add_argument("--upload-group", type=int, default=4, help="e2e leg: shelf images per upload group")
@@ -242,7 +244,7 @@ def run_ours_shelves(args, world, rank, local):
     images, boxes_h, scores_h, seg_h, max_n = build_shelves(args, rank, n_shelves, device)
     hp = pipeline.HotPath(enc, gallery, k=args.k, trunk_batch=args.trunk_batch,
                           trunk_dtype={"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[args.trunk], channels_last=args.channels_last,
-                          n_streams=args.streams)
+                          n_streams=args.streams, pad_channel=not args.no_pad_channel)
     if args.sim == "f32":  # CUDA-core similarity instead of the tcgen05 kernel (debug / cross-check)
         from cvpce_b200 import ops
         ops_sim = ops.sim_topk
@@ -382,7 +384,8 @@ def run_ours_shelves(args, world, rank, local):
                    "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16 convolutions, not rebuilt (%s%s%s, tf32 convs %s)%s" % (
                        args.trunk, ", channels_last" if args.channels_last else "",
                        "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32,
-                       "" if args.plain_trunk else "; the 2x2 max-pools between them run in the library (cvpce_maxpool2x2_nhwc)"),
+                       "" if args.plain_trunk else "; the 2x2 max-pools between them run in the library (cvpce_maxpool2x2_nhwc)" +
+                       ("" if args.no_pad_channel else "; crops carry a zero 4th channel (conv1_1 against a zero-padded weight, same output)")),
                    "trunk_batch": args.trunk_batch,
                    "similarity": "tcgen05 bf16 + exact fp32 re-score" if args.sim == "tc" else "cuda-core fp32",
                    "l2": ("inputs (%.1f GB of shelf images per step) larger than L2" % (n_shelves * 3 * 1536 * 2048 * 4 / 1e9))

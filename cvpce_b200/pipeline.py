@@ -52,8 +52,9 @@ class _NoTimer:
 class HotPath:
     def __init__(self, encoder, gallery_embedding, k=1, size=256, antialias=True, iou_threshold=0.5, detections_per_img=200,
                  min_score=None, trunk_batch=128, trunk_dtype=torch.float32, channels_last=False, exact=True, rmac_levels=0,
-                 n_streams=1):
+                 n_streams=1, pad_channel=True):
         self.encoder = encoder
+        self.pad_channel = pad_channel
         self.gallery = classification.PreparedGallery(gallery_embedding)
         self.k = k
         self.size = size
@@ -161,16 +162,19 @@ class HotPath:
                                                       (boxes[:, 3].long() - boxes[:, 1].long()).clamp(min=0)).sum()) \
             if not isinstance(self.timer, _NoTimer) else 0.0
         image_idx32 = image_idx.to(torch.int32)
+        # fast trunk: 4-channel crops (zero 4th channel) so that cuDNN skips its channel-padding pass before conv1_1
+        pad4 = bool(self.channels_last and self.pad_channel and getattr(self.encoder, "fast_trunk", False)
+                    and getattr(self.encoder, "accepts_padded_input", False))
         if uploads is None:
             with self.timer.span("crop_resize", crop_bytes):
                 crops = ops.crop_resize(table, B, boxes, image_idx32, S, self.antialias, 0.5, self.affine,
-                                        self.trunk_dtype, self.channels_last)
+                                        self.trunk_dtype, self.channels_last, pad_channel=pad4)
             self.launches += 1
             ensure_crops = None
         else:
             # images arrive group by group (step_host): one crop launch per group, issued right before the first trunk batch
             # that needs it, after the main stream has waited for the group's upload
-            phys = torch.empty((K, S, S, 3) if self.channels_last else (K, 3, S, S), dtype=self.trunk_dtype, device=dev)
+            phys = torch.empty((K, S, S, 4 if pad4 else 3) if self.channels_last else (K, 3, S, S), dtype=self.trunk_dtype, device=dev)
             crops = phys.permute(0, 3, 1, 2) if self.channels_last else phys
             first_crop = [0]
             for c in counts_h.tolist():
@@ -186,7 +190,7 @@ class HotPath:
                     if b > a:
                         with self.timer.span("crop_resize", crop_bytes * (b - a) / max(K, 1)):
                             ops.crop_resize(table, B, boxes[a:b], image_idx32[a:b], S, self.antialias, 0.5, self.affine,
-                                            self.trunk_dtype, self.channels_last, out=phys[a:b])
+                                            self.trunk_dtype, self.channels_last, out=phys[a:b], pad_channel=pad4)
                         self.launches += 1
                 if not pending and self._stage_free is None:
                     self._stage_free = torch.cuda.Event()

@@ -38,7 +38,7 @@ typedef enum cvpce_status {
 } cvpce_status;
 
 typedef enum cvpce_dtype { CVPCE_F32 = 0, CVPCE_BF16 = 1, CVPCE_F16 = 2 } cvpce_dtype; /* F16: crop output, max-pool, dense NHWC MAC */
-typedef enum cvpce_layout { CVPCE_NCHW = 0, CVPCE_NHWC = 1 } cvpce_layout;
+typedef enum cvpce_layout { CVPCE_NCHW = 0, CVPCE_NHWC = 1, CVPCE_NHWC4 = 2 } cvpce_layout; /* NHWC4: crop output only (4th channel 0) */
 
 /* Thread-local message of the last failing call on this thread ("" if none). */
 CVPCE_API const char* cvpce_last_error(void);
@@ -143,7 +143,9 @@ CVPCE_API int cvpce_select_candidates(const cvpce_fpn_level* levels, int n_level
  * antialias   1: ATen _upsample_bilinear2d_aa (installed torchvision >= 0.17 default), 0: plain bilinear,
  *             align_corners=False (torchvision 0.9, the version the reference pins).
  * affine      [host] nullable f32[6] = {a_0,b_0,a_1,b_1,a_2,b_2}.
- * out         [K,3,S,S] (NCHW) or [K,S,S,3] (NHWC) of out_dtype.
+ * out         [K,3,S,S] (NCHW), [K,S,S,3] (NHWC) or [K,S,S,4] (NHWC4: a zero 4th channel, 16-byte pixels in fp32 -- the
+ *             input layout on which cuDNN runs VGG16's first convolution without its channel-padding pass, with a
+ *             weight zero-padded to 4 input channels; bit-identical convolution output) of out_dtype.
  * valid       (nullable) i32 [K]: 1, or 0 for an empty crop (x2<=x1 or y2<=y1 after truncation, where the reference
  *             raises); an empty crop's output is pad_value passed through the affine.
  */

@@ -1041,3 +1041,41 @@ def test_hot_path_end_to_end_equals_the_reference_torch_cpu_path(ops):
     got = out["topk_idx"].cpu()
     assert torch.equal(got[clear], want_idx[clear]) and torch.equal(want_idx[clear], top.indices[:, :3][clear])
     assert float(clear.float().mean()) > 0.9
+
+
+def test_four_channel_crops_and_padded_first_convolution(ops):
+    """NHWC4 crops are the NHWC crops plus a zero 4th channel (every dtype, both kernels), the fast trunk on them gives the
+    same feature maps bit for bit (the extra products are exact zeros), and HotPath uses them without changing any result."""
+    from cvpce_b200 import classification, pipeline
+    torch.backends.cudnn.allow_tf32 = False
+    img = dev(synth.shelf_image(15, 300, 410))
+    table = ops.make_image_table([img])
+    boxes = dev(np.array([[3, 4, 200, 280], [0, 0, 410, 300], [100, 100, 101, 250], [50.5, 60.5, 90.2, 75.9], [7, 7, 7, 7]], np.float32))
+    idx = torch.zeros(5, dtype=torch.int32, device="cuda")
+    aff = classification.tanh_normalize_affine()
+    for S in (256, 64, 37):                                                      # band kernel and direct kernel
+        for dtype in (torch.float32, torch.bfloat16, torch.float16):
+            c3 = ops.crop_resize(table, 1, boxes, idx, S, True, 0.5, aff, dtype, True)
+            c4 = ops.crop_resize(table, 1, boxes, idx, S, True, 0.5, aff, dtype, True, pad_channel=True)
+            assert c4.shape == (5, 4, S, S) and c4.is_contiguous(memory_format=torch.channels_last)
+            assert torch.equal(c4[:, :3], c3) and not bool(c4[:, 3].any()), (S, dtype)
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).cuda()
+    enc.enable_fast_trunk()
+    c3 = ops.crop_resize(table, 1, boxes, idx, 64, True, 0.5, aff, torch.float32, True)
+    c4 = ops.crop_resize(table, 1, boxes, idx, 64, True, 0.5, aff, torch.float32, True, pad_channel=True)
+    with torch.no_grad():
+        a4, a5 = enc.features(c3, normalized=True)
+        b4, b5 = enc.features(c4, normalized=True)
+    assert torch.equal(a4, b4) and torch.equal(a5, b5)
+    with pytest.raises(RuntimeError):
+        enc.features(c4, normalized=False)
+    b, s = synth.shelf_candidates(15, 300, 410, n_products=8)
+    b = np.clip(b, 0, [410, 300, 410, 300]).astype(np.float32)
+    gallery = dev(synth.unit_rows(np.random.RandomState(2), 300, 1024))
+    seg = dev(np.array([0, len(s)], np.int32))
+    outs = []
+    for pad in (True, False):
+        hp = pipeline.HotPath(enc, gallery, k=3, size=64, trunk_batch=8, channels_last=True, pad_channel=pad)
+        outs.append(hp.step([img], dev(b), dev(s), seg, len(s)))
+    assert torch.equal(outs[0]["embedding"], outs[1]["embedding"]) and torch.equal(outs[0]["topk_idx"], outs[1]["topk_idx"])
