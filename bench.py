@@ -57,6 +57,8 @@ def parse():
                     "is torch's own GPU default, TF32 convolutions: tools/tf32_check.py measures what that costs in accuracy)")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
+    ap.add_argument("--c5-chunks", type=int, default=2, help="c5 e2e leg: query chunks (upload of chunk c+1 overlaps the search of chunk c)")
+    ap.add_argument("--no-other-configs", action="store_true", help="headline only: skip the c2 / c1 / strict-fp32 / c5 legs reported under other_configs")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="c5, N > 1: how the per-rank top-k blocks reach the other "
                     "ranks: stored by the selection kernel into every peer's gather buffer over NVLink, or an NCCL all-gather")
     ap.add_argument("--from-head", action="store_true", help="start one stage earlier (SURVEY f1): synthetic GLN head outputs "
@@ -295,7 +297,9 @@ def run_ours_shelves(args, world, rank, local):
         out = run_step(images)
     e1.record()
     barrier(world)
-    ms_total = max_over_ranks(e0.elapsed_time(e1), world)
+    ms_rank = e0.elapsed_time(e1)
+    per_rank = gather_per_rank(ms_rank / args.steps, world)
+    ms_total = max_over_ranks(ms_rank, world)
     clocks = sampler.stop() if sampler else None
     launches = hp.launches
     stages = hp.timer.summary()
@@ -335,7 +339,9 @@ def run_ours_shelves(args, world, rank, local):
         e2e_step()
     e1.record()
     barrier(world)
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
+    ms_e2e_rank = e0.elapsed_time(e1)
+    per_rank_e2e = gather_per_rank(ms_e2e_rank / args.steps, world)
+    ms_e2e = max_over_ranks(ms_e2e_rank, world)
     e2e_value = total_crops * args.steps / (ms_e2e / 1e3)
 
     # -------- per-kernel rooflines from the events recorded inside the timed region
@@ -375,9 +381,14 @@ def run_ours_shelves(args, world, rank, local):
 
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True,
+        "ms_per_step": round(ms_total / args.steps, 3),
+        "ms_per_step_per_rank": {"min": round(min(per_rank), 3), "max": round(max(per_rank), 3)}, "higher_is_better": True,
         "scaling": "strong" if args.workload == "c4" and not args.shelves else "weak", "vs_baseline": None,
-        "dtype": args.trunk, "data": "synthetic",
+        # the arithmetic type of the path: the library's own kernels compute in fp32 in every mode; the torch trunk (not rebuilt)
+        # runs cuDNN TF32 convolutions unless --strict-fp32 (reported next to the headline under other_configs.strict_fp32)
+        "dtype": ({"f32": "tf32 trunk convolutions (torch/cuDNN default on GPU), f32 kernels" if torch.backends.cudnn.allow_tf32
+                   else "f32 (strict: fp32 convolutions and kernels)", "f16": "f16 trunk, f32 kernels", "bf16": "bf16 trunk, f32 kernels"}[args.trunk]),
+        "data": "synthetic",
         "config": {"workload": ("%s: %d shelves 2048x1536 x ~%d products per GPU -> " + ("GLN head outputs (800x1066, 160956 anchors) -> "
                                 "sigmoid/top-1000/decode -> " if args.from_head else "") + "NMS(0.5, top200) -> 256x256 crops -> "
                                 "VGG16(random init)+MAC -> cosine top-%d vs %d x 1024 gallery") % (args.workload, n_shelves, args.products, args.k, G),
@@ -395,6 +406,7 @@ def run_ours_shelves(args, world, rank, local):
                    "parallelism": "dp%d (independent images, no data-path collective)" % world},
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": round(ms_e2e / args.steps, 3),
+                "ms_per_step_per_rank": {"min": round(min(per_rank_e2e), 3), "max": round(max(per_rank_e2e), 3)},
                 "upload": "all images before the step" if args.e2e_serial else
                           "copy stream, groups of %d shelves, overlapped with the step's own compute (HotPath.upload_images)" % args.upload_group},
         "gpu_launches": launches,
@@ -461,59 +473,137 @@ def run_reference(args, world, rank):
 
 
 # ----------------------------------------------------------------------------------------------------- workload c5
+def gather_per_rank(ms, world):
+    """[ms of rank 0, ..., ms of rank world-1] on every rank."""
+    if world == 1:
+        return [ms]
+    import torch.distributed as dist
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return [float(x.item()) for x in out]
+
+
+def c5_parity_check(args, searcher, q, k, world, rank, device, n_check=512):
+    """In-run check on a query subsample: the search through the configured exchange (peer scatter) == the NCCL all-gather
+    form == a single-rank search of the WHOLE gallery (rank 0 regenerates all shards' rows: the synthetic generator does not
+    depend on the sharding), bit for bit -- scores and indices.  Returns (ok, detail)."""
+    from cvpce_b200 import dist as cdist
+    import torch.distributed as dist
+    G, D = searcher.global_rows, searcher.D
+    sub = q[torch.linspace(0, q.shape[0] - 1, n_check, device=device).long()].contiguous()
+    s_a, i_a = searcher.search(sub, k)
+    ok, detail = True, {}
+    if world > 1:
+        other = cdist.ShardedGallery(searcher.g32, searcher.idx_base, world, rank, searcher.group, exchange="nccl", global_rows=G)
+        s_b, i_b = other.search(sub, k)
+        same = bool(torch.equal(s_a, s_b) and torch.equal(i_a, i_b))
+        detail["p2p_equals_nccl" if searcher.exchange == "p2p" else "nccl_equals_nccl"] = same
+        ok = ok and same
+        # partitioned-queries form (what the e2e leg runs) against the resident-queries form
+        lo, hi = cdist.shard_range(n_check, world, rank)
+        s_c, i_c = searcher.search_partitioned(sub[lo:hi], lo, n_check, k)
+        same = bool(torch.equal(s_a, s_c) and torch.equal(i_a, i_c))
+        detail["partitioned_equals_resident"] = same
+        ok = ok and same
+        del other
+    if rank == 0:
+        whole = cdist.ShardedGallery.synthetic(G, D, 1, 0, device, seed=5)
+        s_w, i_w = whole.search(sub, k)
+        same = bool(torch.equal(s_a, s_w) and torch.equal(i_a, i_w))
+        detail["sharded_equals_single_rank_whole_gallery"] = same
+        ok = ok and same
+        del whole
+        torch.cuda.empty_cache()
+    if world > 1:
+        flag = torch.tensor([1 if ok else 0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = bool(int(flag.item()))
+    return ok, detail
+
+
 def run_ours_c5(args, world, rank, local):
     """BASELINE.json configs[4]: 1M x 512 gallery sharded over the ranks, 100k queries, cosine top-5, all-gather + merge.
-    Strong scaling: the gallery is fixed, each rank searches G/world rows for ALL queries."""
+    Strong scaling: the gallery is fixed, each rank searches G/world rows for ALL queries.
+    `value`: queries resident in HBM on every rank.  `e2e`: the queries start in PINNED HOST memory, partitioned over the ranks
+    (each rank uploads 1/world of them; cvpce_rows_prepare_scatter replicates the block to every rank over NVLink), each rank
+    downloads its block of the merged result; upload of query chunk c+1 overlaps the search of chunk c."""
     from cvpce_b200 import dist as cdist
     device = torch.device("cuda", local)
     peaks = measured_peaks()
-    G = args.gallery or 1_000_000
+    G = args.gallery if (args.gallery and args.workload == "c5") else 1_000_000
     Q, D, k = args.queries, 512, args.k
+    steps, warmup = args.steps, max(args.warmup, 3)
     searcher = cdist.ShardedGallery.synthetic(G, D, world, rank, device, seed=5, exchange=args.exchange)
     q = cdist.synthetic_queries(Q, D, device, seed=6)
     # the timed region is tens of milliseconds: start sampling clocks before the warm-up so that the sampler (200 ms period)
     # has readings taken under the same load
     sampler = ClockSampler(local) if rank == 0 else None
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         sim, idx = searcher.search(q, k)
     barrier(world)
+    l0 = searcher.launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         sim, idx = searcher.search(q, k)
     e1.record()
     barrier(world)
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
-    # end to end: queries in pinned host memory on every rank, H2D per step, merged [Q,k] indices + scores back to the host
-    q_h = q.cpu().pin_memory()
-
-    def e2e_step():
-        s_, i_ = searcher.search(q_h.to(device, non_blocking=True), k)
-        return s_.cpu(), i_.cpu()
-
-    s_h, i_h = e2e_step()
+    ms_rank = e0.elapsed_time(e1)
+    per_rank = gather_per_rank(ms_rank / steps, world)
+    ms = max_over_ranks(ms_rank, world)
+    launches = searcher.launches - l0
+    # ---- end to end: queries in pinned host memory, partitioned over the ranks and over `chunks` query chunks
+    chunks = max(1, args.c5_chunks)
+    parts = cdist.partition_query_chunks(Q, world, rank, chunks)
+    blocks_h = [(q[g0: g0 + n].cpu().pin_memory(), lo, qc) for (g0, n, lo, qc) in parts]
+    out_h = [(torch.empty((n, k), dtype=torch.float32).pin_memory(), torch.empty((n, k), dtype=torch.int64).pin_memory())
+             for (_, n, _, _) in parts]
+    for _ in range(2):
+        res = searcher.search_host(blocks_h, k, out=out_h)
+    # the e2e result (this rank's rows) equals the resident-queries result
+    e2e_same = all(bool(torch.equal(sh, sim[g0: g0 + n].cpu()) and torch.equal(ih, idx[g0: g0 + n].cpu()))
+                   for (sh, ih), (g0, n, _, _) in zip(res, parts))
     barrier(world)
     e0.record()
-    for _ in range(args.steps):
-        e2e_step()
+    for _ in range(steps):
+        searcher.search_host(blocks_h, k, out=out_h)
     e1.record()
     barrier(world)
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
+    ms_e2e_rank = e0.elapsed_time(e1)
+    per_rank_e2e = gather_per_rank(ms_e2e_rank / steps, world)
+    ms_e2e = max_over_ranks(ms_e2e_rank, world)
     clocks = sampler.stop() if sampler else None
-    flops = 2.0 * Q * G * D * args.steps
+    parity_ok, parity = c5_parity_check(args, searcher, q, k, world, rank, device)
+    parity["e2e_rows_equal_resident"] = e2e_same
+    parity_ok = parity_ok and e2e_same
+    flops = 2.0 * Q * G * D * steps
     tf = flops / (ms / 1e3) / 1e12 / world
-    return {"metric": "gallery queries matched/sec (cosine top-%d)" % k, "value": round(Q * args.steps / (ms / 1e3), 1), "unit": "queries/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
+    h2d = sum(b[0].numel() * 4 for b in blocks_h)
+    d2h = sum(sh.numel() * 4 + ih.numel() * 8 for sh, ih in out_h)
+    line = {"metric": "gallery queries matched/sec (cosine top-%d)" % k, "value": round(Q * steps / (ms / 1e3), 1), "unit": "queries/s",
+            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": round(ms / steps, 3),
+            "ms_per_step_per_rank": {"min": round(min(per_rank), 3), "max": round(max(per_rank), 3)},
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 operands, f32 accumulate + exact f32 re-score",
             "data": "synthetic", "config": {"workload": "c5: %d x %d gallery sharded over %d GPU(s), %d queries, top-%d, all-gather merge" % (G, D, world, Q, k),
                                "exchange": "none (1 GPU)" if world == 1 else ("selection-kernel stores into peer gather buffers over NVLink (symmetric memory) + barrier"
-                                                                           if args.exchange == "p2p" else "NCCL all-gather")},
+                                                                           if searcher.exchange == "p2p" else "NCCL all-gather"),
+                               "l2": "operands (%.0f MB bf16 gallery shard + %.0f MB fp32 for the re-score per GPU) larger than L2" % (G / world * D * 2 / 1e6, G / world * D * 4 / 1e6)},
             "roofline": {"kernel": "sim_topk", "bound": "tensor", "achieved": round(tf, 1), "peak": peaks["tensor_sustained"], "unit": "TFLOP/s",
-                         "frac": round(tf / peaks["tensor_sustained"], 4), "traffic": None,
-                         "peak_source": peaks["source"] + " (bf16_tflops_sustained); includes prepare + re-score + merge time"},
-            "e2e": {"value": round(Q * args.steps / (ms_e2e / 1e3), 1), "unit": "queries/s", "h2d_bytes_per_step": int(q_h.numel() * 4),
-                    "d2h_bytes_per_step": int(s_h.numel() * 4 + i_h.numel() * 8), "ms_per_step": round(ms_e2e / args.steps, 3)},
-            "gpu_launches": searcher.launches, "clocks": clocks}
+                         "frac": round(tf / peaks["tensor_sustained"], 4), "traffic": None, "per_gpu": True,
+                         "peak_source": peaks["source"] + " (bf16_tflops_sustained); the time includes prepare + re-score + exchange + merge"},
+            "e2e": {"value": round(Q * steps / (ms_e2e / 1e3), 1), "unit": "queries/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "h2d_bytes_per_step_all_ranks": int(Q * D * 4), "ms_per_step": round(ms_e2e / steps, 3),
+                    "ms_per_step_per_rank": {"min": round(min(per_rank_e2e), 3), "max": round(max(per_rank_e2e), 3)},
+                    "how": "each rank uploads 1/%d of the queries (%d chunk(s), upload of chunk c+1 overlapped with the search of chunk c), "
+                           "%s, each rank downloads its rows of the merged top-k" % (world, chunks,
+                           "replicates its block into every rank's query buffers with peer stores (cvpce_rows_prepare_scatter)"
+                           if (world > 1 and searcher.exchange == "p2p") else ("all-gathers the blocks (NCCL)" if world > 1 else "no exchange"))},
+            "c5_parity": parity_ok, "c5_parity_detail": parity,
+            "gpu_launches": launches, "clocks": clocks}
+    del searcher, q, blocks_h
+    torch.cuda.empty_cache()
+    return line
 
 
 def main():

@@ -40,6 +40,8 @@ SIGNATURES = {
     "cvpce_version": (c_int, []),
     "cvpce_device_check": (c_int, []),
     "cvpce_shutdown": (c_int, []),
+    "cvpce_tuning_set": (c_int, [ctypes.c_char_p, c_int]),
+    "cvpce_tuning_get": (c_int, [ctypes.c_char_p]),
     "cvpce_nms_batched": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p]),
     "cvpce_nms_segments": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_float, c_float, c_int, c_void_p, c_void_p,
@@ -57,6 +59,7 @@ SIGNATURES = {
     "cvpce_rmac_regions": (c_int, [c_int, c_int, c_int, c_void_p, c_int]),
     "cvpce_l2norm_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_float, c_void_p]),
     "cvpce_rows_prepare": (c_int, [c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
+    "cvpce_rows_prepare_scatter": (c_int, [c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "cvpce_sim_topk_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "cvpce_sim_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -85,6 +88,32 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def tuning_set(name, value):
+    """Development override of a launch heuristic (cvpce_tuning_set; 0 = automatic): A/B measurements and kernel cross-checks."""
+    check(load().cvpce_tuning_set(name.encode(), int(value)), "cvpce_tuning_set")
+
+
+def tuning_get(name):
+    return int(load().cvpce_tuning_get(name.encode()))
+
+
+class tuning:
+    """with _lib.tuning(crop_kernel=1): ...  -- sets the knobs, restores the previous values on exit."""
+
+    def __init__(self, **knobs):
+        self.knobs = knobs
+
+    def __enter__(self):
+        self.saved = {k: tuning_get(k) for k in self.knobs}
+        for k, v in self.knobs.items():
+            tuning_set(k, v)
+        return self
+
+    def __exit__(self, *exc):
+        for k, v in self.saved.items():
+            tuning_set(k, v)
 
 
 def last_error():

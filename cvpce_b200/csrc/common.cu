@@ -1,6 +1,7 @@
 // Library-wide state: last-error string, device check, shutdown.
 #include "common.cuh"
 #include <string.h>
+#include <atomic>
 
 namespace cvpce {
 
@@ -58,6 +59,36 @@ int sm_count() {
 
 void tma_cache_clear();  // sim_topk_sm100.cu
 
+// ---- tuning table: explicit, process-wide development overrides (cvpce_tuning_set); never read from the environment
+struct TuningEntry {
+  const char* name;
+  std::atomic<int> value;
+};
+static TuningEntry g_tuning[] = {
+    {"crop_kernel", {0}},       // 0: automatic; 1: shared-memory band kernel; 2: column-marching kernel; 3: direct kernel
+    {"crop_band_rows", {0}},    // 0: automatic; else output rows per CTA of the antialias kernels (power of two, 8..256)
+    {"sim_plan", {0}},          // 0: automatic; 1: one CTA per (query block, split) (round-1 grid); 2: persistent, unicast; 3: persistent, B multicast over CTA pairs
+    {"sim_split", {0}},         // sim_plan 1: forced split count (0: cost model)
+    {"sim_ctas", {0}},          // persistent plans: forced CTA count (0: SM count)
+    {"mac_cluster", {0}},       // 0: automatic; 2 / 4 / 8: cluster size of the dense channels-last MAC kernel
+    {"pool_persistent", {0}},   // 0: automatic; 1: cluster per image (round-1 grid); 2: persistent pixel-range walk
+};
+
+int tuning(const char* name) {
+  for (auto& e : g_tuning)
+    if (strcmp(e.name, name) == 0) return e.value.load(std::memory_order_relaxed);
+  return 0;
+}
+
+int ensure_dynamic_smem(const void* func, size_t bytes) {
+  // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device, per-function attribute; setting it costs a table lookup
+  // in the runtime, so it is simply set on every launch that needs more than the 48 KB default (no cached flag that a
+  // second device or a second host thread could find stale).
+  if (bytes <= 32 * 1024) return CVPCE_OK;  // the 48 KB default limit also counts the kernel's static shared memory
+  CVPCE_CUDA_OK(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return CVPCE_OK;
+}
+
 }  // namespace cvpce
 
 extern "C" {
@@ -69,5 +100,15 @@ int cvpce_shutdown(void) {
   cvpce::tma_cache_clear();
   return CVPCE_OK;
 }
+int cvpce_tuning_set(const char* name, int value) {
+  if (name)
+    for (auto& e : cvpce::g_tuning)
+      if (strcmp(e.name, name) == 0) {
+        e.value.store(value, std::memory_order_relaxed);
+        return CVPCE_OK;
+      }
+  return cvpce::set_err(CVPCE_ERR_INVALID_ARG, "cvpce_tuning_set: unknown knob '%s'", name ? name : "(null)");
+}
+int cvpce_tuning_get(const char* name) { return name ? cvpce::tuning(name) : 0; }
 
 }  // extern "C"

@@ -757,9 +757,9 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
     // The pixel-split kernel works with any cluster size that divides every C.  Measured on B200 (tools/kbench.py pool,
     // two 512 x 16 x 16 maps per image): about 512 CTAs -- one resident wave, ~0.5 MB streamed per CTA before its
     // reduction tail -- is the sweet spot: B = 256: 0.77 of HBM with clusters of 2 against 0.65 with 4 or 8 (a ragged
-    // second wave); B = 128: 0.62 with 4 against 0.52 (8) and 0.50 (2, too few CTAs).  CVPCE_MAC_CLUSTER overrides.
-    const char* e = getenv("CVPCE_MAC_CLUSTER");
-    const int want = e ? atoi(e) : (B >= 256 ? 2 : (B >= 128 ? 4 : kPoolCluster));
+    // second wave); B = 128: 0.62 with 4 against 0.52 (8) and 0.50 (2, too few CTAs).  cvpce_tuning_set("mac_cluster", n) overrides.
+    const int forced = tuning("mac_cluster");
+    const int want = forced ? forced : (B >= 256 ? 2 : (B >= 128 ? 4 : kPoolCluster));
     if (want == 2 || want == 4) {
       bool ok = true;
       for (int m = 0; m < n_maps; ++m) ok = ok && maps[m].C % want == 0;

@@ -454,14 +454,19 @@ extern "C" int cvpce_select_candidates(const cvpce_fpn_level* levels, int n_leve
   p.seg_counts = seg_counts;
   p.level_counts = level_counts;
 
-  static thread_local bool configured = false;
-  if (!configured) {
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(select_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSelDynSmem));
-    configured = true;
-  }
+  // per-device attribute: set on every launch (a cached flag would be stale after cudaSetDevice to a second GPU)
+  CVPCE_CUDA_OK(cudaFuncSetAttribute(select_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSelDynSmem));
   // one CTA per level; if this device refuses a cluster of exactly n_levels CTAs, pad to the next power of two (the
   // padding CTAs only take part in the count exchange)
-  static thread_local int exact_ok[CVPCE_SELECT_MAX_LEVELS + 1] = {0};  // 0 unknown, 1 yes, -1 no
+  // cached per (thread, device): 0 unknown, 1 yes, -1 no
+  static thread_local int exact_dev = -1;
+  static thread_local int exact_ok[CVPCE_SELECT_MAX_LEVELS + 1] = {0};
+  int cur_dev = 0;
+  CVPCE_CUDA_OK(cudaGetDevice(&cur_dev));
+  if (cur_dev != exact_dev) {
+    for (int i = 0; i <= CVPCE_SELECT_MAX_LEVELS; ++i) exact_ok[i] = 0;
+    exact_dev = cur_dev;
+  }
   int csize = n_levels;
   if (exact_ok[n_levels] == 0) {
     cudaLaunchConfig_t q = {};

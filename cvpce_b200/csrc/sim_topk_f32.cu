@@ -45,6 +45,54 @@ __global__ void __launch_bounds__(256) rows_prepare_kernel(const float* __restri
 }
 
 // ------------------------------------------------------------------------------------------------------------------
+// rows_prepare_scatter: the same preparation of THIS rank's block of query rows, with the three results (fp32 rows for
+// the exact re-score, unit bf16 rows for the tensor cores, inverse norms) stored into the same row slot of EVERY rank's
+// query buffers (peer memory over NVLink): "prepare, then all-gather" as one kernel whose stores are the transfer.
+// One warp per row, 16-byte loads, 16-byte (fp32) and 8-byte (bf16) stores: a warp writes 512 / 256 contiguous bytes.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kMaxPrepPeers = 16;
+struct PrepTargets {
+  int n;
+  float* f32[kMaxPrepPeers];
+  __nv_bfloat16* bf16[kMaxPrepPeers];
+  float* inv[kMaxPrepPeers];
+};
+
+__global__ void __launch_bounds__(256) rows_prepare_scatter_kernel(const float* __restrict__ x, long long R, int D, int normalize,
+                                                                   float eps, const PrepTargets t) {
+  const int lane = threadIdx.x & 31;
+  const long long warps_total = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < R; row += warps_total) {
+    const float4* r = reinterpret_cast<const float4*>(x + row * D);
+    float inv = 1.f;
+    if (normalize) {
+      float s = 0.f;
+      for (int i = lane; i < (D >> 2); i += 32) {
+        const float4 v = __ldg(r + i);
+        s = fmaf(v.x, v.x, s);
+        s = fmaf(v.y, v.y, s);
+        s = fmaf(v.z, v.z, s);
+        s = fmaf(v.w, v.w, s);
+      }
+      s = warp_sum(s);
+      inv = 1.f / fmaxf(sqrtf(s), eps);
+    }
+    if (lane == 0)
+      for (int p = 0; p < t.n; ++p)
+        if (t.inv[p]) t.inv[p][row] = inv;
+    for (int i = lane; i < (D >> 2); i += 32) {
+      const float4 v = __ldg(r + i);  // second pass: L1 / L2 hit
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * inv, v.y * inv), hi = __floats2bfloat162_rn(v.z * inv, v.w * inv);
+      const uint2 b = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+      for (int p = 0; p < t.n; ++p) {
+        if (t.f32[p]) reinterpret_cast<float4*>(t.f32[p] + row * D)[i] = v;
+        if (t.bf16[p]) reinterpret_cast<uint2*>(t.bf16[p] + row * D)[i] = b;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
 // fp32 similarity + top-k.  CTA = 64 query rows, streams the gallery in 64-row tiles, 4x4 register micro-tiles.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int F_BM = 64, F_BN = 64, F_BK = 16, F_THREADS = 256, F_KMAX = 64;
@@ -209,6 +257,32 @@ extern "C" int cvpce_rows_prepare(const float* x, int64_t R, int D, int normaliz
   rows_prepare_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, R, D, normalize, eps,
                                                                           reinterpret_cast<__nv_bfloat16*>(x_bf16), inv_norm);
   CVPCE_LAUNCH_OK("rows_prepare_kernel");
+  return CVPCE_OK;
+}
+
+extern "C" int cvpce_rows_prepare_scatter(const float* x, int64_t R, int D, int normalize, float eps, float* const* peer_f32,
+                                          void* const* peer_bf16, float* const* peer_inv_norm, int n_peers, void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(R >= 0 && D > 0, CVPCE_ERR_INVALID_ARG, "rows_prepare_scatter: bad shape R=%lld D=%d", (long long)R, D);
+  CVPCE_REQUIRE(D % 4 == 0, CVPCE_ERR_UNSUPPORTED, "rows_prepare_scatter: D=%d must be a multiple of 4", D);
+  CVPCE_REQUIRE(n_peers >= 1 && n_peers <= kMaxPrepPeers, CVPCE_ERR_INVALID_ARG, "rows_prepare_scatter: n_peers=%d outside [1,%d]",
+                n_peers, kMaxPrepPeers);
+  if (R == 0) return CVPCE_OK;
+  CVPCE_REQUIRE(x && aligned16(x), CVPCE_ERR_INVALID_ARG, "rows_prepare_scatter: x null or not 16-byte aligned");
+  PrepTargets t;
+  t.n = n_peers;
+  for (int p = 0; p < n_peers; ++p) {
+    t.f32[p] = peer_f32 ? peer_f32[p] : nullptr;
+    t.bf16[p] = peer_bf16 ? reinterpret_cast<__nv_bfloat16*>(peer_bf16[p]) : nullptr;
+    t.inv[p] = peer_inv_norm ? peer_inv_norm[p] : nullptr;
+    CVPCE_REQUIRE(aligned16(t.f32[p]) && (reinterpret_cast<uintptr_t>(t.bf16[p]) & 7u) == 0, CVPCE_ERR_INVALID_ARG,
+                  "rows_prepare_scatter: peer %d buffers must be 16-byte (fp32) / 8-byte (bf16) aligned", p);
+  }
+  if (int rc = require_sm100()) return rc;
+  long long blocks = (R + 7) / 8;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  rows_prepare_scatter_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, R, D, normalize, eps, t);
+  CVPCE_LAUNCH_OK("rows_prepare_scatter_kernel");
   return CVPCE_OK;
 }
 

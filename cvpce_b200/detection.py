@@ -45,7 +45,7 @@ def postprocess_detections(head_outputs, anchors, image_shapes, score_thresh=0.0
     model's thresholds passed explicitly: a list of {'boxes','scores','labels'} per image."""
     boxes, scores, counts, stride = postprocess_detections_batch(head_outputs, anchors, image_shapes, score_thresh,
                                                                  topk_candidates, nms_thresh, detections_per_img)
-    counts = counts.tolist()  # the one host read
+    counts = ops.checked_counts(counts.cpu(), "postprocess_detections").tolist()  # the one host read
     out = []
     for b, n in enumerate(counts):
         out.append({"boxes": boxes[b * stride: b * stride + n], "scores": scores[b * stride: b * stride + n],

@@ -49,7 +49,8 @@ def nms_batched(boxes, scores, seg_offsets, max_n, iou_threshold=0.5, min_score=
 
     boxes f32[total,4], scores f32[total], seg_offsets i32[n_images+1] (device), max_n = host upper bound of candidates per image.
     Returns (keep i64[total] local indices laid out per segment, keep_counts i32[n_images], kept_boxes|None, kept_scores|None).
-    No host synchronisation."""
+    No host synchronisation.  keep_counts[b] = -1 flags a segment longer than max_n: pass the host copy of the counts through
+    checked_counts() before using them."""
     _need_cuda("nms_batched", boxes, scores, seg_offsets, box_scale)
     boxes = boxes.contiguous().float()
     scores = scores.contiguous().float()
@@ -218,6 +219,17 @@ def select_candidates(cls_logits, bbox_regression, anchors, image_sizes, score_t
     return boxes, scores, labels, seg_counts, level_counts, seg_stride
 
 
+def checked_counts(counts_host, what="nms"):
+    """The kernels report a segment with more candidates than the caller's max_n bound (or than CVPCE_NMS_MAX_N) by writing
+    keep_counts[b] = -1.  Call this on the HOST copy of the counts (the step's one D2H read): a wrong bound raises instead of
+    silently dropping or garbling detections."""
+    bad = (counts_host < 0).nonzero()
+    if bad.numel():
+        raise RuntimeError("%s: image(s) %s hold more candidates than max_n / CVPCE_NMS_MAX_N=%d allows (keep_counts = -1)"
+                           % (what, bad.flatten().tolist()[:8], _lib.NMS_MAX_N))
+    return counts_host
+
+
 def nms(boxes, scores, iou_threshold):
     """Drop-in for torchvision.ops.nms(boxes, scores, iou_threshold) -> int64[K] (one D2H read of the count)."""
     _need_cuda("nms", boxes, scores)
@@ -226,7 +238,7 @@ def nms(boxes, scores, iou_threshold):
         return torch.empty(0, dtype=torch.int64, device=boxes.device)
     seg = torch.tensor([0, n], dtype=torch.int32, device=boxes.device)
     keep, counts, _, _ = nms_batched(boxes, scores, seg, n, iou_threshold)
-    return keep[: int(counts.item())]
+    return keep[: int(checked_counts(counts.cpu(), "nms")[0])]
 
 
 def batched_nms(boxes, scores, idxs, iou_threshold):
@@ -375,6 +387,22 @@ def rows_prepare(x, normalize=True, eps=1e-8, want_bf16=True):
     rc = _lib.load().cvpce_rows_prepare(_ptr(x), R, D, 1 if normalize else 0, float(eps), _ptr(xb), _ptr(inv), _stream())
     _lib.check(rc, "cvpce_rows_prepare")
     return xb, inv
+
+
+def rows_prepare_scatter(x, peer_f32_ptrs, peer_bf16_ptrs, peer_inv_ptrs, normalize=True, eps=1e-8):
+    """rows_prepare of this rank's block x f32[R,D] whose three results are stored by the kernel into every rank's query
+    buffers: the pointer lists are raw device addresses (ints) of row 0 of THIS block inside each rank's [Q,D] fp32, [Q,D]
+    bf16 and [Q] inverse-norm buffers (peer memory over NVLink).  The caller synchronises the ranks before searching."""
+    _need_cuda("rows_prepare_scatter", x)
+    x = x.contiguous().float()
+    R, D = x.shape
+    n = len(peer_f32_ptrs)
+    if n < 1 or len(peer_bf16_ptrs) != n or len(peer_inv_ptrs) != n:
+        raise RuntimeError("rows_prepare_scatter: need one fp32, one bf16 and one inverse-norm pointer per peer")
+    arrs = [(ctypes.c_void_p * n)(*[int(p) for p in ptrs]) for ptrs in (peer_f32_ptrs, peer_bf16_ptrs, peer_inv_ptrs)]
+    rc = _lib.load().cvpce_rows_prepare_scatter(_ptr(x), R, D, 1 if normalize else 0, float(eps),
+                                                *[ctypes.cast(a, ctypes.c_void_p) for a in arrs], n, _stream())
+    _lib.check(rc, "cvpce_rows_prepare_scatter")
 
 
 def sim_topk_f32(queries, gallery, k=1, idx_base=0, normalize=True, eps=1e-8):

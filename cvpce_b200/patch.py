@@ -8,7 +8,7 @@ import sys
 
 import torch
 
-from . import classification, datautils, detection, metrics, ops, planograms, production
+from . import _lib, classification, datautils, detection, metrics, ops, planograms, production
 
 _saved = []
 
@@ -18,10 +18,16 @@ def _swap(obj, name, new):
     setattr(obj, name, new)
 
 
-def _batched_nms(boxes, scores, idxs, iou_threshold):
-    if boxes.is_cuda:
-        return ops.batched_nms(boxes, scores, idxs, iou_threshold)
-    raise RuntimeError("cvpce_b200.patch: batched_nms called with CPU tensors; the B200 path has no CPU fallback")
+def _make_batched_nms(original):
+    """retinanet.box_ops IS torchvision.ops.boxes, a module shared by every torchvision detector of the process (Faster R-CNN
+    RPN / RoIHeads, FCOS, SSD ...).  Only calls the sm_100a kernel is built for are taken over: CUDA boxes, at most
+    CVPCE_NMS_MAX_N of them.  Anything else is not this library's call site and runs torchvision's own function unchanged
+    (an RPN training step may pass 10k boxes; data-preparation code may call it on the host)."""
+    def _batched_nms(boxes, scores, idxs, iou_threshold):
+        if boxes.is_cuda and boxes.shape[0] <= _lib.NMS_MAX_N:
+            return ops.batched_nms(boxes, scores, idxs, iou_threshold)
+        return original(boxes, scores, idxs, iou_threshold)
+    return _batched_nms
 
 
 def _macvgg_forward(self, x, eps=1e-8):
@@ -48,10 +54,17 @@ def _generate_proposals_and_images(self, image):
     return boxes, datautils.crops_for_classification(image.to(boxes.device), boxes)
 
 
-def _resize_for_classification(img):
-    if not img.is_cuda:
-        raise RuntimeError("cvpce_b200.patch: resize_for_classification needs a CUDA image; no CPU fallback")
-    return datautils.resize_for_classification(img)
+def _make_resize_for_classification(original):
+    """datautils.resize_for_classification has two kinds of callers in the reference: the hot path's per-box crop loop
+    (production.py:20, classification_eval.py:24, detection_eval.py:29 -- replaced wholesale by the batched kernel, and served
+    here when a straggler passes a CUDA crop) and HOST-side data preparation that is not on the path at all: the gallery
+    dataset's __getitem__ inside forked DataLoader workers (datautils.py:511, under Classifier.build_index) and
+    PlanogramComparator.compare on a host image (production.py:111).  Host images keep running the reference's own function."""
+    def _resize_for_classification(img):
+        if img.is_cuda:
+            return datautils.resize_for_classification(img)
+        return original(img)
+    return _resize_for_classification
 
 
 def _classify(self, images, return_embedding=False):
@@ -64,7 +77,7 @@ def apply(ref=None):
         return
     ref = ref or sys.modules.get("cvpce")
     from torchvision.models.detection import retinanet
-    _swap(retinanet.box_ops, "batched_nms", _batched_nms)                       # tv:retinanet.py:560
+    _swap(retinanet.box_ops, "batched_nms", _make_batched_nms(retinanet.box_ops.batched_nms))   # tv:retinanet.py:560
     if ref is None:
         return
     gln = getattr(getattr(ref.models, "proposals", None), "GaussianLayerNetwork", None)
@@ -84,7 +97,7 @@ def apply(ref=None):
         _swap(ref.utils, "nearest_neighbors", classification.nearest_neighbors) # utils.py:20
     _swap(rc.MACVGG, "forward", _macvgg_forward)                                # classification.py:38-51
     _swap(rc.MACResNet, "forward", _macresnet_forward)                          # classification.py:78-85
-    _swap(rd, "resize_for_classification", _resize_for_classification)          # datautils.py:234
+    _swap(rd, "resize_for_classification", _make_resize_for_classification(rd.resize_for_classification))  # datautils.py:234
     _swap(rp.ProposalGenerator, "generate_proposals_and_images", _generate_proposals_and_images)  # production.py:16
     # f3: detection-evaluation matching and the planogram box_iou call site
     rm = getattr(ref, "metrics", None)

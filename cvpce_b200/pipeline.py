@@ -148,7 +148,7 @@ class HotPath:
 
     def _classify_kept(self, images, counts, kept_boxes, seg_begin, uploads=None):
         B = len(images)
-        counts_h = counts.cpu()  # the one host synchronisation of the step
+        counts_h = ops.checked_counts(counts.cpu(), "HotPath.step")  # the one host synchronisation of the step
         K = int(counts_h.sum())
         dev = kept_boxes.device
         counts64 = counts.to(torch.int64)

@@ -88,8 +88,10 @@ class Classifier:
         searches the shard, exchanges the per-rank top-k blocks and merges, and every rank maps the same GLOBAL indices to
         annotations (the annotation list stays whole on every rank).  Returns the ShardedGallery."""
         from . import dist as cdist
-        lo, hi = cdist.shard_range(int(self.embedding.shape[0]), world, rank)
-        self._sharded = cdist.ShardedGallery(self.embedding[lo:hi].to(self.emb_device), lo, world, rank, group, exchange=exchange)
+        G = int(self.embedding.shape[0])
+        lo, hi = cdist.shard_range(G, world, rank)
+        self._sharded = cdist.ShardedGallery(self.embedding[lo:hi].to(self.emb_device), lo, world, rank, group, exchange=exchange,
+                                             global_rows=G)
         return self._sharded
 
     def prepared_gallery(self):
@@ -115,10 +117,15 @@ class Classifier:
             return (res, emb) if return_embedding else res
         emb = self.embed(images)
         if getattr(self, "_sharded", None) is not None:
+            # every rank must pass the SAME images here (the shards are searched for all queries and the per-rank blocks merged);
+            # image data-parallel ranks keep the whole gallery on every GPU instead (dist.partition_images)
             _, nearest = self._sharded.search(emb, self.k)
         else:
             _, nearest = classification.similarity_topk(self.embedding, emb, self.k, prepared=self.prepared_gallery())
-        nearest = nearest.cpu().tolist()
+        nearest = nearest.cpu()
+        if bool((nearest < 0).any()):  # padding (-1) can only survive when the gallery holds fewer rows than requested
+            raise RuntimeError("Classifier.classify: the search returned padding indices (gallery smaller than k?)")
+        nearest = nearest.tolist()
         res = [[self.annotations[j] for j in row] for row in nearest]
         if return_embedding:
             return res, emb

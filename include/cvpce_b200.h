@@ -48,6 +48,12 @@ CVPCE_API int cvpce_version(void);
 CVPCE_API int cvpce_device_check(void);
 /* Frees lazily created module state (TMA descriptor cache). Safe to call more than once. */
 CVPCE_API int cvpce_shutdown(void);
+/* Development overrides of launch heuristics (A/B measurements, cross-checks of alternative kernels): process-wide named
+ * integers, 0 = automatic.  Knobs: "crop_kernel", "crop_band_rows", "sim_plan", "sim_split", "sim_ctas", "mac_cluster", "pool_persistent"
+ * (csrc/common.cu lists their values).  Results never depend on them beyond fp32 summation order; the library reads no
+ * environment variables.  Unknown names return CVPCE_ERR_INVALID_ARG. */
+CVPCE_API int cvpce_tuning_set(const char* name, int value);
+CVPCE_API int cvpce_tuning_get(const char* name);
 
 /* ------------------------------------------------------------------------------------------------------------
  * a1 + a2  Batched greedy IoU-NMS.
@@ -235,6 +241,15 @@ CVPCE_API int cvpce_maxpool2x2_nhwc(const void* in, int dtype, int B, int H, int
  */
 CVPCE_API int cvpce_rows_prepare(const float* x, int64_t R, int D, int normalize, float eps,
                        void* x_bf16, float* inv_norm, void* stream);
+/* Gallery-sharded search with the QUERIES partitioned over the ranks too (each rank received 1/W of them from its host):
+ * the same preparation of this rank's R rows, with the results stored into this block's row slot of EVERY rank's query
+ * buffers -- peer_f32[p] / peer_bf16[p] / peer_inv_norm[p] [host arrays of n_peers <= 16 device pointers, each array nullable]
+ * address row 0 of this rank's block inside rank p's [Q,D] fp32, [Q,D] bf16 and [Q] inverse-norm buffers (peer memory mapped
+ * over NVLink; the own buffers are among them).  The all-gather of the query block IS the kernel's stores; the caller
+ * synchronises the ranks before the search reads the buffers.  D % 4 == 0; fp32 targets 16-byte, bf16 targets 8-byte aligned. */
+CVPCE_API int cvpce_rows_prepare_scatter(const float* x, int64_t R, int D, int normalize, float eps,
+                               float* const* peer_f32, void* const* peer_bf16, float* const* peer_inv_norm, int n_peers,
+                               void* stream);
 /* tcgen05 path.  q_bf16 [Q,D], g_bf16 [G,D] bf16 row-major, 16-byte aligned, D % 64 == 0, 64 <= D <= 4096, 1 <= k <= 32.
  * The kernel computes S = Q x G^T tile by tile on the tensor cores (TMA-fed, fp32 accumulators in TMEM) and keeps a
  * per-row candidate list in registers; S never reaches HBM.  When q_f32/g_f32 are given (parity mode), the k' >= k + 8

@@ -5,6 +5,8 @@ same torch / torchvision CPU ops the reference executes, in the same order, so t
 rather than the cost of oracle.c's scalar loops.  /root/reference cannot travel to the GPU box; tests/test_reference_pin.py
 checks this port against the real reference where it is available.  Never imported by cvpce_b200/.
 """
+import time
+
 import torch
 import torchvision
 from torch import nn
@@ -72,27 +74,49 @@ def nearest_neighbors_chunked(anchors, queries, k=1, chunk=8):
     return torch.cat([nearest_neighbors(anchors, queries[i:i + chunk], k) for i in range(0, len(queries), chunk)])
 
 
+def _tick(stages, name, t0):
+    """Accumulates wall seconds of one stage into `stages` (per-stage CPU timings)."""
+    if stages is not None:
+        stages[name] = stages.get(name, 0.0) + (time.perf_counter() - t0)
+
+
 @torch.no_grad()
-def classify(encoder, gallery_embedding, images, k=1, batch_size=32, nn_chunk=None):
-    """cvpce/production.py:57-74 (returns indices instead of annotation strings)."""
-    res = []
+def classify(encoder, gallery_embedding, images, k=1, batch_size=32, nn_chunk=None, stages=None, return_embedding=False):
+    """cvpce/production.py:57-74 (returns indices instead of annotation strings).  `stages`: optional dict that receives the
+    seconds spent in the encoder and in nearest_neighbors."""
+    res, embs = [], []
     for i in range(0, len(images), batch_size):
+        t0 = time.perf_counter()
         batch = images[i:i + batch_size] * 2 - 1  # utils.scale_to_tanh
         emb = encoder(batch)
+        _tick(stages, "encoder", t0)
+        t0 = time.perf_counter()
         if nn_chunk:
             res.append(nearest_neighbors_chunked(gallery_embedding, emb, k, nn_chunk))
         else:
             res.append(nearest_neighbors(gallery_embedding, emb, k))
-    return torch.cat(res) if res else torch.empty((0, k), dtype=torch.int64)
+        _tick(stages, "nearest_neighbors", t0)
+        embs.append(emb)
+    idx = torch.cat(res) if res else torch.empty((0, k), dtype=torch.int64)
+    if return_embedding:
+        return idx, (torch.cat(embs) if embs else torch.empty((0, encoder.embedding_size)))
+    return idx
 
 
 @torch.no_grad()
 def hot_path(encoder, gallery_embedding, image, cand_boxes, cand_scores, k=1, detections_per_img=200, max_crops=None,
-             batch_size=32, nn_chunk=None):
+             batch_size=32, nn_chunk=None, stages=None, return_embedding=False):
     """One shelf image through the whole path on the CPU: NMS -> crops -> encoder -> nearest neighbours."""
+    t0 = time.perf_counter()
     keep = postprocess_nms(cand_boxes, cand_scores, 0.5, detections_per_img)
     boxes = cand_boxes[keep]
+    _tick(stages, "nms", t0)
     if max_crops is not None:
         boxes = boxes[:max_crops]
+    t0 = time.perf_counter()
     crops = crops_for_boxes(image, boxes)
-    return boxes, classify(encoder, gallery_embedding, crops, k, batch_size, nn_chunk)
+    _tick(stages, "crop_loop", t0)
+    res = classify(encoder, gallery_embedding, crops, k, batch_size, nn_chunk, stages, return_embedding)
+    if return_embedding:
+        return boxes, res[0], res[1]
+    return boxes, res

@@ -162,15 +162,20 @@ def test_crops_multi_image_layouts_affine(ops):
     np.testing.assert_allclose(out.float().cpu().numpy(), want_aff, rtol=1e-2, atol=1e-2)
 
 
-def test_crops_band_kernel_paths(ops, monkeypatch):
-    """The separable band kernel against the oracle and against the direct kernel: band heights 8..64 (few / many
-    crops), ring wrap-around (strong down-sampling), the >16-tap direct fallback inside the band kernel, all
-    output layouts."""
+def test_crops_band_kernel_paths(ops):
+    """The column-marching kernel (default) and the shared-memory band kernel against the oracle and against the direct
+    kernel: band heights 8..64 (few / many crops), up-sampling, 2-4 and 5-6 tap filters, the direct fallback inside the
+    antialias kernels for wider filters (the 900 x 700 box at S = 32 / 64), ring wrap-around, all output layouts."""
+    from cvpce_b200 import _lib
     img = synth.shelf_image(77, 700, 900)
     gimg = dev(img)
     table = ops.make_image_table([gimg])
     rs = np.random.RandomState(4)
-    few = np.array([[0, 0, 900, 700], [10, 20, 600, 500], [100, 100, 140, 130], [5, 5, 300, 690]], dtype=np.float32)
+    few = np.array([[0, 0, 900, 700], [10, 20, 600, 500], [100, 100, 140, 130], [5, 5, 300, 690],
+                    # crops narrower than the filter (1 and 3 pixels wide; up-sampling, 2-4 and 5-6 taps), a 3 x 3 crop, and
+                    # crops touching the right / bottom image border (the shifted tap window must stay inside the row)
+                    [100, 100, 101, 300], [10, 10, 13, 600], [50, 50, 53, 53], [700, 10, 900, 400], [880, 650, 900, 700],
+                    [899, 0, 900, 700], [0, 699, 900, 700]], dtype=np.float32)
     x1, y1 = rs.uniform(0, 700, 700), rs.uniform(0, 500, 700)
     many = np.stack([x1, y1, x1 + rs.uniform(3, 200, 700), y1 + rs.uniform(3, 200, 700)], 1).astype(np.float32)
     for boxes, S in ((few, 256), (few, 64), (few, 32), (many, 64), (few, 224)):
@@ -182,10 +187,25 @@ def test_crops_band_kernel_paths(ops, monkeypatch):
         b16 = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16)
         b16n = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16, channels_last=True)
         assert torch.equal(b16, out.to(torch.bfloat16)) and torch.equal(b16n.contiguous(), b16)
-        monkeypatch.setenv("CVPCE_CROP_DIRECT", "1")
-        direct = ops.crop_resize(table, 1, dev(boxes), None, S, True)
-        monkeypatch.delenv("CVPCE_CROP_DIRECT")
+        n4 = ops.crop_resize(table, 1, dev(boxes), None, S, True, channels_last=True, pad_channel=True)
+        assert torch.equal(n4[:, :3].contiguous(), out) and float(n4[:, 3].abs().max()) == 0.0
+        with _lib.tuning(crop_kernel=3):
+            direct = ops.crop_resize(table, 1, dev(boxes), None, S, True)
         np.testing.assert_allclose(direct.cpu().numpy(), out.cpu().numpy(), rtol=0, atol=2e-6)
+        with _lib.tuning(crop_kernel=1):
+            band = ops.crop_resize(table, 1, dev(boxes), None, S, True)
+            band16 = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16, channels_last=True)
+        np.testing.assert_allclose(band.cpu().numpy(), want, rtol=0, atol=1e-5)
+        np.testing.assert_allclose(band.cpu().numpy(), out.cpu().numpy(), rtol=0, atol=2e-6)
+        np.testing.assert_allclose(band16.float().cpu().numpy(), b16.float().cpu().numpy(), rtol=1e-2, atol=1e-2)
+        for rows in (8, 32, 256):
+            with _lib.tuning(crop_band_rows=rows):
+                assert torch.equal(ops.crop_resize(table, 1, dev(boxes), None, S, True), out)
+    # odd sizes (no vector width to respect in the column kernel) and a size above the band kernel's 256
+    for S in (33, 100, 320):
+        want, _ = oracle.crop_resize(img, few, S, True)
+        out = ops.crop_resize(table, 1, dev(few), None, S, True)
+        np.testing.assert_allclose(out.cpu().numpy(), want, rtol=0, atol=1e-5)
 
 
 def test_crops_strided_view_empty_and_zero(ops):
@@ -941,6 +961,10 @@ def test_patch_layer_on_a_reference_shaped_package(ops):
         # a4: same signature, CUDA image in
         img = dev(synth.shelf_image(8, 150, 90))
         assert float((pkg.datautils.resize_for_classification(img) - ref_resize(img)).abs().max()) <= 1e-5
+        # ... and the two shared helpers hand HOST tensors (dataset workers, other detectors) to the original functions
+        assert torch.equal(pkg.datautils.resize_for_classification(img.cpu()), ref_resize(img.cpu()))
+        assert torch.equal(retinanet.box_ops.batched_nms(torch.from_numpy(b), torch.from_numpy(s), labels.cpu(), 0.5),
+                           tv_batched_nms(torch.from_numpy(b), torch.from_numpy(s), labels.cpu(), 0.5))
         # f3: matching on the GPU, bookkeeping handed to the package's own _do_calculate; box_iou behind the tvops name
         cases = synth.match_cases()
         t = [torch.from_numpy(cases[n][0]) for n in ("kat0", "kat1", "kat2")]

@@ -80,8 +80,10 @@ def test_matching_oracle_equals_reference_on_fresh_inputs(ref):
 
 
 def test_patch_swaps_and_restores_every_call_site(ref):
-    """cvpce_b200.patch on the UNMODIFIED reference: every hot-path call site is swapped, the swapped functions refuse CPU
-    tensors loudly (no CPU fallback), and revert() puts back exactly the original objects."""
+    """cvpce_b200.patch on the UNMODIFIED reference: every hot-path call site is swapped, the swapped hot-path functions refuse
+    CPU tensors loudly (no CPU fallback), the two shared helpers that the reference also calls from host-side data preparation
+    (resize_for_classification in dataset workers, torchvision's batched_nms in other detectors) hand host tensors to the
+    ORIGINAL function, and revert() puts back exactly the original objects."""
     import cvpce.metrics as rmetrics
     import cvpce.planograms as rplan
     import cvpce.models.proposals as rprop
@@ -101,11 +103,17 @@ def test_patch_swaps_and_restores_every_call_site(ref):
         assert all(a is not b for a, b in zip(after, before)), [n for (o, n), a, b in zip(sites, after, before) if a is b]
         assert "postprocess_detections" in vars(rprop.GaussianLayerNetwork)
         b = torch.tensor([[0., 0., 10., 10.], [1., 1., 11., 11.]])
-        for call in (lambda: retinanet.box_ops.batched_nms(b, torch.tensor([.9, .8]), torch.zeros(2, dtype=torch.int64), 0.5),
-                     lambda: rd.resize_for_classification(torch.rand(3, 20, 30)),
-                     lambda: rc.nearest_neighbors(torch.rand(4, 8), torch.rand(2, 8), 1)):
-            with pytest.raises(RuntimeError):
-                call()
+        with pytest.raises(RuntimeError):
+            rc.nearest_neighbors(torch.rand(4, 8), torch.rand(2, 8), 1)
+        with pytest.raises(RuntimeError):
+            rc.MACVGG.forward(rc.macvgg_embedder('vgg16', pretrained=False).eval(), torch.rand(1, 3, 64, 64))
+        # host-side callers of the two shared helpers keep the reference's / torchvision's own arithmetic, bit for bit
+        sc, lab = torch.tensor([.9, .8]), torch.zeros(2, dtype=torch.int64)
+        assert torch.equal(retinanet.box_ops.batched_nms(b, sc, lab, 0.5), before[sites.index((retinanet.box_ops, "batched_nms"))](b, sc, lab, 0.5))
+        host_img = torch.rand(3, 20, 30, generator=torch.Generator().manual_seed(1))
+        assert torch.equal(rd.resize_for_classification(host_img), before[sites.index((rd, "resize_for_classification"))](host_img))
+        # ... so the gallery dataset's __getitem__ (datautils.py:511, run in DataLoader workers under Classifier.build_index)
+        # and PlanogramComparator.compare on a host image (production.py:111) work with the patch applied
         if not torch.cuda.is_available():   # the GPU-backed metrics / box_iou replacements say so instead of computing on the host
             with pytest.raises(RuntimeError):
                 rmetrics.iou_matrices(b, b)

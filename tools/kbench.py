@@ -155,11 +155,12 @@ def bench_crop(args):
     from cvpce_b200 import classification
     aff = classification.tanh_normalize_affine()
     for S in args.sizes:
-        for dt, cl in ((torch.float32, False), (torch.float32, True), (torch.bfloat16, True)):
+        for dt, cl, p4 in ((torch.float32, False, False), (torch.float32, True, False), (torch.float32, True, True), (torch.bfloat16, True, False)):
             esz = 4 if dt == torch.float32 else 2
-            nbytes = 12.0 * src + 3.0 * esz * S * S * K
-            ms, best = timeit(lambda: ops.crop_resize(table, args.shelves, boxes, idx, S, True, 0.5, aff, dt, cl), args.iters)
-            report("crop_resize S=%d %s %s K=%d" % (S, "f32" if esz == 4 else "bf16", "nhwc" if cl else "nchw", K), ms, best, nbytes)
+            nbytes = 12.0 * src + (4.0 if p4 else 3.0) * esz * S * S * K  # bytes the kernel really moves (NHWC4 writes 16 B / pixel)
+            ms, best = timeit(lambda: ops.crop_resize(table, args.shelves, boxes, idx, S, True, 0.5, aff, dt, cl, pad_channel=p4), args.iters)
+            report("crop_resize S=%d %s %s K=%d" % (S, "f32" if esz == 4 else "bf16", ("nhwc4" if p4 else "nhwc") if cl else "nchw", K), ms, best, nbytes,
+                   frac_hbm_survey_bytes=round((12.0 * src + 3.0 * esz * S * S * K) / ms / 1e6 / HBM, 4))
     ms, best = timeit(lambda: ops.crop_resize(table, args.shelves, boxes, idx, 256, False, 0.5, aff), args.iters)
     report("crop_resize S=256 f32 nchw plain-bilinear K=%d" % K, ms, best, 12.0 * src + 12.0 * 256 * 256 * K)
 
@@ -254,8 +255,15 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--sizes", type=int, nargs="*", default=[256, 224])
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--tune", nargs="*", default=[], help="name=value overrides passed to cvpce_tuning_set")
     args = ap.parse_args()
     torch.cuda.set_device(0)
+    from cvpce_b200 import _lib
+    for t in args.tune:
+        name, value = t.split("=")
+        _lib.tuning_set(name, int(value))
+    if args.tune:
+        print(json.dumps({"tuning": args.tune}), flush=True)
     for w in args.which:
         {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "match": bench_match, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
 
