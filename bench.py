@@ -416,14 +416,20 @@ def run_ours_shelves(args, world, rank, local):
         "own_kernels_share_of_step": round(ours_ms / ms_total, 4),
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_reference_rate(args, G, sample_crops=args.cpu_sample_crops, repeats=1)
+        # BASELINE.md section 3 protocol: 1 warm-up + best of 3 on all host threads with per-stage seconds, plus a 1-thread figure
+        line["cpu_baseline"] = cpu_reference_rate(args, G, sample_crops=args.cpu_sample_crops, repeats=3, warmup=1, one_thread_crops=8)
     return line
 
 
 # ------------------------------------------------------------------------------------------- reference / cpu baseline
-def cpu_reference_rate(args, G, sample_crops, repeats, warmup=0):
-    """Times the CPU port of the reference path (oracle/torch_port.py) on a bounded sample: one shelf's NMS, then the first
-    `sample_crops` surviving boxes through crop -> VGG16 -> MAC -> nearest_neighbors, on all host threads."""
+NN_NATIVE_BUDGET = 8e9  # bytes of the two gathered [Q,G,D] fp32 tensors the reference form of nearest_neighbors may allocate
+
+
+def cpu_reference_rate(args, G, sample_crops, repeats, warmup=0, one_thread_crops=0):
+    """Times the CPU port of the reference path (oracle/torch_port.py: the reference's torch / torchvision CPU ops in the
+    reference's order) on a bounded sample: one shelf's NMS of all candidates, then the first `sample_crops` surviving boxes
+    through crop loop -> VGG16 fp32 -> MAC -> nearest_neighbors, on all host threads; best of `repeats` after `warmup`, with the
+    seconds of each stage of the best run.  `one_thread_crops` > 0 adds a single-thread figure."""
     from oracle import torch_port
     from cvpce_b200 import synth
     threads = os.cpu_count() or 1
@@ -437,22 +443,45 @@ def cpu_reference_rate(args, G, sample_crops, repeats, warmup=0):
     image = torch.rand((3, H, W), generator=torch.Generator().manual_seed(100))
     b, s = synth.shelf_candidates(100, H, W, args.products)
     b, s = torch.from_numpy(b), torch.from_numpy(s)
-    nn_chunk = 4 if G > 1024 else None  # the reference form materialises Q*G*D*4 B twice; chunk queries to stay in memory
-    times = []
+    batch = 32  # Classifier's default batch_size (production.py:23)
+    # nearest_neighbors in the reference's own form gathers two [Q,G,D] fp32 tensors: run it natively on the reference's
+    # batch of 32 queries when that fits the budget, else in query chunks (a restatement of how it would have to be called)
+    nn_chunk = None if 2.0 * batch * G * 1024 * 4 <= NN_NATIVE_BUDGET else max(1, int(NN_NATIVE_BUDGET // (2.0 * G * 1024 * 4)))
+    times, stage_runs = [], []
     n = 0
     for it in range(warmup + repeats):
+        stages = {}
         t0 = time.perf_counter()
         boxes, idx = torch_port.hot_path(enc, gallery, image, b, s, k=args.k, detections_per_img=200, max_crops=sample_crops,
-                                         batch_size=32, nn_chunk=nn_chunk)
+                                         batch_size=batch, nn_chunk=nn_chunk, stages=stages)
         dt = time.perf_counter() - t0
         n = len(boxes)
         if it >= warmup:
             times.append(dt)
-    best = min(times)
-    return {"value": round(n / best, 3), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": "1 shelf: NMS of %d candidates, first %d kept boxes -> crop -> VGG16 fp32 -> MAC -> nearest_neighbors vs %d x 1024"
-                      " (torch CPU ops of the reference, best of %d)" % (len(s), n, G, repeats),
-            "seconds_per_step": [round(t, 3) for t in times]}
+            stage_runs.append(stages)
+    best = int(np.argmin(times))
+    out = {"value": round(n / times[best], 3), "unit": UNIT, "cores": threads, "kind": "port",
+           "sample": "1 shelf: NMS of %d candidates, first %d kept boxes -> crop loop -> VGG16 fp32 -> MAC -> nearest_neighbors vs %d x 1024 "
+                     "(%s); torch CPU ops of the reference, %d warm-up + best of %d"
+                     % (len(s), n, G, "reference-native form, batches of %d queries" % batch if nn_chunk is None
+                        else "reference form in chunks of %d queries (nn_chunk: the native batch of %d would gather %.1f GB)" % (nn_chunk, batch, 2.0 * batch * G * 4096 / 1e9),
+                        warmup, repeats),
+           "seconds_per_step": [round(t, 3) for t in times],
+           "stage_seconds": {k: round(v, 4) for k, v in stage_runs[best].items()},
+           "stage_note": "NMS covers all %d candidates of the shelf; the other stages cover the %d sampled crops" % (len(s), n)}
+    if one_thread_crops > 0:
+        torch.set_num_threads(1)
+        try:
+            st1 = {}
+            t0 = time.perf_counter()
+            boxes1, _ = torch_port.hot_path(enc, gallery, image, b, s, k=args.k, detections_per_img=200, max_crops=one_thread_crops,
+                                            batch_size=batch, nn_chunk=nn_chunk, stages=st1)
+            dt1 = time.perf_counter() - t0
+            out["one_thread"] = {"value": round(len(boxes1) / dt1, 3), "unit": UNIT, "cores": 1, "crops": len(boxes1),
+                                 "seconds": round(dt1, 3), "stage_seconds": {k: round(v, 4) for k, v in st1.items()}, "runs": 1}
+        finally:
+            torch.set_num_threads(threads)
+    return out
 
 
 def run_reference(args, world, rank):
@@ -467,9 +496,80 @@ def run_reference(args, world, rank):
     return {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(1e3 * sum(secs) / len(secs), 2), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s (bounded sample per step: %s)" % (args.workload, base["sample"])},
+            "config": {"workload": "%s (bounded sample per step: %s)" % (args.workload, base["sample"]),
+                       "processes": "ONE CPU process on rank 0 with all host threads, whatever --gpus says (the other ranks exit 0): "
+                                    "the reference's CPU path is not data-parallel over GPUs",
+                       "value_is": "crops of the sample / seconds, mean over the timed steps; per-crop extrapolation to the repo arm's "
+                                   "%s crops per step is linear (encoder-bound)" % ("~6400" if args.workload == "c3" else "larger")},
             "cpu_baseline": base,
             "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# ------------------------------------------------------------------------------------------------------- workload c1
+def run_c1(args, device, with_cpu):
+    """BASELINE.json configs[0]: DIHE random-init VGG16 embed + MAC + cosine top-1 for 64 synthetic crops vs a 180-item gallery,
+    through the Classifier mirror (production.py:57-74): S = 224 (as BASELINE states) and S = 256 (the reference's native
+    CLASSIFICATION_IMAGE_SIZE).  `value`: crops already on the device; `e2e`: crops in pinned host memory, indices back on the host
+    (classify() returns python lists of annotation strings, like the reference).  With `with_cpu` the reference's CPU path
+    (oracle/torch_port.py) is timed on exactly this configuration (1 warm-up + best of 2) and top-1 agreement is reported."""
+    from cvpce_b200 import production
+    from oracle import torch_port
+    a1 = argparse.Namespace(**vars(args))
+    a1.trunk = "f32"
+    enc = build_encoder(a1, device)
+    res = {}
+    gen = torch.Generator().manual_seed(1000)
+    gal_imgs = torch.rand((180, 3, 256, 256), generator=gen) * 2 - 1  # gallery images arrive in [-1,1] (datautils.py:412-414)
+    samples = [(gal_imgs[i], gal_imgs[i], [], "sku%03d" % i) for i in range(180)]
+    clf = production.Classifier(enc, samples, device=device, emb_device=device, batch_size=32, num_workers=0, k=1)
+    cpu_enc = cpu_gal = None
+    if with_cpu:
+        torch.manual_seed(__import__("cvpce_b200.synth", fromlist=["x"]).WEIGHT_SEED)
+        cpu_enc = torch_port.MACVGGPort().eval().requires_grad_(False)
+        with torch.no_grad():
+            cpu_gal = torch.cat([cpu_enc(gal_imgs[i:i + 32]) for i in range(0, 180, 32)])
+    for S in (224, 256):
+        crops_h = torch.rand((64, 3, S, S), generator=torch.Generator().manual_seed(7)).pin_memory()
+        crops_d = crops_h.to(device)
+        steps, warm = 20, 5
+        for _ in range(warm):
+            lab = clf.classify(crops_d)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            lab = clf.classify(crops_d)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        for _ in range(2):
+            clf.classify(crops_h)
+        e0.record()
+        for _ in range(steps):
+            lab_h = clf.classify(crops_h)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_e2e = e0.elapsed_time(e1) / steps
+        ent = {"workload": "c1: 64 synthetic %dx%d crops -> VGG16(random init)+MAC -> cosine top-1 vs 180 x 1024 gallery (Classifier.classify)" % (S, S),
+               "value": round(64 / ms * 1e3, 1), "unit": UNIT, "ms_per_step": round(ms, 3), "steps": steps,
+               "e2e": round(64 / ms_e2e * 1e3, 1), "e2e_ms_per_step": round(ms_e2e, 3), "h2d_bytes_per_step": int(crops_h.numel() * 4),
+               "d2h_bytes_per_step": 64 * 8, "same_labels_resident_and_e2e": lab == lab_h}
+        if with_cpu:
+            ts = []
+            for it in range(3):
+                st = {}
+                t0 = time.perf_counter()
+                idx = torch_port.classify(cpu_enc, cpu_gal, crops_h, k=1, batch_size=32, stages=st)
+                ts.append((time.perf_counter() - t0, st))
+            best = min(ts[1:], key=lambda t: t[0])
+            ent["cpu_baseline"] = {"value": round(64 / best[0], 3), "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                                   "sample": "the whole configuration (64 crops, reference-native nearest_neighbors), 1 warm-up + best of 2",
+                                   "seconds": round(best[0], 3), "stage_seconds": {k: round(v, 4) for k, v in best[1].items()}}
+            ent["top1_agreement_with_cpu_fp32"] = round(float(np.mean([lab[i][0] == "sku%03d" % int(idx[i, 0]) for i in range(64)])), 4)
+        res["S%d" % S] = ent
+    del clf, enc
+    torch.cuda.empty_cache()
+    return res
 
 
 # ----------------------------------------------------------------------------------------------------- workload c5
@@ -606,6 +706,17 @@ def run_ours_c5(args, world, rank, local):
     return line
 
 
+def _brief(l):
+    """The fields of a full bench line that other_configs keeps."""
+    out = {"workload": l["config"]["workload"], "value": l["value"], "unit": l["unit"], "ms_per_step": l["ms_per_step"],
+           "steps": l["steps"], "warmup": l["warmup"], "dtype": l["dtype"], "e2e": l["e2e"]["value"],
+           "e2e_ms_per_step": l["e2e"]["ms_per_step"], "h2d_bytes_per_step": l["e2e"]["h2d_bytes_per_step"],
+           "d2h_bytes_per_step": l["e2e"]["d2h_bytes_per_step"]}
+    if "ms_per_step_per_rank" in l:
+        out["ms_per_step_per_rank"] = l["ms_per_step_per_rank"]
+    return out
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -622,28 +733,53 @@ def main():
     if args.strict_fp32:
         torch.backends.cudnn.allow_tf32 = False
         torch.backends.cuda.matmul.allow_tf32 = False
+    import copy
     if args.workload == "c5":
         line = run_ours_c5(args, world, rank, local)
     else:
         line = run_ours_shelves(args, world, rank, local)
-        if world == 1 and args.trunk == "f32" and not args.strict_fp32 and not args.no_extension_modes and not args.plain_trunk:
+        headline_default = args.trunk == "f32" and not args.strict_fp32 and not args.plain_trunk
+        if headline_default and args.workload == "c3" and not args.no_other_configs:
+            other = {}
+            # (1) BASELINE.json configs[4] on the driver's clock at EVERY N: the 1M x 512 gallery sharded over the ranks
+            torch.cuda.empty_cache()
+            a5 = copy.copy(args)
+            a5.workload, a5.gallery, a5.steps, a5.warmup = "c5", None, max(3, min(args.steps, 5)), 3
+            l5 = run_ours_c5(a5, world, rank, local)
+            other["c5"] = {"workload": l5["config"]["workload"], "exchange": l5["config"]["exchange"], "value": l5["value"], "unit": l5["unit"],
+                           "ms_per_step": l5["ms_per_step"], "ms_per_step_per_rank": l5["ms_per_step_per_rank"], "steps": l5["steps"],
+                           "warmup": l5["warmup"], "scaling": "strong", "dtype": l5["dtype"],
+                           "tflops_per_gpu": l5["roofline"]["achieved"], "frac_of_bf16_tflops_sustained": l5["roofline"]["frac"],
+                           "e2e": l5["e2e"], "c5_parity": l5["c5_parity"], "c5_parity_detail": l5["c5_parity_detail"],
+                           "gpu_launches": l5["gpu_launches"], "clocks": l5["clocks"]}
+            if world == 1:
+                # (2) the parity mode of the headline ("parity mode keeps fp32"): the same configuration with fp32
+                # convolutions; ~10x slower (cuDNN fp32 convolutions run on the CUDA cores), so one warm-up and two steps
+                torch.cuda.empty_cache()
+                a32 = copy.copy(args)
+                a32.no_cpu_baseline, a32.steps, a32.warmup = True, 2, 1
+                tf32_state = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+                torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+                try:
+                    other["strict_fp32"] = _brief(run_ours_shelves(a32, world, rank, local))
+                finally:
+                    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32_state
+                # (3) BASELINE.json configs[1] (one shelf, ~200 boxes, 180 references): the same step at batch 1, the latency case
+                torch.cuda.empty_cache()
+                a2 = copy.copy(args)
+                a2.workload, a2.shelves, a2.gallery, a2.no_cpu_baseline, a2.steps, a2.warmup = "c2", None, None, True, 20, 5
+                other["c2"] = _brief(run_ours_shelves(a2, world, rank, local))
+                # (4) BASELINE.json configs[0]: 64 given crops vs 180 references through Classifier.classify, CPU reference beside it
+                torch.cuda.empty_cache()
+                other["c1"] = run_c1(args, torch.device("cuda", local), with_cpu=not args.no_cpu_baseline)
+            line["other_configs"] = other
+        if world == 1 and headline_default and not args.no_extension_modes:
             # reported next to the headline, never instead of it: the same step with the half-precision trunk hand-off
             # (same 10-bit mantissa as the TF32 convolutions of the headline, same measured deviation)
-            import copy
             a16 = copy.copy(args)
             a16.trunk, a16.no_cpu_baseline, a16.steps = "f16", True, max(1, min(args.steps, 2))
             torch.cuda.empty_cache()
             l16 = run_ours_shelves(a16, world, rank, local)
-            if args.workload == "c3":
-                # BASELINE.json configs[1] (one shelf, ~200 boxes, 180 references) next to the headline: the same step at
-                # batch 1, i.e. the latency case (the headline is configs[2], the largest single-GPU configuration)
-                a2 = copy.copy(args)
-                a2.workload, a2.shelves, a2.gallery, a2.no_cpu_baseline, a2.steps, a2.warmup = "c2", None, None, True, 20, 5
-                torch.cuda.empty_cache()
-                l2 = run_ours_shelves(a2, world, rank, local)
-                line["other_configs"] = {"c2": {"workload": l2["config"]["workload"], "value": l2["value"], "unit": l2["unit"],
-                                                "ms_per_step": l2["ms_per_step"], "e2e": l2["e2e"]["value"],
-                                                "e2e_ms_per_step": l2["e2e"]["ms_per_step"], "steps": a2.steps}}
             line["extension_modes"] = {"trunk_f16": {"value": l16["value"], "unit": l16["unit"], "ms_per_step": l16["ms_per_step"],
                                                      "e2e": l16["e2e"]["value"], "steps": a16.steps,
                                                      "note": "half weights/activations, fp32 accumulation; not the headline"}}

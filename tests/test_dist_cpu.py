@@ -40,6 +40,76 @@ def _merge_numpy(s_all, i_all):
     return torch.from_numpy(out_s), torch.from_numpy(out_i)
 
 
+class _OracleBackend:
+    """Stands in for cvpce_b200.ops inside ShardedGallery (tests only): the oracle's exact top-k on the host."""
+
+    @staticmethod
+    def rows_prepare(x, normalize=True):
+        n = x.norm(dim=1).clamp_min(1e-8)
+        return (x / n[:, None]).to(torch.bfloat16), 1.0 / n
+
+    @staticmethod
+    def sim_topk_workspace_bytes(Q, G, D, k):
+        return 16
+
+    @staticmethod
+    def _topk(q32, g32, k, base):
+        import oracle
+        kk = min(k, len(g32))
+        sim, idx = oracle.sim_topk(q32.numpy(), g32.numpy(), kk)
+        s = np.full((len(q32), k), -np.inf, np.float32)
+        i = np.full((len(q32), k), -1, np.int64)
+        s[:, :kk], i[:, :kk] = sim, idx + base
+        return torch.from_numpy(s), torch.from_numpy(i)
+
+    def sim_topk(self, qb, gb, k, base, q32, g32, qinv, ginv, workspace=None):
+        return self._topk(q32, g32, k, base)
+
+    def sim_topk_f32(self, q, g, k, base, normalize=True):
+        return self._topk(q, g, k, base)
+
+    @staticmethod
+    def topk_merge(s_all, i_all):
+        return _merge_numpy(s_all, i_all)
+
+
+def _worker_sharded(rank, world, port, tmp):
+    """The real ShardedGallery host logic (k clamp, unsupported-D fallback, padded all-gather of partitioned queries, ranks
+    without rows) on gloo, with the oracle standing in for the kernels."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import oracle
+    cpu = torch.device("cpu")
+    ok = True
+    for G, D, Q, k in ((1000, 64, 41, 5), (1000, 48, 40, 5), (3, 64, 7, 5), (1, 64, 5, 2)):   # D=48: fp32 fallback; G < k; G < world
+        full = cdist.synthetic_rows(0, G, D, cpu, 5)
+        q = cdist.synthetic_queries(Q, D, cpu, 6, full)
+        lo, hi = cdist.shard_range(G, world, rank)
+        sg = cdist.ShardedGallery(full[lo:hi], lo, world, rank, backend=_OracleBackend())
+        ok = ok and sg.global_rows == G
+        wsim, widx = oracle.sim_topk(q.numpy(), full.numpy(), min(k, G))
+        s, i = sg.search(q, k)
+        ok = ok and tuple(i.shape) == (Q, min(k, G)) and np.array_equal(i.numpy(), widx) and np.allclose(s.numpy(), wsim, atol=1e-6)
+        qlo, qhi = cdist.shard_range(Q, world, rank)
+        s2, i2 = sg.search_partitioned(q[qlo:qhi], qlo, Q, k)
+        ok = ok and torch.equal(i2, i) and torch.equal(s2, s)
+    parts = cdist.partition_query_chunks(10, world, rank, 3)
+    got = [None] * world
+    dist.all_gather_object(got, [(g0, n) for g0, n, _, _ in parts])
+    rows = sorted(r for per in got for g0, n in per for r in range(g0, g0 + n))
+    ok = ok and rows == list(range(10))
+    with open(os.path.join(tmp, "sharded%d" % rank), "w") as f:
+        f.write("1" if ok else "0")
+    dist.destroy_process_group()
+
+
+def test_sharded_gallery_host_logic_world2_gloo(tmp_path):
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_worker_sharded, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert [open(tmp_path / ("sharded%d" % r)).read() for r in range(2)] == ["1", "1"]
+
+
 def _worker(rank, world, port, tmp):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
