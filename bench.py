@@ -57,7 +57,7 @@ def parse():
                     "is torch's own GPU default, TF32 convolutions: tools/tf32_check.py measures what that costs in accuracy)")
     ap.add_argument("--sim", default="tc", choices=["tc", "f32"], help="similarity kernel: tcgen05 or CUDA-core fp32")
     ap.add_argument("--queries", type=int, default=100000, help="c5 only")
-    ap.add_argument("--c5-chunks", type=int, default=2, help="c5 e2e leg: query chunks (upload of chunk c+1 overlaps the search of chunk c)")
+    ap.add_argument("--c5-chunks", type=int, default=4, help="c5 e2e leg: query chunks (upload of chunk c+1 overlaps the search of chunk c)")
     ap.add_argument("--no-other-configs", action="store_true", help="headline only: skip the c2 / c1 / strict-fp32 / c5 legs reported under other_configs")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="c5, N > 1: how the per-rank top-k blocks reach the other "
                     "ranks: stored by the selection kernel into every peer's gather buffer over NVLink, or an NCCL all-gather")

@@ -171,7 +171,8 @@ def similarity_topk(anchors, queries, k=1, exact=True, prepared=None):
     if Q == 0 or k_eff == 0:
         return (torch.empty((Q, k_eff), dtype=torch.float32, device=queries.device),
                 torch.empty((Q, k_eff), dtype=torch.int64, device=queries.device))
-    use_tc = (D % 64 == 0 and 64 <= D <= 4096 and k_eff <= 32 and Q * G >= _TENSOR_CORE_MIN_WORK)
+    # the tcgen05 kernel keeps k + 8 <= 32 candidates per row for the exact re-score: k <= 24 (32 without the re-score)
+    use_tc = (D % 64 == 0 and 64 <= D <= 4096 and k_eff <= (24 if exact else 32) and Q * G >= _TENSOR_CORE_MIN_WORK)
     if not use_tc:
         g = anchors if prepared is None else prepared.f32
         return ops.sim_topk_f32(queries, g, k_eff, normalize=True)

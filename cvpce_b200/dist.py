@@ -194,20 +194,21 @@ class ShardedGallery:
     def load_index_rows(pth, world, rank):
         """This rank's row range of an index file in the reference's format ({'embedding', 'annotations'}, written by
         Classifier.save_index, cvpce/production.py:52-56): the file is memory-mapped, so a rank pages in only its own rows.
-        Returns (rows f32 [hi-lo, D] on the host, first global row index, annotations list (whole: it maps global indices))."""
+        Returns (rows f32 [hi-lo, D] on the host, first global row index, annotations list (whole: it maps global indices),
+        rows of the whole gallery)."""
         try:
             idx = torch.load(pth, map_location="cpu", mmap=True, weights_only=False)
         except (RuntimeError, ValueError, TypeError):  # legacy (non-zip) serialisation cannot be mapped
             idx = torch.load(pth, map_location="cpu", weights_only=False)
         emb = idx["embedding"]
         lo, hi = shard_range(int(emb.shape[0]), world, rank)
-        return emb[lo:hi].contiguous().float(), lo, idx["annotations"]
+        return emb[lo:hi].contiguous().float(), lo, idx["annotations"], int(emb.shape[0])
 
     @classmethod
     def from_index(cls, pth, world, rank, device, group=None, exchange="nccl"):
         """(ShardedGallery over this rank's rows of the index file, annotations)."""
-        rows, lo, annotations = cls.load_index_rows(pth, world, rank)
-        return cls(rows.to(device), lo, world, rank, group, exchange=exchange), annotations
+        rows, lo, annotations, total = cls.load_index_rows(pth, world, rank)
+        return cls(rows.to(device), lo, world, rank, group, exchange=exchange, global_rows=total), annotations
 
     # ------------------------------------------------------------------------------------------------------------ helpers
     def _k_eff(self, k):

@@ -49,7 +49,7 @@ CVPCE_API int cvpce_device_check(void);
 /* Frees lazily created module state (TMA descriptor cache). Safe to call more than once. */
 CVPCE_API int cvpce_shutdown(void);
 /* Development overrides of launch heuristics (A/B measurements, cross-checks of alternative kernels): process-wide named
- * integers, 0 = automatic.  Knobs: "crop_kernel", "crop_band_rows", "sim_plan", "sim_split", "sim_ctas", "mac_cluster", "pool_persistent"
+ * integers, 0 = automatic.  Knobs: "crop_kernel", "crop_band_rows", "sim_plan", "sim_split", "sim_ctas", "sim_epi_groups", "sim_debug", "mac_cluster", "pool_persistent"
  * (csrc/common.cu lists their values).  Results never depend on them beyond fp32 summation order; the library reads no
  * environment variables.  Unknown names return CVPCE_ERR_INVALID_ARG. */
 CVPCE_API int cvpce_tuning_set(const char* name, int value);
@@ -250,7 +250,8 @@ CVPCE_API int cvpce_rows_prepare(const float* x, int64_t R, int D, int normalize
 CVPCE_API int cvpce_rows_prepare_scatter(const float* x, int64_t R, int D, int normalize, float eps,
                                float* const* peer_f32, void* const* peer_bf16, float* const* peer_inv_norm, int n_peers,
                                void* stream);
-/* tcgen05 path.  q_bf16 [Q,D], g_bf16 [G,D] bf16 row-major, 16-byte aligned, D % 64 == 0, 64 <= D <= 4096, 1 <= k <= 32.
+/* tcgen05 path.  q_bf16 [Q,D], g_bf16 [G,D] bf16 row-major, 16-byte aligned, D % 64 == 0, 64 <= D <= 4096, 1 <= k <= 32
+ * (k <= 24 with the exact re-score: k + 8 <= 32 candidates per row are kept; larger k returns CVPCE_ERR_UNSUPPORTED).
  * The kernel computes S = Q x G^T tile by tile on the tensor cores (TMA-fed, fp32 accumulators in TMEM) and keeps a
  * per-row candidate list in registers; S never reaches HBM.  When q_f32/g_f32 are given (parity mode), the k' >= k + 8
  * candidates of each row are re-scored in exact fp32 (score = dot(q,g) * q_inv_norm * g_inv_norm; inv norms nullable = 1)

@@ -150,8 +150,8 @@ def test_index_file_rows_per_rank(tmp_path):
     for world in (1, 2, 3, 8):
         parts, nxt = [], 0
         for rank in range(world):
-            rows, lo, a = cdist.ShardedGallery.load_index_rows(pth, world, rank)
-            assert lo == nxt and a == ann and rows.dtype == torch.float32 and rows.is_contiguous()
+            rows, lo, a, total = cdist.ShardedGallery.load_index_rows(pth, world, rank)
+            assert lo == nxt and a == ann and total == 101 and rows.dtype == torch.float32 and rows.is_contiguous()
             nxt += rows.shape[0]
             parts.append(rows)
         assert torch.equal(torch.cat(parts), emb)

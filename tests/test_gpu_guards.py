@@ -141,8 +141,12 @@ def test_search_kernels_stay_inside_their_outputs(guarded):
         gb, gi = ops.rows_prepare(gal)
         g.check("rows_prepare %d/%d x %d" % (Q, G, D))
         kk = min(k, 32)
-        ops.sim_topk(qb, gb, kk, 7, q, gal, qi, gi)
-        g.check("sim_topk exact Q=%d G=%d D=%d k=%d" % (Q, G, D, kk))
+        ke = min(k, 24)                                       # the exact re-score keeps k + 8 <= 32 candidates per row
+        ops.sim_topk(qb, gb, ke, 7, q, gal, qi, gi)
+        g.check("sim_topk exact Q=%d G=%d D=%d k=%d" % (Q, G, D, ke))
+        if kk > 24:
+            with pytest.raises(RuntimeError, match="k \\+ 8"):
+                ops.sim_topk(qb, gb, kk, 7, q, gal, qi, gi)
         ops.sim_topk(qb, gb, kk, 0)
         g.check("sim_topk bf16 Q=%d G=%d D=%d k=%d" % (Q, G, D, kk))
         ops.sim_topk_f32(q, gal, min(k, G), 3)
