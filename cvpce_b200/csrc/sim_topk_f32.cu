@@ -66,13 +66,13 @@ __global__ void __launch_bounds__(256) rows_prepare_scatter_kernel(const float* 
     const float4* r = reinterpret_cast<const float4*>(x + row * D);
     float inv = 1.f;
     if (normalize) {
+      // the same summation order as rows_prepare_kernel (lane i takes elements i, i + 32, ...): the inverse norm of a row,
+      // and with it every re-scored similarity, is bit-identical whether the queries were prepared locally or scattered
+      const float* rs = x + row * D;
       float s = 0.f;
-      for (int i = lane; i < (D >> 2); i += 32) {
-        const float4 v = __ldg(r + i);
-        s = fmaf(v.x, v.x, s);
-        s = fmaf(v.y, v.y, s);
-        s = fmaf(v.z, v.z, s);
-        s = fmaf(v.w, v.w, s);
+      for (int i = lane; i < D; i += 32) {
+        const float v = __ldg(rs + i);
+        s = fmaf(v, v, s);
       }
       s = warp_sum(s);
       inv = 1.f / fmaxf(sqrtf(s), eps);
