@@ -369,3 +369,89 @@ def planogram_case(seed, n=60, n_labels=12, missing=9, extra=7):
     b2 = np.array(b2, dtype=np.float32)
     solution = [pairs[t] for t in rs.permutation(len(pairs))[:14] if l2[pairs[t][1]] == l1[pairs[t][0]]]
     return b1, l1, b2, l2, solution
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a14: a small synthetic evaluation set for the two entry points that drive the path
+# (cvpce/classification_eval.py:6-56 eval_dihe, cvpce/detection_eval.py:6-49 evaluate_detections)
+# ---------------------------------------------------------------------------------------------------------------------
+EVAL_CROP_SIZE = 64          # CLASSIFICATION_IMAGE_SIZE used for the evaluation goldens (keeps the CPU reference run short)
+EVAL_IMAGE_HW = (240, 320)
+EVAL_THRESHOLDS = (0.5, 0.75)
+
+
+def _resize_bilinear(img, h, w):
+    """[3,H,W] -> [3,h,w], plain bilinear (numpy; only used to paint gallery items into the synthetic shelves)."""
+    C, H, W = img.shape
+    ys = np.clip((np.arange(h) + 0.5) * H / h - 0.5, 0, H - 1)
+    xs = np.clip((np.arange(w) + 0.5) * W / w - 0.5, 0, W - 1)
+    y0, x0 = np.floor(ys).astype(int), np.floor(xs).astype(int)
+    y1, x1 = np.minimum(y0 + 1, H - 1), np.minimum(x0 + 1, W - 1)
+    fy, fx = (ys - y0)[None, :, None], (xs - x0)[None, None, :]
+    a = img[:, y0][:, :, x0] * (1 - fx) + img[:, y0][:, :, x1] * fx
+    b = img[:, y1][:, :, x0] * (1 - fx) + img[:, y1][:, :, x1] * fx
+    return (a * (1 - fy) + b * fy).astype(np.float32)
+
+
+def eval_case(seed=61, n_images=4, n_products=9, n_gallery=12):
+    """Gallery images [G,3,64,64] in [-1,1] (annotations "g<i>") and `n_images` synthetic shelves [3,H,W] in [0,1] on which
+    `n_products` gallery items are painted (resized to their box, plus noise), with their boxes and labels.  About a fifth of
+    the products are painted from a DIFFERENT item than their label says, and the box list of each shelf has one box that
+    sticks out of the image (clip_boxes_to_image, classification_eval.py:23), so accuracy is neither 0 nor 1.
+    Returns (gallery, annotations, shelves) with shelves = list of (image, boxes f32 [n,4], labels i64 [n])."""
+    rs = np.random.RandomState(seed)
+    H, W = EVAL_IMAGE_HW
+    gallery = (rs.rand(n_gallery, 3, 64, 64) * 2 - 1).astype(np.float32)
+    # smooth the items a little so that resizing keeps them recognisable to a random-init encoder
+    for g in gallery:
+        g[:] = (g + np.roll(g, 1, 1) + np.roll(g, 1, 2) + np.roll(np.roll(g, 1, 1), 1, 2)) / 4
+    gallery = np.clip(gallery * 1.8, -1, 1).astype(np.float32)
+    annotations = ["g%d" % i for i in range(n_gallery)]
+    shelves = []
+    for _ in range(n_images):
+        img = (0.45 + 0.1 * rs.rand(3, H, W)).astype(np.float32)
+        boxes, labels = [], []
+        cols = 3
+        for p in range(n_products):
+            cw, ch = W // cols, H // ((n_products + cols - 1) // cols)
+            bw, bh = int(rs.randint(40, cw - 8)), int(rs.randint(36, ch - 6))
+            x1 = (p % cols) * cw + int(rs.randint(0, cw - bw))
+            y1 = (p // cols) * ch + int(rs.randint(0, ch - bh))
+            label = len(shelves) * n_products + p           # the first n_gallery products cover every class once
+            label = label if label < n_gallery else int(rs.randint(0, n_gallery))
+            painted = label if rs.rand() > 0.2 else int(rs.randint(0, n_gallery))
+            patch = _resize_bilinear((gallery[painted] + 1) / 2, bh, bw) + 0.02 * rs.randn(3, bh, bw).astype(np.float32)
+            img[:, y1:y1 + bh, x1:x1 + bw] = np.clip(patch, 0, 1)
+            boxes.append([x1, y1, x1 + bw, y1 + bh])
+            labels.append(label)
+        boxes = np.asarray(boxes, dtype=np.float32)
+        boxes[-1, 2:] += np.array([W, H], dtype=np.float32) * 0.1   # sticks out of the image on purpose
+        shelves.append((img, boxes, np.asarray(labels, dtype=np.int64)))
+    return gallery, annotations, shelves
+
+
+def eval_detector_heads(shelves, seed=71):
+    """Synthetic detector-head outputs for the evaluate_detections golden: every ground-truth box of a shelf gets one well
+    scored candidate (jittered by ~2 px) and two low-scored duplicates, two thirds of the shelves' boxes only (missed products
+    lower the recall), plus a few false positives.  One (logits, regression, anchors) triple per shelf, frame = image size."""
+    rs = np.random.RandomState(seed)
+    H, W = EVAL_IMAGE_HW
+    heads = []
+    for si, (_, boxes, _) in enumerate(shelves):
+        gt = np.clip(boxes, 0, [W, H, W, H])
+        keep = rs.rand(len(gt)) > 0.3
+        cand, score = [], []
+        for b in gt[keep]:
+            cand.append(b + rs.randn(4) * 2.0)
+            score.append(rs.uniform(0.6, 0.98))
+            for _ in range(2):
+                cand.append(b + rs.randn(4) * 5.0)
+                score.append(rs.uniform(0.08, 0.5))
+        for _ in range(3):
+            x, y = rs.uniform(0, W - 60), rs.uniform(0, H - 60)
+            cand.append(np.array([x, y, x + rs.uniform(30, 60), y + rs.uniform(30, 60)]))
+            score.append(rs.uniform(0.3, 0.7))
+        cand = np.clip(np.asarray(cand, dtype=np.float32), 0, [W, H, W, H]).astype(np.float32)
+        lg, rg, anc, _ = head_from_candidates(cand, np.asarray(score, dtype=np.float32), (H, W), seed * 100 + si, frame=(H, W))
+        heads.append((lg, rg, anc))
+    return heads

@@ -209,6 +209,70 @@ def golden_match(ref):
     print("match:", {k: int(v.sum()) for k, v in out.items() if "/tp_" in k or "/matched_" in k})
 
 
+def run_reference_evals(ref):
+    """The reference's two evaluation entry points on the synthetic evaluation set, CPU:
+    cvpce/classification_eval.py:6-56 eval_dihe and cvpce/detection_eval.py:6-49 evaluate_detections run UNMODIFIED; only what
+    pins them to a GPU is overridden -- Classifier's device defaults (production.py:23) and SKU110KBatch.cuda
+    (datautils.py:124-127) -- plus CLASSIFICATION_IMAGE_SIZE = 64 to keep the CPU run short.  The network body of the detector
+    is a stand-in (a random-init GLN detects nothing) that feeds seeded head outputs to the reference's own
+    GaussianLayerNetwork.postprocess_detections.  Returns the dict stored as tests/golden/eval.npz."""
+    import functools
+    import types
+    import cvpce.classification_eval as ce
+    import cvpce.detection_eval as de
+    import cvpce.models.proposals as proposals
+    from . import eval_harness as eh
+    cpu = torch.device("cpu")
+    out = {}
+    gallery, annotations, shelves = synth.eval_case()
+    torch.manual_seed(synth.WEIGHT_SEED)
+    enc = ref.models.classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False)
+    predicted = []
+
+    class SpyClassifier(ref.production.Classifier):
+        def classify(self, images, return_embedding=False):
+            res = super().classify(images, return_embedding)
+            predicted.append(res[0] if return_embedding else res)
+            return res
+
+    saved = (ce.production, de.production, ref.datautils.CLASSIFICATION_IMAGE_SIZE, ref.datautils.SKU110KBatch.cuda)
+    stand_in = types.SimpleNamespace(Classifier=functools.partial(SpyClassifier, device=cpu, emb_device=cpu))
+    try:
+        ce.production = de.production = stand_in
+        ref.datautils.CLASSIFICATION_IMAGE_SIZE = synth.EVAL_CROP_SIZE
+        ref.datautils.SKU110KBatch.cuda = lambda self, device=None, non_blocking=True: self
+        # ---- eval_dihe
+        k = (1, 3)
+        acc = ce.eval_dihe(enc, synth.GalleryDataset(gallery), eh.DiheTestSet(annotations, shelves), batch_size=4, num_workers=0,
+                           k=k, verbose=False)
+        out["dihe/accuracy"] = np.array([acc[x] for x in k], dtype=np.float64)
+        out["dihe/predicted"] = np.array([[annotations.index(a) for a in row] for per_img in predicted for row in per_img], dtype=np.int64)
+        # ---- evaluate_detections
+        predicted.clear()
+        gln = proposals.gln(num_classes=1, pretrained_backbone=False).eval()
+        gln.detections_per_img = 200
+        heads = synth.eval_detector_heads(shelves)
+        det = eh.StubDetector(heads, gln.postprocess_detections)
+        per_class, overall = de.evaluate_detections(det, enc, eh.DetectionTestSet(annotations, shelves), synth.GalleryDataset(gallery),
+                                                    thresholds=synth.EVAL_THRESHOLDS, proposal_batch_size=2,
+                                                    classification_batch_size=4, num_workers=0)
+        for name, arr in eh.flatten_metrics(per_class, overall, synth.EVAL_THRESHOLDS).items():
+            out["det/" + name] = arr
+        out["det/predicted_top1"] = np.array([annotations.index(row[0]) for per_img in predicted for row in per_img], dtype=np.int64)
+        mam = de.mean_average_metrics(per_class, synth.EVAL_THRESHOLDS)
+        out["det/map_mar300"] = np.array([[float(mam[t]["map"]), float(mam[t]["mar300"])] for t in synth.EVAL_THRESHOLDS])
+    finally:
+        ce.production, de.production, ref.datautils.CLASSIFICATION_IMAGE_SIZE, ref.datautils.SKU110KBatch.cuda = saved
+    return out
+
+
+def golden_eval(ref):
+    out = run_reference_evals(ref)
+    np.savez_compressed(os.path.join(OUT, "eval.npz"), **out)
+    print("eval: dihe accuracy", out["dihe/accuracy"].tolist(), "detections classified", len(out["det/predicted_top1"]),
+          "mAP / mAR300 per threshold", out["det/map_mar300"].tolist())
+
+
 def main():
     if not shim.available():
         sys.exit("reference tree not present; golden vectors can only be regenerated in the authoring container")
@@ -223,6 +287,7 @@ def main():
     golden_classify(ref)
     golden_head(ref)
     golden_match(ref)
+    golden_eval(ref)
     with open(os.path.join(OUT, "VERSIONS.txt"), "w") as f:
         f.write("torch %s\ntorchvision %s\nnumpy %s\nreference commit 7509e7d (laitalaj/cvpce)\n" %
                 (torch.__version__, torchvision.__version__, np.__version__))

@@ -120,3 +120,49 @@ def hot_path(encoder, gallery_embedding, image, cand_boxes, cand_scores, k=1, de
     if return_embedding:
         return boxes, res[0], res[1]
     return boxes, res
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# detection-metric bookkeeping (cvpce/metrics.py:36-124): NOT on the hot path and not rebuilt in cvpce_b200 -- the product
+# hands its matches to the reference's own _do_calculate.  The GPU box has no reference, so the a14 integration test passes
+# this restatement instead; tests/test_reference_pin.py checks it against the live metrics._do_calculate.
+# ---------------------------------------------------------------------------------------------------------------------
+def _precision_and_recall(tp, fp, total_targets):
+    """metrics.py:46-55"""
+    tp, fp = tp.cumsum(0), fp.cumsum(0)
+    precision = tp / (tp + fp)
+    precision[torch.isnan(precision)] = 0
+    recall = tp / total_targets if total_targets > 0 else torch.zeros_like(tp)
+    return precision, recall
+
+
+def _average_precision(precision, recall):
+    """metrics.py:62-70: 11-point interpolated AP."""
+    values = torch.zeros(11, dtype=torch.float)
+    for i, r in enumerate(torch.linspace(0, 1, 11)):
+        at = precision[recall >= r]
+        if len(at) == 0:
+            break
+        values[i] = at.max()
+    return values.mean()
+
+
+def do_calculate(iou_thresholds, matches_for_threshold, sorted_confidences, total_targets):
+    """metrics.py:36-44 (merge_matches) + :97-124 (_do_calculate)."""
+    conf, order = torch.sort(torch.cat(sorted_confidences), descending=True)
+    res = {}
+    for t in iou_thresholds:
+        d = matches_for_threshold[t]
+        tp, fp = torch.cat(d["true_positives"])[order], torch.cat(d["false_positives"])[order]
+        ar_300 = sum(d["recall_300"]) / len(d["recall_300"])
+        p, r = _precision_and_recall(tp, fp, total_targets)
+        f = 2 * p * r / (p + r)
+        f[torch.isnan(f)] = 0
+        if len(f) > 0:
+            max_f, at = f.max(0)
+            best = (max_f, p[at], r[at], conf[at])
+        else:
+            best = (0.0, 0.0, 0.0, 0.0)
+        res[t] = {"raw": {"p": p, "r": r, "f": f, "c": conf}, "f": best[0], "p": best[1], "r": best[2], "c": best[3],
+                  "ap": _average_precision(p, r), "ar_300": ar_300}
+    return res

@@ -131,3 +131,40 @@ def test_patch_swaps_and_restores_every_call_site(ref):
 def torchvision_ops():
     import torchvision
     return torchvision.ops
+
+
+def test_eval_entry_points_reproduce_the_golden(ref):
+    """a14: tests/golden/eval.npz IS what the unmodified eval_dihe / evaluate_detections return on the synthetic evaluation set
+    (re-run here against the live reference), and the AP-bookkeeping restatement the GPU test hands to the mirror agrees with
+    the reference's metrics._do_calculate."""
+    import os
+    import cvpce.metrics as metrics
+    from oracle import make_golden, torch_port
+    want = np.load(os.path.join(os.path.dirname(__file__), "golden", "eval.npz"))
+    got = make_golden.run_reference_evals(ref)
+    assert sorted(got) == sorted(want.files)
+    for k in want.files:
+        np.testing.assert_array_equal(got[k], want[k], err_msg=k)
+    rs = np.random.RandomState(5)
+    for n_img in (1, 4):
+        thr = (0.5, 0.75)
+        m = {t: {"true_positives": [], "false_positives": [], "recall_300": []} for t in thr}
+        conf, total = [], 0
+        for _ in range(n_img):
+            n = int(rs.randint(1, 30))
+            c = torch.sort(torch.from_numpy(rs.rand(n).astype(np.float32)), descending=True).values
+            conf.append(c)
+            nt = int(rs.randint(0, 12))
+            total += nt
+            for t in thr:
+                tp = torch.from_numpy((rs.rand(n) < 0.5).astype(np.float32))
+                m[t]["true_positives"].append(tp)
+                m[t]["false_positives"].append(1 - tp)
+                m[t]["recall_300"].append(tp.cumsum(0)[:300][-1] / nt if nt else torch.tensor(0.0))
+        a = metrics._do_calculate(thr, m, conf, total)
+        b = torch_port.do_calculate(thr, m, conf, total)
+        for t in thr:
+            for key in ("f", "p", "r", "c", "ap", "ar_300"):
+                assert float(a[t][key]) == float(b[t][key]), (t, key)
+            for key in ("p", "r", "f", "c"):
+                assert torch.equal(a[t]["raw"][key], b[t]["raw"][key])
