@@ -30,7 +30,7 @@ def _spy(production, annotations, sink):
     class Spy(production.Classifier):
         def classify(self, images, return_embedding=False):
             res = super().classify(images, return_embedding)
-            sink += [[annotations.index(a) for a in row] for row in (res[0] if return_embedding else res)]
+            sink.extend([annotations.index(a) for a in row] for row in (res[0] if return_embedding else res))
             return res
     return Spy
 
