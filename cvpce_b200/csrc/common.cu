@@ -67,13 +67,8 @@ struct TuningEntry {
 static TuningEntry g_tuning[] = {
     {"crop_kernel", {0}},       // 0: automatic; 1: shared-memory band kernel; 2: column-marching kernel; 3: direct kernel
     {"crop_band_rows", {0}},    // 0: automatic; else output rows per CTA of the antialias kernels (power of two, 8..256)
-    {"sim_plan", {0}},          // 0: automatic; 1: one CTA per (query block, split), cta_group::1; 2: persistent CTA pairs, cta_group::2
-    {"sim_split", {0}},         // sim_plan 1: forced split count (0: cost model)
-    {"sim_epi_groups", {0}},    // pair kernel: epilogue warp groups per CTA (1 / 2; 0: automatic)
-    {"sim_debug", {0}},         // pair kernel epilogue experiments (csrc/sim_topk_sm100.cu PtcParams::dbg_mode)
-    {"sim_ctas", {0}},          // persistent pair kernel: forced CTA count (0: SM count)
+    {"sim_split", {0}},         // tcgen05 search: forced gallery split count (0: cost model)
     {"mac_cluster", {0}},       // 0: automatic; 2 / 4 / 8: cluster size of the dense channels-last MAC kernel
-    {"pool_persistent", {0}},   // 0: automatic; 1: cluster per image (round-1 grid); 2: persistent pixel-range walk
 };
 
 int tuning(const char* name) {

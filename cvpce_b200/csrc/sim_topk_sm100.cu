@@ -14,8 +14,17 @@
 //               against the current k'-th score first, so the common case costs one compare per similarity
 //   grid = (query blocks of 128) x (gallery splits); each CTA writes its k' candidates per row to a small workspace.
 // Kernel 2  sim_select_kernel    (one warp per query row)
-//   merges the splits' candidates, re-scores the surviving k' in exact fp32 from the fp32 operands (parity mode) and
-//   writes the final top-k ordered by (similarity desc, gallery index asc).
+//   merges the splits' candidate lists by rank (every candidate finds its overall rank with binary searches in the other
+//   sorted lists), re-scores the survivors in exact fp32 from the fp32 operands (parity mode) -- in approximate order, stopping
+//   as soon as the bf16 error bound proves that no remaining candidate can enter the top-k -- and writes the final top-k
+//   ordered by (similarity desc, gallery index asc).
+//
+// Round-2 measurements that shaped this file (profiles/r2*_kbench_sim_*.jsonl, r2p_sim_launches_ncu_*.csv):
+//   the MMA + TMA pipeline alone sustains 0.86-0.93 of the measured cuBLAS burst rate; what costs the rest is the epilogue's
+//   per-row list maintenance (one warp per scheduler executing a long dependent instruction stream at every list warm-up).
+//   A persistent CTA-pair variant (tcgen05 cta_group::2, each CTA holding half of the gallery tile) and a cluster-multicast
+//   variant were built, validated bit-identical and measured: no faster, because operand feed is not the limiter; they are
+//   kept as evidence under profiles/r2_experiments/, not in the product.
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>
@@ -390,366 +399,6 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------------------------------------
-// Persistent CTA-pair kernel (tcgen05 cta_group::2): one CTA per SM, two SMs of a TPC form a pair that owns 256 query rows.
-//
-// What bounded round 1's kernel (one CTA per (query block, gallery split), cta_group::1), measured on B200 at both judged
-// shapes: ~0.47 us per 128 x 256 x 64 MMA block whether the CTA pulled 48 KB per block through the L2 (D = 1024: query block
-// streams too) or 32 KB (D = 512: query block resident) -- against 0.27 us of tensor work.  A CTA's shared memory holds only
-// 3-4 such stages, so the bytes in flight per SM (~100-190 KB) over the ~1.1 us round trip of a TMA load cap the feed rate at
-// ~50 B/clk per SM: the pipeline is load-latency bound, 57 % (D = 1024) / 73-77 % (D = 512) of the tensor rate.  Sharing the
-// gallery tile over a cluster by TMA multicast (tried: clusters of 2 and 4, every CTA still receives the whole tile) changed
-// nothing -- the limit is what each SM must take in, not what the L2 reads.
-// With cta_group::2 the pair computes a 256 x 256 tile per instruction: each CTA holds its own 128 query rows and only HALF
-// of the gallery tile (128 rows), the tensor cores read the other half from the partner's shared memory.  Per MMA block an SM
-// now takes in 16 KB (query block resident) or 32 KB (streaming) for the same tensor work, and the ring holds 6 stages.
-//  * both CTAs run a TMA producer (own query rows + own half of the gallery tile; the transaction bytes of both land on the
-//    LEADER's full barrier); only the leader's MMA thread issues tcgen05.mma.cta_group::2; tcgen05.commit multicasts the
-//    "slot free" / "accumulator ready" arrivals to both CTAs; both CTAs' epilogue warps read their own TMEM (their 128 rows of
-//    the 256-column accumulator) and arrive on the leader's "accumulator drained" barrier.
-//  * persistent work list per pair c of C pairs: whole query groups c, c + C, ... (all pairs stream the gallery tiles in
-//    lock-step, so concurrent reads of a tile are served by one L2 fill), then an equal share (+-1 tile) of the (group, tile)
-//    items of the remaining groups, flattened in (group, tile) order.  A pair that works on part of a group's tiles writes
-//    its candidates to slot (c - first pair of that group); the selection kernel merges the slots.
-// ------------------------------------------------------------------------------------------------------------------------
-constexpr int kPairStages = 6;
-constexpr int kPairBHalf = B_TILE_BYTES / 2;  // bytes of a gallery tile one CTA of the pair fetches (128 rows x 64 x bf16)
-constexpr uint32_t kInstrDescPair = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
-
-struct PtcParams {
-  int Q, G, D;
-  int n_tiles;       // ceil(G / BN)
-  int m_groups;      // ceil(ceil(Q / BM) / 2): query groups of 256 rows
-  int n_clusters;    // C pairs
-  int rounds;        // R = m_groups / C whole-group rounds
-  long long rem_items;  // (m_groups - R * C) * n_tiles
-  int max_slots;     // candidate lists per row in the workspace
-  int dbg_mode;      // development (cvpce_tuning_set("sim_debug")): 0 normal; 1 epilogue loads TMEM but skips the compares;
-                     // 2 epilogue skips TMEM.  Modes 1 and 2 give wrong results by design (they time the MMA pipeline alone).
-  float* cand_s;     // [Q, max_slots, KP]
-  int* cand_i;
-};
-
-__host__ __device__ __forceinline__ long long ptc_lo(long long rem_items, int C, int c) { return (rem_items * c) / C; }
-// pair whose remainder range [lo_c, lo_{c+1}) contains `item`
-__host__ __device__ __forceinline__ int ptc_cluster_of(long long rem_items, int C, long long item) {
-  int c = (int)((item * C) / rem_items);
-  if (c >= C) c = C - 1;
-  while (c + 1 < C && ptc_lo(rem_items, C, c + 1) <= item) ++c;
-  while (c > 0 && ptc_lo(rem_items, C, c) > item) --c;
-  return c;
-}
-// candidate lists of query group mg: first pair and count (whole-group rounds: one list in slot 0)
-__host__ __device__ __forceinline__ void ptc_lists_of_group(int mg, int C, int rounds, int n_tiles, long long rem_items, int* first,
-                                                            int* count) {
-  if (mg < rounds * C) {
-    *first = -1;
-    *count = 1;
-    return;
-  }
-  const long long g = mg - (long long)rounds * C;
-  const int a = ptc_cluster_of(rem_items, C, g * n_tiles);
-  const int b = ptc_cluster_of(rem_items, C, (g + 1) * n_tiles - 1);
-  *first = a;
-  *count = b - a + 1;
-}
-
-struct PtcWork {  // the work list of one pair
-  int C, c, rounds, n_tiles;
-  long long rem_lo, n_items;
-  __device__ __forceinline__ void init(const PtcParams& p, int cluster) {
-    C = p.n_clusters;
-    c = cluster;
-    rounds = p.rounds;
-    n_tiles = p.n_tiles;
-    rem_lo = ptc_lo(p.rem_items, C, c);
-    n_items = (long long)rounds * n_tiles + (ptc_lo(p.rem_items, C, c + 1) - rem_lo);
-  }
-  __device__ __forceinline__ void item(long long j, int* mg, int* tile) const {
-    const long long whole = (long long)rounds * n_tiles;
-    if (j < whole) {
-      const int r = (int)(j / n_tiles);
-      *mg = r * C + c;
-      *tile = (int)(j - (long long)r * n_tiles);
-    } else {
-      const long long it = rem_lo + (j - whole);
-      const long long g = it / n_tiles;
-      *mg = rounds * C + (int)g;
-      *tile = (int)(it - g * n_tiles);
-    }
-  }
-};
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
-}
-// shared::cluster address of the same shared-memory location in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
-}
-// TMA tile load into THIS CTA's shared memory whose transaction bytes complete on an mbarrier of either CTA of the pair
-__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-          smem_u32(smem_dst)),
-      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_dst, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-// D[tmem of both CTAs] (+)= A[smem of both CTAs: 128 rows each] * B[smem of both CTAs: 128 of the 256 rows each]^T
-__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// arrive on the mbarrier at this shared-memory offset in BOTH CTAs of the pair once all previously issued MMAs have completed
-__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
-               "h"((uint16_t)3)
-               : "memory");
-}
-
-// EW: epilogue warp groups per CTA.  Group g (4 warps, one per TMEM lane quadrant) scans columns [g, g+1) * 256 / EW of every
-// tile and keeps its own candidate list per row, so a row's candidates of one segment come as EW lists.
-template <bool RESIDENT_A, int KP, int EW>
-__global__ void __launch_bounds__(128 + 128 * EW, 1)
-sim_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_g, const PtcParams p) {
-  constexpr int kStages = kPairStages;
-  constexpr int kStageBytes = RESIDENT_A ? kPairBHalf : (A_TILE_BYTES + kPairBHalf);  // per CTA
-  extern __shared__ __align__(1024) uint8_t smem_dyn[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
-  uint8_t* a_res = smem;
-  uint8_t* ring = smem + (RESIDENT_A ? kMaxResidentKB * A_TILE_BYTES : 0);
-
-  __shared__ __align__(8) uint64_t full_bar[kStages];    // used in the leader: both CTAs' loads of a stage have landed
-  __shared__ __align__(8) uint64_t empty_bar[kStages];   // per CTA: the MMAs that read this stage are done
-  __shared__ __align__(8) uint64_t tmem_full_bar[2];     // per CTA: accumulator complete
-  __shared__ __align__(8) uint64_t tmem_empty_bar[2];    // used in the leader: 8 epilogue warps (both CTAs) drained it
-  __shared__ __align__(8) uint64_t a_full_bar;           // used in the leader: both CTAs' resident query tiles have landed
-  __shared__ __align__(8) uint64_t a_empty_bar;          // per CTA: the MMAs of the previous query group are done
-  __shared__ uint32_t tmem_base_smem;
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int rank = (int)cluster_ctarank();
-  const bool leader = rank == 0;
-  const int cluster = blockIdx.x >> 1;
-  const int KB = p.D / BK;
-  PtcWork work;
-  work.init(p, cluster);
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_q);
-    tma_prefetch_desc(&tmap_g);
-  }
-  if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], 8 * EW);  // one arrival per epilogue warp of both CTAs
-    }
-    mbar_init(&a_full_bar, 1);
-    mbar_init(&a_empty_bar, 1);
-    fence_barrier_init();
-  }
-  if (warp == 2) tmem_alloc_pair(&tmem_base_smem, kTmemCols);
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();  // the partner's barriers are initialised before any TMA completion / commit / arrive can reach them
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
-
-  if (warp == 0) {
-    // ================================================ TMA producer (both CTAs) ================================================
-    if (lane == 0) {
-      int stage = 0, cur_mg = -1;
-      uint32_t phase = 0, a_empty_phase = 0;
-      const uint32_t a_full_leader = mapa_u32(smem_u32(&a_full_bar), 0);
-      for (long long j = 0; j < work.n_items; ++j) {
-        int mg, tile;
-        work.item(j, &mg, &tile);
-        const int m0 = (mg * 2 + rank) * BM;
-        if (RESIDENT_A && mg != cur_mg) {
-          if (cur_mg >= 0) {  // the MMAs of the previous query group have finished reading the resident tiles
-            mbar_wait(&a_empty_bar, a_empty_phase);
-            a_empty_phase ^= 1;
-          }
-          if (leader) mbar_expect_tx(&a_full_bar, (uint32_t)(2 * KB * A_TILE_BYTES));
-          for (int kb = 0; kb < KB; ++kb) tma_load_2d_pair(a_res + kb * A_TILE_BYTES, &tmap_q, a_full_leader, kb * BK, m0);
-        }
-        cur_mg = mg;
-        for (int kb = 0; kb < KB; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (leader) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * kStageBytes));
-          const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
-          uint8_t* st = ring + stage * kStageBytes;
-          if (!RESIDENT_A) {
-            tma_load_2d_pair(st, &tmap_q, full_leader, kb * BK, m0);
-            tma_load_2d_pair(st + A_TILE_BYTES, &tmap_g, full_leader, kb * BK, tile * BN + rank * (BN / 2));
-          } else {
-            tma_load_2d_pair(st, &tmap_g, full_leader, kb * BK, tile * BN + rank * (BN / 2));
-          }
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ================================================= MMA issuer (leader CTA) =================================================
-    if (lane == 0 && leader) {
-      int stage = 0, cur_mg = -1;
-      uint32_t phase = 0, acc_phase = 0, a_phase = 0;
-      for (long long j = 0; j < work.n_items; ++j) {
-        int mg, tile;
-        work.item(j, &mg, &tile);
-        if (RESIDENT_A && mg != cur_mg) {
-          mbar_wait(&a_full_bar, a_phase);
-          a_phase ^= 1;
-          tc_fence_after();
-        }
-        cur_mg = mg;
-        const int acc = (int)(j & 1);
-        mbar_wait(&tmem_empty_bar[acc], ((acc_phase >> acc) & 1u) ^ 1u);
-        acc_phase ^= 1u << acc;
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-        for (int kb = 0; kb < KB; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint8_t* st = ring + stage * kStageBytes;
-          const uint32_t a_addr = RESIDENT_A ? smem_u32(a_res + kb * A_TILE_BYTES) : smem_u32(st);
-          const uint32_t b_addr = RESIDENT_A ? smem_u32(st) : smem_u32(st + A_TILE_BYTES);
-          const uint64_t a_desc = make_smem_desc(a_addr);
-          const uint64_t b_desc = make_smem_desc(b_addr);
-#pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), kInstrDescPair, (uint32_t)((kb | k) != 0));
-          umma_commit_pair(&empty_bar[stage]);  // frees the slot in both CTAs once these MMAs have read it
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-        umma_commit_pair(&tmem_full_bar[acc]);  // accumulator complete -> both CTAs' epilogues
-        if (RESIDENT_A && j + 1 < work.n_items) {
-          int mg2, tile2;
-          work.item(j + 1, &mg2, &tile2);
-          if (mg2 != mg) umma_commit_pair(&a_empty_bar);  // the resident query tiles of both CTAs may be overwritten
-        }
-      }
-    }
-  } else if (warp >= kEpilogueWarp0) {
-    // ================================================== epilogue (both CTAs) ==================================================
-    const int ew = (warp - kEpilogueWarp0) & 3;   // == warp % 4: the TMEM lane quadrant this warp may read
-    const int grp = (warp - kEpilogueWarp0) >> 2; // column group
-    constexpr int kCols = BN / EW;                // columns of a tile this group scans
-    TopList<KP> top;
-    top.init();
-    uint32_t acc_phase = 0;
-    const uint32_t tmem_empty_leader[2] = {mapa_u32(smem_u32(&tmem_empty_bar[0]), 0), mapa_u32(smem_u32(&tmem_empty_bar[1]), 0)};
-    for (long long j = 0; j < work.n_items; ++j) {
-      int mg, tile;
-      work.item(j, &mg, &tile);
-      const int acc = (int)(j & 1);
-      mbar_wait(&tmem_full_bar[acc], (acc_phase >> acc) & 1u);
-      acc_phase ^= 1u << acc;
-      tc_fence_after();
-      const int n0 = tile * BN + grp * kCols;   // first gallery row of this group's columns
-      const int valid = min(kCols, p.G - n0);   // columns beyond the gallery are TMA zero-fill: must not become candidates
-      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN + grp * kCols);
-      // common case: one compare per similarity against the row's current k'-th score; the (rare) survivors are collected in
-      // a bitmask and inserted in ascending column order, so equal scores keep the lower index
-      auto scan = [&](uint32_t (&r)[32], int c0) {
-        if (c0 >= valid) return;  // warp-uniform
-        const float thr = top.threshold();
-        uint32_t m = 0;
-#pragma unroll
-        for (int q = 0; q < 32; ++q) m |= (__uint_as_float(r[q]) > thr) ? (1u << q) : 0u;
-        if (c0 + 32 > valid) m &= (1u << (valid - c0)) - 1u;
-        while (m) {
-          const int q = __ffs(m) - 1;
-          m &= m - 1;
-          const float v = __uint_as_float(pick32(r, q));
-          if (v > top.threshold()) top.insert(v, n0 + c0 + q);
-        }
-      };
-      if (p.dbg_mode != 2) {
-        // software-pipelined: the TMEM load of the next 32 columns is in flight while this thread scans the current 32
-        // (a tcgen05.ld + wait round trip measured ~0.5 us while the tensor cores are accumulating into the other buffer)
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32(taddr, ra);
-#pragma unroll 1
-        for (int c0 = 0; c0 < kCols; c0 += 64) {
-          tmem_ld_wait();
-          if (c0 + 32 < kCols) tmem_ld_32x32(taddr + (uint32_t)(c0 + 32), rb);
-          if (p.dbg_mode != 1) scan(ra, c0);
-          if (c0 + 32 < kCols) {
-            tmem_ld_wait();
-            if (c0 + 64 < kCols) tmem_ld_32x32(taddr + (uint32_t)(c0 + 64), ra);
-            if (p.dbg_mode != 1) scan(rb, c0 + 32);
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(acc ? tmem_empty_leader[1] : tmem_empty_leader[0]);
-      // end of this pair's share of the query group: hand the candidate list over and start a fresh one
-      bool last = j + 1 == work.n_items;
-      if (!last) {
-        int mg2, tile2;
-        work.item(j + 1, &mg2, &tile2);
-        last = mg2 != mg;
-      }
-      if (last) {
-        const int row = (mg * 2 + rank) * BM + ew * 32 + lane;
-        if (row < p.Q) {
-          int first, count;
-          ptc_lists_of_group(mg, p.n_clusters, p.rounds, p.n_tiles, p.rem_items, &first, &count);
-          const int slot = (first < 0 ? 0 : cluster - first) * EW + grp;
-          float* cs = p.cand_s + ((size_t)row * p.max_slots * EW + slot) * KP;
-          int* ci = p.cand_i + ((size_t)row * p.max_slots * EW + slot) * KP;
-#pragma unroll
-          for (int q = 0; q < KP; q += 4) {
-            *reinterpret_cast<float4*>(cs + q) = make_float4(top.s[q], top.s[q + 1], top.s[q + 2], top.s[q + 3]);
-            *reinterpret_cast<int4*>(ci + q) = make_int4(top.i[q], top.i[q + 1], top.i[q + 2], top.i[q + 3]);
-          }
-        }
-        top.init();
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the partner's MMAs / loads / arrives may still touch it
-  if (warp == 2) {
-    tc_fence_after();
-    tmem_dealloc_pair(tmem_base, kTmemCols);
-  }
-}
-
-// ------------------------------------------------------------------------------------------------------------------------
 // select: merge split candidates, exact fp32 re-score, final ordering.  One warp per query row.
 // ------------------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool before(float sa, int ia, float sb, int ib) {
@@ -768,30 +417,15 @@ struct OutTargets {
   long long* i[kMaxOutTargets];
 };
 
-// How the candidate lists of a row are laid out in the workspace: `pitch` lists of KP entries per row, of which the first
-// n (row-dependent for the pair kernel) are valid; every list is sorted by (score desc, index asc); indices are unique across
-// the lists of a row.
-struct ListPlan {
-  int persistent;  // 0: n_split lists for every row (one CTA per (query block, split)); 1: pair kernel's work split
-  int pitch;
-  int n_split;
-  int ew, C, rounds, n_tiles;
-  long long rem_items;
-};
-
-__device__ __forceinline__ int lists_of_row(const ListPlan& lp, int row) {
-  if (!lp.persistent) return lp.n_split;
-  int first, count;
-  ptc_lists_of_group((row / BM) / 2, lp.C, lp.rounds, lp.n_tiles, lp.rem_items, &first, &count);
-  return count * lp.ew;
-}
+// The workspace holds n_split candidate lists of KP entries per row (one per gallery split), each sorted by (score desc,
+// index asc); indices are unique across the lists of a row.
 
 constexpr int kSelWarps = 4;
 constexpr int kSelMaxCand = 512;  // candidates of a row staged in shared memory (more take the serial merge)
 
 template <int KP>
 __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float* __restrict__ cand_s, const int* __restrict__ cand_i, int Q,
-                                                                    const ListPlan lp, int k, long long idx_base, int D,
+                                                                    int n_split, int k, long long idx_base, int D,
                                                                     const float* __restrict__ q32, const float* __restrict__ g32,
                                                                     const float* __restrict__ q_inv, const float* __restrict__ g_inv,
                                                                     const OutTargets out) {
@@ -802,10 +436,10 @@ __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float*
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int row = blockIdx.x * kSelWarps + wib;
   if (row >= Q) return;
-  const int n_lists = lists_of_row(lp, row);
+  const int n_lists = n_split;
   const int C = n_lists * KP;
-  const float* cs = cand_s + (size_t)row * lp.pitch * KP;
-  const int* ci = cand_i + (size_t)row * lp.pitch * KP;
+  const float* cs = cand_s + (size_t)row * n_split * KP;
+  const int* ci = cand_i + (size_t)row * n_split * KP;
   // ---- stage 1: the KP best candidates by kernel-1 score; lane j ends up holding the j-th
   float my_s = -INFINITY;
   int my_i = -1;
@@ -1116,115 +750,16 @@ static int launch_tc(const CUtensorMap& tq, const CUtensorMap& tg, const TcParam
   return CVPCE_OK;
 }
 
-// ---- persistent CTA-pair kernel: grid and work split
-struct PtcPlan {
-  int n_clusters, kp;
-  PtcParams p;
-};
-
-static size_t pair_smem_bytes(bool resident) {
-  const int stage_bytes = resident ? kPairBHalf : (A_TILE_BYTES + kPairBHalf);
-  return 1024 + (resident ? (size_t)kMaxResidentKB * A_TILE_BYTES : 0) + (size_t)kPairStages * stage_bytes;
-}
-
-static PtcPlan make_ptc_plan(int Q, int G, int D, int k, bool rescore) {
-  PtcPlan pl;
-  pl.kp = kp_for(k, rescore);
-  const int m_blocks = (Q + BM - 1) / BM;
-  PtcParams& p = pl.p;
-  p.Q = Q; p.G = G; p.D = D;
-  p.n_tiles = (G + BN - 1) / BN;
-  p.m_groups = (m_blocks + 1) / 2;
-  int max_clusters = sm_count() / 2;
-  const int forced = tuning("sim_ctas");
-  if (forced >= 2) max_clusters = forced / 2;
-  const long long items = (long long)p.m_groups * p.n_tiles;
-  pl.n_clusters = (int)(items < max_clusters ? (items > 0 ? items : 1) : max_clusters);
-  p.n_clusters = pl.n_clusters;
-  p.rounds = p.m_groups / pl.n_clusters;
-  p.rem_items = (long long)(p.m_groups - p.rounds * pl.n_clusters) * p.n_tiles;
-  int max_slots = p.rounds > 0 ? 1 : 0;
-  const int rem_groups = p.m_groups - p.rounds * pl.n_clusters;
-  for (int g = 0; g < rem_groups; ++g) {
-    int first, count;
-    ptc_lists_of_group(p.rounds * pl.n_clusters + g, pl.n_clusters, p.rounds, p.n_tiles, p.rem_items, &first, &count);
-    if (count > max_slots) max_slots = count;
-  }
-  p.max_slots = max_slots > 0 ? max_slots : 1;
-  p.dbg_mode = tuning("sim_debug");
-  p.cand_s = nullptr;
-  p.cand_i = nullptr;
-  return pl;
-}
-
-template <bool RES, int KP, int EW>
-static int launch_pair_ew(const CUtensorMap& tq, const CUtensorMap& tg, const PtcPlan& pl, cudaStream_t st) {
-  const size_t smem = pair_smem_bytes(RES);
-  auto kern = sim_topk_pair_kernel<RES, KP, EW>;
-  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem)) return rc;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(pl.n_clusters * 2), 1, 1);
-  cfg.blockDim = dim3(128 + 128 * EW, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  CVPCE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tq, tg, pl.p));
-  CVPCE_LAUNCH_OK("sim_topk_pair_kernel");
-  return CVPCE_OK;
-}
-
-template <bool RES, int KP>
-static int launch_pair(const CUtensorMap& tq, const CUtensorMap& tg, const PtcPlan& pl, int ew, cudaStream_t st) {
-  if (ew == 1) return launch_pair_ew<RES, KP, 1>(tq, tg, pl, st);
-  return launch_pair_ew<RES, KP, 2>(tq, tg, pl, st);
-}
-
-// epilogue warp groups of the pair kernel (cvpce_tuning_set("sim_epi_groups", 1 / 2); 0 = automatic).  Four groups (640
-// threads) leave 96 registers per thread: the two TMEM load buffers and the candidate list spill.
-static int pair_epilogue_groups() {
-  const int forced = tuning("sim_epi_groups");
-  return (forced == 1 || forced == 2) ? forced : 2;
-}
-
-// which tcgen05 kernel: cvpce_tuning_set("sim_plan", 1) = one CTA per (query block, split), cta_group::1 (round 1);
-// 2 = persistent CTA pairs, cta_group::2; 0 = automatic
-static bool use_round1_grid(int Q) {
-  const int forced = tuning("sim_plan");
-  if (forced == 1) return true;
-  if (forced == 2) return false;
-  return true;  // TODO(measure): flip to the pair kernel for Q > 128 once it is validated on the GPU
-}
-
 }  // namespace cvpce
 
 extern "C" size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k) {
   using namespace cvpce;
   if (Q <= 0 || G <= 0 || D <= 0 || k <= 0 || k > 32) return 0;
-  // sized for k' = 32 and for whichever grid a tuning override may select
+  // sized for k' = 32 and for whichever split count a tuning override may select
   const TcPlan a = make_plan(Q, G, D, k, true);
   size_t lists = (size_t)(a.n_split > 64 ? a.n_split : 64);  // any forced split count
   if (lists > (size_t)a.n_tiles) lists = (size_t)a.n_tiles;
   if (lists < (size_t)a.n_split) lists = (size_t)a.n_split;
-  {
-    const int m_groups = ((Q + BM - 1) / BM + 1) / 2;
-    const long long items = (long long)m_groups * a.n_tiles;
-    long long C = sm_count() / 2;
-    if (items < C) C = items;
-    // a group's n_tiles items are spread over at most ceil(n_tiles / floor(items per pair)) + 1 pairs
-    const long long rem_groups = m_groups % C;
-    if (rem_groups != 0) {
-      const long long per = (rem_groups * a.n_tiles) / C;
-      const size_t slots = (size_t)((per > 0 ? (a.n_tiles + per - 1) / per : a.n_tiles) + 1);
-      if (slots * 2 > lists) lists = slots * 2;  // two epilogue warp groups, one list each
-    }
-    if (lists < 2) lists = 2;
-  }
   return (size_t)Q * lists * 32 * 8 + 256;
 }
 
@@ -1251,62 +786,30 @@ static int sim_topk_impl(const void* q_bf16, const void* g_bf16, int Q, int G, i
   uintptr_t ws = (reinterpret_cast<uintptr_t>(workspace) + 127) & ~(uintptr_t)127;
   CUtensorMap tq, tg;
   if (int rc = make_tmap(q_bf16, Q, D, BM, &tq)) return rc;
-  ListPlan lp = {};
-  int kp;
-  float* cand_s;
-  int* cand_i;
-  if (use_round1_grid(Q)) {
-    const TcPlan pl = make_plan(Q, G > 0 ? G : 1, D, k, rescore);
-    kp = pl.kp;
-    const size_t need = (size_t)Q * pl.n_split * pl.kp * 8 + 256;
-    CVPCE_REQUIRE(workspace && workspace_bytes >= need, CVPCE_ERR_WORKSPACE, "sim_topk: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
-    cand_s = reinterpret_cast<float*>(ws);
-    cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.n_split * pl.kp * 4);
-    TcParams p;
-    p.Q = Q; p.G = G; p.D = D;
-    p.n_tiles = G > 0 ? pl.n_tiles : 0;
-    p.m_blocks = pl.m_blocks;
-    p.n_split = pl.n_split;
-    p.tiles_per_split = pl.tiles_per_split;
-    p.cand_s = cand_s;
-    p.cand_i = cand_i;
-    if (int rc = make_tmap(G > 0 ? g_bf16 : q_bf16, G > 0 ? G : Q, D, BN, &tg)) return rc;
-    int rc;
-    if (pl.kp == 16) rc = resident ? launch_tc<true, 16>(tq, tg, p, st) : launch_tc<false, 16>(tq, tg, p, st);
-    else             rc = resident ? launch_tc<true, 32>(tq, tg, p, st) : launch_tc<false, 32>(tq, tg, p, st);
-    if (rc) return rc;
-    lp.persistent = 0;
-    lp.pitch = pl.n_split;
-    lp.n_split = pl.n_split;
-  } else {
-    PtcPlan pl = make_ptc_plan(Q, G > 0 ? G : 1, D, k, rescore);
-    kp = pl.kp;
-    const int ew = pair_epilogue_groups();
-    const size_t need = (size_t)Q * pl.p.max_slots * ew * pl.kp * 8 + 256;
-    CVPCE_REQUIRE(workspace && workspace_bytes >= need, CVPCE_ERR_WORKSPACE, "sim_topk: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
-    cand_s = reinterpret_cast<float*>(ws);
-    cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.p.max_slots * ew * pl.kp * 4);
-    pl.p.G = G;  // G = 0: one (empty) tile whose columns are all invalid, so every row hands over an empty list
-    pl.p.cand_s = cand_s;
-    pl.p.cand_i = cand_i;
-    if (int rc = make_tmap(G > 0 ? g_bf16 : q_bf16, G > 0 ? G : Q, D, BN / 2, &tg)) return rc;
-    int rc;
-    if (pl.kp == 16) rc = resident ? launch_pair<true, 16>(tq, tg, pl, ew, st) : launch_pair<false, 16>(tq, tg, pl, ew, st);
-    else             rc = resident ? launch_pair<true, 32>(tq, tg, pl, ew, st) : launch_pair<false, 32>(tq, tg, pl, ew, st);
-    if (rc) return rc;
-    lp.persistent = 1;
-    lp.pitch = pl.p.max_slots * ew;
-    lp.ew = ew;
-    lp.C = pl.p.n_clusters;
-    lp.rounds = pl.p.rounds;
-    lp.n_tiles = pl.p.n_tiles;
-    lp.rem_items = pl.p.rem_items;
-  }
+  const TcPlan pl = make_plan(Q, G > 0 ? G : 1, D, k, rescore);
+  const int kp = pl.kp;
+  const size_t need = (size_t)Q * pl.n_split * pl.kp * 8 + 256;
+  CVPCE_REQUIRE(workspace && workspace_bytes >= need, CVPCE_ERR_WORKSPACE, "sim_topk: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  float* cand_s = reinterpret_cast<float*>(ws);
+  int* cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.n_split * pl.kp * 4);
+  TcParams p;
+  p.Q = Q; p.G = G; p.D = D;
+  p.n_tiles = G > 0 ? pl.n_tiles : 0;
+  p.m_blocks = pl.m_blocks;
+  p.n_split = pl.n_split;
+  p.tiles_per_split = pl.tiles_per_split;
+  p.cand_s = cand_s;
+  p.cand_i = cand_i;
+  if (int rc = make_tmap(G > 0 ? g_bf16 : q_bf16, G > 0 ? G : Q, D, BN, &tg)) return rc;
+  int rc;
+  if (pl.kp == 16) rc = resident ? launch_tc<true, 16>(tq, tg, p, st) : launch_tc<false, 16>(tq, tg, p, st);
+  else             rc = resident ? launch_tc<true, 32>(tq, tg, p, st) : launch_tc<false, 32>(tq, tg, p, st);
+  if (rc) return rc;
   const int grid = (Q + kSelWarps - 1) / kSelWarps;
   if (kp == 16)
-    sim_select_kernel<16><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, lp, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
+    sim_select_kernel<16><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
   else
-    sim_select_kernel<32><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, lp, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
+    sim_select_kernel<32><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
   CVPCE_LAUNCH_OK("sim_select_kernel");
   return CVPCE_OK;
 }
