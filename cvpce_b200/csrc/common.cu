@@ -65,8 +65,8 @@ struct TuningEntry {
   std::atomic<int> value;
 };
 static TuningEntry g_tuning[] = {
-    {"crop_kernel", {0}},       // 0: automatic; 1: shared-memory band kernel; 2: column-marching kernel; 3: direct kernel
-    {"crop_band_rows", {0}},    // 0: automatic; else output rows per CTA of the antialias kernels (power of two, 8..256)
+    {"crop_kernel", {0}},       // 0: automatic (column-marching kernel for antialias); 3: direct kernel
+    {"crop_band_rows", {0}},    // 0: automatic; else output rows per CTA of the antialias kernels (power of two, 8..256; column-marching kernel)
     {"sim_split", {0}},         // tcgen05 search: forced gallery split count (0: cost model)
     {"mac_cluster", {0}},       // 0: automatic; 2 / 4 / 8: cluster size of the dense channels-last MAC kernel
 };

@@ -7,24 +7,21 @@
 // The padded canvas is never materialised: a tap at (y,x) reads the image when y<h and x<w and is the pad value
 // otherwise.
 //
-// Three kernels:
+// Two kernels:
 //  * crop_resize_col_kernel (antialias, S <= 1024: the production case).  The triangle filter is separable and, down a
 //    column of the output, the vertical taps slide over consecutive source rows.  A thread owns ONE output column of a
 //    band of output rows and marches down it: each source row is filtered horizontally once (the column's taps and
 //    weights live in registers, read through the read-only path; a warp reads a contiguous span of the row) into a
 //    register ring of the last NT filtered rows, and each output row is the ring weighted by that row's vertical taps
 //    (broadcast reads of a small shared-memory table) -> affine -> one store per pixel (a warp writes 512 contiguous
-//    bytes in the 4-channel layout).  No shared-memory traffic for pixel data, no barrier inside the walk; ~7 thread
-//    instructions per output value instead of ~20 in the band kernel below.
-//  * crop_resize_sep_kernel (antialias, S % 4 == 0; round-1 kernel, kept for filters wider than the register ring).  The triangle filter is separable, so a CTA
-//    owns a band of output rows of one crop and walks it in chunks: a HORIZONTAL pass filters the source rows the chunk
-//    needs into a shared-memory ring ([row][3][S] fp32; rows shared by consecutive chunks are computed once), then a
-//    VERTICAL pass reads the ring with 128-bit LDS and writes 4 consecutive output pixels per thread with 128-bit
-//    streaming stores.  Tap ranges and normalised weights of the S columns / band rows are computed once per CTA into
-//    shared memory.  Per output pixel this costs ~(scale+1)*taps loads instead of taps^2 (x3 channels), which is what
-//    moves the kernel from L1/LSU-bound to HBM-bound.
-//  * crop_resize_kernel (direct form: one thread per output pixel, all taps): plain bilinear (antialias=0, 4 taps),
-//    odd S, and the fallback for extreme down-sampling whose tap table does not fit the shared-memory budget.
+//    bytes in the 4-channel layout).  No shared-memory traffic for pixel data, no barrier inside the walk.  The band's
+//    source rows are read exactly once, so they are prefetched into L1 six rows ahead and the next row's taps are
+//    loaded while the current row is filtered.  CTA-uniform specialisation on the crop's widest filter (2 / 4 / 6 taps:
+//    up-sampling, down-sampling by <= 2x, <= 3x); wider filters (boxes more than 3 S pixels long) take direct evaluation
+//    inside the kernel.  Round 1's shared-memory band kernel (2.56 ms for 6400 4-channel crops, long_scoreboard-bound,
+//    ~20 thread instructions per output value) was replaced by this one (1.32 ms, 0.93 of HBM on the bytes it moves).
+//  * crop_resize_kernel (direct form: one thread per output pixel, all taps): plain bilinear (antialias=0, 4 taps) and
+//    S > 1024.
 #include "common.cuh"
 #include <cuda_fp16.h>
 
@@ -117,22 +114,6 @@ __device__ __forceinline__ int tap_index(const TapSet& t, int j, int L) {
   return i < L ? i : L - 1;  // i1 = i0 + (i0 < L-1)
 }
 
-// ------------------------------------------------------------------------------------------------------------------------
-// separable band kernel (antialias)
-// ------------------------------------------------------------------------------------------------------------------------
-constexpr int kSepThreads = 256;
-#ifndef CVPCE_CROP_MIN_CTAS
-#define CVPCE_CROP_MIN_CTAS 4  // resident CTAs per SM the register allocation is held to
-#endif
-
-struct SepLayout {
-  int band_rows;   // output rows per CTA
-  int bands;       // CTAs per crop
-  int cap_rows;    // ring capacity in source rows
-  int max_taps;    // rows of the tap-weight tables (a crop whose filter is wider takes the direct fallback)
-  int chunk_rows;  // output rows per chunk (upper bound; shrinks when the ring cannot hold the source rows)
-};
-
 // direct evaluation of one output pixel (shared by the direct kernel and the band kernel's fallback)
 template <bool AA>
 __device__ __forceinline__ void direct_pixel(const float* __restrict__ base, long long sh, long long sc, int h, int w, int L, int ox,
@@ -219,408 +200,6 @@ __device__ __forceinline__ void store_pixel(void* outp, size_t k, int npix, int 
       out[o + 2] = to16<DTYPE>(a2);
     }
   }
-}
-
-// 4 consecutive output pixels (ox4 .. ox4+3) of row oy, 3 channels
-template <int DTYPE, int LAYOUT>
-__device__ __forceinline__ void store_quad(void* outp, size_t k, int S, int oy, int ox4, const float4& c0, const float4& c1,
-                                           const float4& c2) {
-  const size_t npix = (size_t)S * S;
-  const size_t pix = (size_t)oy * S + ox4;
-  if (LAYOUT == CVPCE_NCHW) {
-    const size_t o = k * 3 * npix + pix;
-    if (DTYPE == CVPCE_F32) {
-      float* out = reinterpret_cast<float*>(outp);
-      __stcs(reinterpret_cast<float4*>(out + o), c0);
-      __stcs(reinterpret_cast<float4*>(out + o + npix), c1);
-      __stcs(reinterpret_cast<float4*>(out + o + 2 * npix), c2);
-    } else {
-      unsigned short* out = reinterpret_cast<unsigned short*>(outp);
-      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack16x2<DTYPE>(c0.x, c0.y), pack16x2<DTYPE>(c0.z, c0.w)));
-      __stcs(reinterpret_cast<uint2*>(out + o + npix), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 2 * npix), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
-    }
-  } else if (LAYOUT == CVPCE_NHWC4) {
-    const size_t o = (k * npix + pix) * 4;  // 16 consecutive values: c0.x c1.x c2.x 0 c0.y ...
-    if (DTYPE == CVPCE_F32) {
-      float4* out = reinterpret_cast<float4*>(reinterpret_cast<float*>(outp) + o);
-      __stcs(out, make_float4(c0.x, c1.x, c2.x, 0.f));
-      __stcs(out + 1, make_float4(c0.y, c1.y, c2.y, 0.f));
-      __stcs(out + 2, make_float4(c0.z, c1.z, c2.z, 0.f));
-      __stcs(out + 3, make_float4(c0.w, c1.w, c2.w, 0.f));
-    } else {
-      uint4* out = reinterpret_cast<uint4*>(reinterpret_cast<unsigned short*>(outp) + o);  // 32 bytes, 32-byte aligned
-      __stcs(out, make_uint4(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, 0.f), pack16x2<DTYPE>(c0.y, c1.y), pack16x2<DTYPE>(c2.y, 0.f)));
-      __stcs(out + 1, make_uint4(pack16x2<DTYPE>(c0.z, c1.z), pack16x2<DTYPE>(c2.z, 0.f), pack16x2<DTYPE>(c0.w, c1.w), pack16x2<DTYPE>(c2.w, 0.f)));
-    }
-  } else {
-    const size_t o = (k * npix + pix) * 3;  // 12 consecutive values: c0.x c1.x c2.x c0.y ...
-    if (DTYPE == CVPCE_F32) {
-      float* out = reinterpret_cast<float*>(outp);
-      __stcs(reinterpret_cast<float4*>(out + o), make_float4(c0.x, c1.x, c2.x, c0.y));
-      __stcs(reinterpret_cast<float4*>(out + o + 4), make_float4(c1.y, c2.y, c0.z, c1.z));
-      __stcs(reinterpret_cast<float4*>(out + o + 8), make_float4(c2.z, c0.w, c1.w, c2.w));
-    } else {
-      unsigned short* out = reinterpret_cast<unsigned short*>(outp);  // 24 bytes, 8-byte aligned (S % 4 == 0)
-      __stcs(reinterpret_cast<uint2*>(out + o), make_uint2(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, c0.y)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 4), make_uint2(pack16x2<DTYPE>(c1.y, c2.y), pack16x2<DTYPE>(c0.z, c1.z)));
-      __stcs(reinterpret_cast<uint2*>(out + o + 8), make_uint2(pack16x2<DTYPE>(c2.z, c0.w), pack16x2<DTYPE>(c1.w, c2.w)));
-    }
-  }
-}
-
-// 4 consecutive output pixels of one row, 3 channels, at a precomputed byte address (NCHW: channel planes plane_bytes
-// apart; NHWC: 12 interleaved values)
-template <int DTYPE, int LAYOUT>
-__device__ __forceinline__ void store_quad_at(unsigned char* at, size_t plane_bytes, const float4& c0, const float4& c1,
-                                              const float4& c2) {
-  if (LAYOUT == CVPCE_NCHW) {
-    if (DTYPE == CVPCE_F32) {
-      __stcs(reinterpret_cast<float4*>(at), c0);
-      __stcs(reinterpret_cast<float4*>(at + plane_bytes), c1);
-      __stcs(reinterpret_cast<float4*>(at + 2 * plane_bytes), c2);
-    } else {
-      __stcs(reinterpret_cast<uint2*>(at), make_uint2(pack16x2<DTYPE>(c0.x, c0.y), pack16x2<DTYPE>(c0.z, c0.w)));
-      __stcs(reinterpret_cast<uint2*>(at + plane_bytes), make_uint2(pack16x2<DTYPE>(c1.x, c1.y), pack16x2<DTYPE>(c1.z, c1.w)));
-      __stcs(reinterpret_cast<uint2*>(at + 2 * plane_bytes), make_uint2(pack16x2<DTYPE>(c2.x, c2.y), pack16x2<DTYPE>(c2.z, c2.w)));
-    }
-  } else if (LAYOUT == CVPCE_NHWC4) {
-    if (DTYPE == CVPCE_F32) {
-      float4* o = reinterpret_cast<float4*>(at);
-      __stcs(o, make_float4(c0.x, c1.x, c2.x, 0.f));
-      __stcs(o + 1, make_float4(c0.y, c1.y, c2.y, 0.f));
-      __stcs(o + 2, make_float4(c0.z, c1.z, c2.z, 0.f));
-      __stcs(o + 3, make_float4(c0.w, c1.w, c2.w, 0.f));
-    } else {
-      uint4* o = reinterpret_cast<uint4*>(at);
-      __stcs(o, make_uint4(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, 0.f), pack16x2<DTYPE>(c0.y, c1.y), pack16x2<DTYPE>(c2.y, 0.f)));
-      __stcs(o + 1, make_uint4(pack16x2<DTYPE>(c0.z, c1.z), pack16x2<DTYPE>(c2.z, 0.f), pack16x2<DTYPE>(c0.w, c1.w), pack16x2<DTYPE>(c2.w, 0.f)));
-    }
-  } else {
-    if (DTYPE == CVPCE_F32) {
-      float4* o = reinterpret_cast<float4*>(at);
-      __stcs(o, make_float4(c0.x, c1.x, c2.x, c0.y));
-      __stcs(o + 1, make_float4(c1.y, c2.y, c0.z, c1.z));
-      __stcs(o + 2, make_float4(c2.z, c0.w, c1.w, c2.w));
-    } else {
-      uint2* o = reinterpret_cast<uint2*>(at);  // 24 bytes, 8-byte aligned (S % 4 == 0)
-      __stcs(o, make_uint2(pack16x2<DTYPE>(c0.x, c1.x), pack16x2<DTYPE>(c2.x, c0.y)));
-      __stcs(o + 1, make_uint2(pack16x2<DTYPE>(c1.y, c2.y), pack16x2<DTYPE>(c0.z, c1.z)));
-      __stcs(o + 2, make_uint2(pack16x2<DTYPE>(c2.z, c0.w), pack16x2<DTYPE>(c1.w, c2.w)));
-    }
-  }
-}
-
-// Everything a band walk needs, set up once per CTA.
-struct BandCtx {
-  const float* base;  // first pixel of the crop, channel 0
-  long long sc, sh;   // channel / row stride of the image (elements)
-  int h, w;           // crop extent inside the image (the rest of the L x L canvas is pad)
-  int b0, nb;         // band: first output row, number of rows
-  float pad;
-  float a[3], o[3];   // output affine
-  // shared memory
-  float* ring;        // [cap_rows][3][S] horizontally filtered source rows
-  const float* xw;    // [max_taps][S]   column tap weights, zero beyond a column's tap count
-  const float* yw;    // [band_rows][max_taps] row tap weights, zero beyond a row's tap count
-  const int* xmn;     // [S] first source column of each output column
-  const int* xsz;     // [S]
-  const int* ymn;     // [band_rows]
-  const int* ysz;     // [band_rows]
-};
-
-// Walks one band of one crop: chunks of output rows; per chunk a horizontal pass (global -> ring) and a vertical pass
-// (ring -> global).  ST: compile-time S (0 = run time); NT: compile-time upper bound of the tap count of every column
-// and row of this crop (2: up-sampling, 4: down-sampling by <= 1.5x; 0 = run-time loops over the tap tables).
-template <int ST, int NT, int DTYPE, int LAYOUT>
-__device__ __forceinline__ void band_walk(const CropParams& p, const SepLayout& lay, const BandCtx& c, size_t k) {
-  const int S = ST ? ST : p.S;
-  const int tid = threadIdx.x;
-  const int q = S >> 2;
-  // fixed thread -> column mappings (no per-item division): horizontal pass: thread t owns output column t % S of
-  // source rows hr, hr + rows_h, ...; vertical pass: quad t % (S/4) of chunk rows vr, vr + rows_v, ...
-  const int hx = tid % S, hr = tid / S, rows_h = kSepThreads / S;
-  const int qx = tid % q, vr = tid / q, rows_v = kSepThreads / q;
-  const int cap = lay.cap_rows;
-  const int MT = lay.max_taps;
-  const int RP = 3 * S;  // ring row pitch (floats)
-  const float pad = c.pad;
-
-  // ---- per-thread column invariants of the horizontal pass
-  const int hmn = c.xmn[hx], hsz = c.xsz[hx];
-  const int hin = max(0, min(hsz, c.w - hmn));  // taps [0, hin) read the image, [hin, hsz) the pad canvas
-  float wx[NT ? NT : 1];
-#pragma unroll
-  for (int j = 0; j < NT; ++j) wx[j] = c.xw[j * S + hx];  // zero beyond hsz
-  float padsum = 0.f;  // a source row below the image: every tap is the pad value
-  for (int j = 0; j < hsz; ++j) padsum = fmaf(c.xw[j * S + hx], pad, padsum);
-  const long long step = (long long)rows_h * c.sh;
-  const float* const col0 = c.base + hmn;
-
-  // ---- per-thread output pointer of the vertical pass (row b0, this thread's quad)
-  const size_t npix = (size_t)S * S;
-  const size_t esz = DTYPE == CVPCE_F32 ? 4 : 2;
-  unsigned char* outq = reinterpret_cast<unsigned char*>(p.out) +
-                        (LAYOUT == CVPCE_NCHW ? (k * 3 * npix + (size_t)c.b0 * S + (qx << 2)) * esz
-                                              : ((k * npix + (size_t)c.b0 * S + (qx << 2)) * (LAYOUT == CVPCE_NHWC4 ? 4 : 3)) * esz);
-  const size_t out_row_bytes = (LAYOUT == CVPCE_NCHW ? (size_t)S : (size_t)(LAYOUT == CVPCE_NHWC4 ? 4 : 3) * S) * esz;
-  const size_t plane_bytes = npix * esz;
-  const float* const ringq = c.ring + (qx << 2);
-
-  int done_until = c.ymn[0];  // source rows < done_until are either in the ring or no longer needed
-  int r0 = 0;                 // first band row of the chunk
-  while (r0 < c.nb) {
-    // chunk height: as many rows (<= chunk_rows) as the ring can serve
-    const int src_lo = c.ymn[r0];
-    int tb = min(lay.chunk_rows, c.nb - r0);
-    while (tb > 1 && c.ymn[r0 + tb - 1] + c.ysz[r0 + tb - 1] - src_lo > cap) --tb;
-    const int src_hi = c.ymn[r0 + tb - 1] + c.ysz[r0 + tb - 1];  // tap ranges are monotone in the output row
-    const int ra = max(done_until, src_lo);
-    const int lo_slot = src_lo % cap;  // ring slot of source row src_lo (CTA-uniform, once per chunk)
-
-    // ---- horizontal pass: source rows [ra, src_hi) -> ring
-    if (hr < rows_h) {
-      int y = ra + hr;
-      int slot = lo_slot + (y - src_lo);
-      if (slot >= cap) slot -= cap;
-      float* dst = c.ring + slot * RP + hx;
-      const float* rp0 = col0 + (long long)y * c.sh;
-      const float* rp1 = rp0 + c.sc;
-      const float* rp2 = rp1 + c.sc;
-      if (NT) {
-        float v[NT ? NT : 1][3];  // taps beyond hin keep the pad value for the whole walk
-#pragma unroll
-        for (int j = 0; j < NT; ++j) v[j][0] = v[j][1] = v[j][2] = pad;
-        for (; y < src_hi; y += rows_h) {
-          float t0, t1, t2;
-          if (y < c.h) {
-#pragma unroll
-            for (int j = 0; j < NT; ++j) {  // 3*NT independent loads in flight, then the fma chains
-              if (j < hin) {
-                v[j][0] = __ldg(rp0 + j);
-                v[j][1] = __ldg(rp1 + j);
-                v[j][2] = __ldg(rp2 + j);
-              }
-            }
-            t0 = wx[0] * v[0][0];
-            t1 = wx[0] * v[0][1];
-            t2 = wx[0] * v[0][2];
-#pragma unroll
-            for (int j = 1; j < NT; ++j) {
-              t0 = fmaf(wx[j], v[j][0], t0);
-              t1 = fmaf(wx[j], v[j][1], t1);
-              t2 = fmaf(wx[j], v[j][2], t2);
-            }
-          } else {
-            t0 = t1 = t2 = padsum;
-          }
-          dst[0] = t0;
-          dst[S] = t1;
-          dst[2 * S] = t2;
-          slot += rows_h;
-          dst += rows_h * RP;
-          if (slot >= cap) {  // rows_h <= cap
-            slot -= cap;
-            dst -= cap * RP;
-          }
-          rp0 += step;
-          rp1 += step;
-          rp2 += step;
-        }
-      } else {
-        for (; y < src_hi; y += rows_h) {
-          float t0 = 0.f, t1 = 0.f, t2 = 0.f;
-          if (y < c.h) {
-            for (int j = 0; j < hsz; ++j) {
-              const float wj = c.xw[j * S + hx];
-              const bool in = j < hin;
-              t0 = fmaf(wj, in ? __ldg(rp0 + j) : pad, t0);
-              t1 = fmaf(wj, in ? __ldg(rp1 + j) : pad, t1);
-              t2 = fmaf(wj, in ? __ldg(rp2 + j) : pad, t2);
-            }
-          } else {
-            t0 = t1 = t2 = padsum;
-          }
-          dst[0] = t0;
-          dst[S] = t1;
-          dst[2 * S] = t2;
-          slot += rows_h;
-          dst += rows_h * RP;
-          if (slot >= cap) {
-            slot -= cap;
-            dst -= cap * RP;
-          }
-          rp0 += step;
-          rp1 += step;
-          rp2 += step;
-        }
-      }
-    }
-    done_until = src_hi;
-    __syncthreads();
-
-    // ---- vertical pass: tb output rows x S/4 quads, 3 channels each
-    if (vr < rows_v) {
-      for (int rr = vr; rr < tb; rr += rows_v) {
-        const int r = r0 + rr;
-        const int mn = c.ymn[r], sz = c.ysz[r];
-        int slot = lo_slot + (mn - src_lo);
-        if (slot >= cap) slot -= cap;
-        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0, c2 = c0;
-        if (NT) {
-          float wy[NT ? NT : 1];
-          if (NT == 2) {
-            const float2 t = *reinterpret_cast<const float2*>(c.yw + r * MT);
-            wy[0] = t.x;
-            wy[NT > 1 ? 1 : 0] = t.y;
-          } else {
-#pragma unroll
-            for (int i = 0; i < NT; i += 4) {
-              const float4 t = *reinterpret_cast<const float4*>(c.yw + r * MT + i);
-              wy[i] = t.x;
-              wy[(i + 1) % (NT ? NT : 1)] = t.y;
-              wy[(i + 2) % (NT ? NT : 1)] = t.z;
-              wy[(i + 3) % (NT ? NT : 1)] = t.w;
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < NT; ++i) {
-            // a tap beyond this row's count has weight 0; it re-reads the row's last real tap so the data is finite
-            int s = slot + min(i, sz - 1);
-            if (s >= cap) s -= cap;
-            const float* src = ringq + s * RP;
-            const float4 v0 = *reinterpret_cast<const float4*>(src);
-            const float4 v1 = *reinterpret_cast<const float4*>(src + S);
-            const float4 v2 = *reinterpret_cast<const float4*>(src + 2 * S);
-            const float wi = wy[i];
-            c0.x = fmaf(wi, v0.x, c0.x); c0.y = fmaf(wi, v0.y, c0.y); c0.z = fmaf(wi, v0.z, c0.z); c0.w = fmaf(wi, v0.w, c0.w);
-            c1.x = fmaf(wi, v1.x, c1.x); c1.y = fmaf(wi, v1.y, c1.y); c1.z = fmaf(wi, v1.z, c1.z); c1.w = fmaf(wi, v1.w, c1.w);
-            c2.x = fmaf(wi, v2.x, c2.x); c2.y = fmaf(wi, v2.y, c2.y); c2.z = fmaf(wi, v2.z, c2.z); c2.w = fmaf(wi, v2.w, c2.w);
-          }
-        } else {
-          const float* wyp = c.yw + r * MT;
-          for (int i = 0; i < sz; ++i) {
-            const float wi = wyp[i];
-            const float* src = ringq + slot * RP;
-            const float4 v0 = *reinterpret_cast<const float4*>(src);
-            const float4 v1 = *reinterpret_cast<const float4*>(src + S);
-            const float4 v2 = *reinterpret_cast<const float4*>(src + 2 * S);
-            c0.x = fmaf(wi, v0.x, c0.x); c0.y = fmaf(wi, v0.y, c0.y); c0.z = fmaf(wi, v0.z, c0.z); c0.w = fmaf(wi, v0.w, c0.w);
-            c1.x = fmaf(wi, v1.x, c1.x); c1.y = fmaf(wi, v1.y, c1.y); c1.z = fmaf(wi, v1.z, c1.z); c1.w = fmaf(wi, v1.w, c1.w);
-            c2.x = fmaf(wi, v2.x, c2.x); c2.y = fmaf(wi, v2.y, c2.y); c2.z = fmaf(wi, v2.z, c2.z); c2.w = fmaf(wi, v2.w, c2.w);
-            if (++slot == cap) slot = 0;
-          }
-        }
-        c0.x = fmaf(c0.x, c.a[0], c.o[0]); c0.y = fmaf(c0.y, c.a[0], c.o[0]); c0.z = fmaf(c0.z, c.a[0], c.o[0]); c0.w = fmaf(c0.w, c.a[0], c.o[0]);
-        c1.x = fmaf(c1.x, c.a[1], c.o[1]); c1.y = fmaf(c1.y, c.a[1], c.o[1]); c1.z = fmaf(c1.z, c.a[1], c.o[1]); c1.w = fmaf(c1.w, c.a[1], c.o[1]);
-        c2.x = fmaf(c2.x, c.a[2], c.o[2]); c2.y = fmaf(c2.y, c.a[2], c.o[2]); c2.z = fmaf(c2.z, c.a[2], c.o[2]); c2.w = fmaf(c2.w, c.a[2], c.o[2]);
-        store_quad_at<DTYPE, LAYOUT>(outq + (size_t)r * out_row_bytes, plane_bytes, c0, c1, c2);
-      }
-    }
-    r0 += tb;
-    __syncthreads();  // the next horizontal pass overwrites ring slots this pass was reading
-  }
-}
-
-template <int ST, int DTYPE, int LAYOUT>
-__global__ void __launch_bounds__(kSepThreads, CVPCE_CROP_MIN_CTAS) crop_resize_sep_kernel(const CropParams p, const SepLayout lay) {
-  extern __shared__ __align__(16) unsigned char sep_smem[];
-  const int S = ST ? ST : p.S;
-  const int k = blockIdx.x / lay.bands;
-  const int band = blockIdx.x - k * lay.bands;
-  const int b0 = band * lay.band_rows;
-  const int nb = min(S, b0 + lay.band_rows) - b0;
-  const int tid = threadIdx.x;
-  const int MT = lay.max_taps;
-
-  // shared-memory carve-up (all regions 16-byte aligned: S % 4 == 0, max_taps % 4 == 0)
-  float* ring = reinterpret_cast<float*>(sep_smem);                     // [cap_rows][3][S]
-  float* xw = ring + (size_t)lay.cap_rows * 3 * S;                      // [max_taps][S]
-  float* yw = xw + (size_t)MT * S;                                      // [band_rows][max_taps]
-  int* xmn = reinterpret_cast<int*>(yw + (size_t)MT * lay.band_rows);   // [S]
-  int* xsz = xmn + S;                                                   // [S]
-  int* ymn = xsz + S;                                                   // [band_rows]
-  int* ysz = ymn + lay.band_rows;                                       // [band_rows]
-  __shared__ int s_max_taps;
-
-  const float4 bx = __ldg(p.boxes + k);
-  int img_i = p.box_image_idx ? __ldg(p.box_image_idx + k) : 0;
-  if (img_i < 0 || img_i >= p.n_images) img_i = 0;
-  const int64_t* row = p.image_table + (size_t)img_i * 5;
-  const float* img = reinterpret_cast<const float*>(static_cast<uintptr_t>(__ldg(row + 0)));
-  const long long H = __ldg(row + 1), W = __ldg(row + 2);
-  const long long sc = __ldg(row + 3), sh = __ldg(row + 4);
-  const long long xs = slice_index(trunc_to_long(bx.x), W), xe = slice_index(trunc_to_long(bx.z), W);
-  const long long ys = slice_index(trunc_to_long(bx.y), H), ye = slice_index(trunc_to_long(bx.w), H);
-  const int w = (int)(xe > xs ? xe - xs : 0), h = (int)(ye > ys ? ye - ys : 0);
-  const int L = max(h, w);
-  if (band == 0 && tid == 0 && p.valid) p.valid[k] = L > 0 ? 1 : 0;
-  const float pad = p.pad;
-
-  if (L == 0) {  // empty crop: pad value through the affine
-    const float e0 = fmaf(pad, p.a[0], p.b[0]), e1 = fmaf(pad, p.a[1], p.b[1]), e2 = fmaf(pad, p.a[2], p.b[2]);
-    const float4 c0 = make_float4(e0, e0, e0, e0), c1 = make_float4(e1, e1, e1, e1), c2 = make_float4(e2, e2, e2, e2);
-    const int q = S >> 2;
-    for (int it = tid; it < nb * q; it += kSepThreads) {
-      const int r = it / q;
-      store_quad<DTYPE, LAYOUT>(p.out, (size_t)k, S, b0 + r, (it - r * q) << 2, c0, c1, c2);
-    }
-    return;
-  }
-
-  const float scale = (float)L / (float)S;
-  const float support = scale >= 1.f ? scale : 1.f;
-  const float invscale = scale >= 1.f ? 1.f / scale : 1.f;
-  const float* base = img + ys * sh + xs;
-
-  // ---- tap tables: S columns and the band's rows (weights zero-filled up to max_taps)
-  if (tid == 0) s_max_taps = 0;
-  __syncthreads();
-  int my_max = 0;
-  for (int o = tid; o < S + nb; o += kSepThreads) {
-    const bool isx = o < S;
-    const TapSet t = make_taps<true>(isx ? o : b0 + (o - S), L, scale, support, invscale);
-    my_max = max(my_max, t.sz);
-    if (t.sz <= MT) {
-      float* wt = isx ? (xw + o) : (yw + (size_t)(o - S) * MT);
-      const int pitch = isx ? S : 1;
-      for (int j = 0; j < MT; ++j) wt[(size_t)j * pitch] = j < t.sz ? tap_weight<true>(t, j, invscale) : 0.f;
-      if (isx) {
-        xmn[o] = t.mn;
-        xsz[o] = t.sz;
-      } else {
-        ymn[o - S] = t.mn;
-        ysz[o - S] = t.sz;
-      }
-    }
-  }
-  if (my_max > 0) atomicMax(&s_max_taps, my_max);
-  __syncthreads();
-  const int max_taps = s_max_taps;
-  // Filters wider than the tap tables, or a single output row needing more source rows than the ring holds:
-  // evaluate the band directly.
-  if (max_taps > MT || max_taps > lay.cap_rows) {
-    for (int it = tid; it < nb * S; it += kSepThreads) {
-      const int r = it / S, ox = it - r * S;
-      float v0, v1, v2;
-      direct_pixel<true>(base, sh, sc, h, w, L, ox, b0 + r, scale, support, invscale, pad, v0, v1, v2);
-      store_pixel<DTYPE, LAYOUT>(p.out, (size_t)k, S * S, (b0 + r) * S + ox, fmaf(v0, p.a[0], p.b[0]), fmaf(v1, p.a[1], p.b[1]),
-                                 fmaf(v2, p.a[2], p.b[2]));
-    }
-    return;
-  }
-
-  BandCtx c;
-  c.base = base; c.sc = sc; c.sh = sh; c.h = h; c.w = w; c.b0 = b0; c.nb = nb; c.pad = pad;
-  for (int i = 0; i < 3; ++i) {
-    c.a[i] = p.a[i];
-    c.o[i] = p.b[i];
-  }
-  c.ring = ring; c.xw = xw; c.yw = yw; c.xmn = xmn; c.xsz = xsz; c.ymn = ymn; c.ysz = ysz;
-  // CTA-uniform specialisation on the widest filter of this crop
-  if (max_taps <= 2) band_walk<ST, 2, DTYPE, LAYOUT>(p, lay, c, (size_t)k);
-  else if (max_taps <= 4) band_walk<ST, 4, DTYPE, LAYOUT>(p, lay, c, (size_t)k);
-  else band_walk<ST, 0, DTYPE, LAYOUT>(p, lay, c, (size_t)k);
 }
 
 // ------------------------------------------------------------------------------------------------------------------------
@@ -948,66 +527,6 @@ static int launch_col(const CropParams& p, int out_dtype, int out_layout, cudaSt
   return launch_col_one<CVPCE_BF16, CVPCE_NHWC>(p, lay, st);
 }
 
-static size_t sep_smem_bytes(int S, const SepLayout& lay) {
-  return ((size_t)lay.cap_rows * 3 * S + (size_t)lay.max_taps * S + (size_t)lay.max_taps * lay.band_rows) * sizeof(float) +
-         (size_t)(2 * S + 2 * lay.band_rows) * sizeof(int);
-}
-
-template <int ST, int DTYPE, int LAYOUT>
-static int launch_sep_st(const CropParams& p, const SepLayout& lay, size_t smem, cudaStream_t st) {
-  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&crop_resize_sep_kernel<ST, DTYPE, LAYOUT>), smem)) return rc;
-  crop_resize_sep_kernel<ST, DTYPE, LAYOUT><<<(unsigned)((long long)p.K * lay.bands), kSepThreads, smem, st>>>(p, lay);
-  CVPCE_LAUNCH_OK("crop_resize_sep_kernel");
-  return CVPCE_OK;
-}
-
-// S = 256 (the reference's CLASSIFICATION_IMAGE_SIZE, datautils.py:232) and 224 get compile-time strides
-template <int DTYPE, int LAYOUT>
-static int launch_sep_one(const CropParams& p, const SepLayout& lay, size_t smem, cudaStream_t st) {
-  if (p.S == 256) return launch_sep_st<256, DTYPE, LAYOUT>(p, lay, smem, st);
-  if (p.S == 224) return launch_sep_st<224, DTYPE, LAYOUT>(p, lay, smem, st);
-  return launch_sep_st<0, DTYPE, LAYOUT>(p, lay, smem, st);
-}
-
-// Returns -1 when the shape is outside what the band kernel handles (the caller then uses the direct kernel).
-static int launch_sep(const CropParams& p, int out_dtype, int out_layout, cudaStream_t st) {
-  const int S = p.S;
-  if (S < 32 || S > kSepThreads) return -1;
-  SepLayout lay;
-  // band height: 64 output rows when there are enough crops to fill the machine, fewer rows per CTA otherwise
-  const long long want_ctas = 4ll * sm_count();
-  int band_rows = tuning("crop_band_rows");
-  if (band_rows < 8 || band_rows > 256 || (band_rows & (band_rows - 1))) band_rows = 64;
-  while (band_rows > 8 && (long long)p.K * ((S + band_rows - 1) / band_rows) < want_ctas) band_rows >>= 1;
-  if (band_rows > S) band_rows = (S + 3) & ~3;
-  lay.band_rows = band_rows;
-  lay.bands = (S + band_rows - 1) / band_rows;
-  lay.max_taps = S >= 128 ? 8 : 16;  // 8 taps: down-sampling by up to 3.5x; wider filters take the direct fallback
-  lay.chunk_rows = 16;
-  // ring capacity from a shared-memory budget per CTA (48 KB: 4 CTAs = 32 warps resident per SM)
-  const size_t budget = (size_t)48 * 1024;
-  lay.cap_rows = 0;
-  const size_t fixed = sep_smem_bytes(S, lay);
-  long long cap = fixed < budget ? (long long)((budget - fixed) / ((size_t)3 * S * sizeof(float))) : 0;
-  if (cap < 8) cap = 8;
-  if (cap > 128) cap = 128;
-  lay.cap_rows = (int)cap;
-  const size_t smem = sep_smem_bytes(S, lay);
-  if (smem > 200 * 1024) return -1;
-  if (out_layout == CVPCE_NHWC4) {
-    if (out_dtype == CVPCE_F32) return launch_sep_one<CVPCE_F32, CVPCE_NHWC4>(p, lay, smem, st);
-    if (out_dtype == CVPCE_F16) return launch_sep_one<CVPCE_F16, CVPCE_NHWC4>(p, lay, smem, st);
-    return launch_sep_one<CVPCE_BF16, CVPCE_NHWC4>(p, lay, smem, st);
-  }
-  if (out_dtype == CVPCE_F32 && out_layout == CVPCE_NCHW) return launch_sep_one<CVPCE_F32, CVPCE_NCHW>(p, lay, smem, st);
-  if (out_dtype == CVPCE_F32) return launch_sep_one<CVPCE_F32, CVPCE_NHWC>(p, lay, smem, st);
-  if (out_dtype == CVPCE_F16)
-    return out_layout == CVPCE_NCHW ? launch_sep_one<CVPCE_F16, CVPCE_NCHW>(p, lay, smem, st)
-                                    : launch_sep_one<CVPCE_F16, CVPCE_NHWC>(p, lay, smem, st);
-  if (out_layout == CVPCE_NCHW) return launch_sep_one<CVPCE_BF16, CVPCE_NCHW>(p, lay, smem, st);
-  return launch_sep_one<CVPCE_BF16, CVPCE_NHWC>(p, lay, smem, st);
-}
-
 // ------------------------------------------------------------------------------------------------------------------------
 // direct kernel: one thread per output pixel
 // ------------------------------------------------------------------------------------------------------------------------
@@ -1110,18 +629,11 @@ extern "C" int cvpce_crop_resize(const int64_t* image_table, int n_images, const
   }
   p.out = out;
   p.valid = valid;
-  // kernel choice: the column-marching kernel for every antialias shape it covers; cvpce_tuning_set("crop_kernel", 1 | 3)
-  // selects the round-1 band kernel / the direct kernel instead (A/B measurements and cross-checks of the kernels)
-  const int which = tuning("crop_kernel");
-  if (antialias && which != 3) {
-    if (which != 1) {
-      const int rc = launch_col(p, out_dtype, out_layout, (cudaStream_t)stream);
-      if (rc >= 0) return rc;
-    }
-    if ((S & 3) == 0) {
-      const int rc = launch_sep(p, out_dtype, out_layout, (cudaStream_t)stream);
-      if (rc >= 0) return rc;
-    }
+  // kernel choice: the column-marching kernel for every antialias shape it covers (S <= 1024); cvpce_tuning_set("crop_kernel", 3)
+  // forces the direct kernel (cross-check of the two kernels)
+  if (antialias && tuning("crop_kernel") != 3) {
+    const int rc = launch_col(p, out_dtype, out_layout, (cudaStream_t)stream);
+    if (rc >= 0) return rc;
   }
   return antialias ? launch_crop<true>(p, out_dtype, out_layout, (cudaStream_t)stream)
                    : launch_crop<false>(p, out_dtype, out_layout, (cudaStream_t)stream);

@@ -163,9 +163,9 @@ def test_crops_multi_image_layouts_affine(ops):
 
 
 def test_crops_band_kernel_paths(ops):
-    """The column-marching kernel (default) and the shared-memory band kernel against the oracle and against the direct
-    kernel: band heights 8..64 (few / many crops), up-sampling, 2-4 and 5-6 tap filters, the direct fallback inside the
-    antialias kernels for wider filters (the 900 x 700 box at S = 32 / 64), ring wrap-around, all output layouts."""
+    """The column-marching kernel against the oracle and against the direct kernel: band heights 8..256 (few / many crops),
+    up-sampling, 2-4 and 5-6 tap filters, the direct fallback inside the kernel for wider filters (the 900 x 700 box at
+    S = 32 / 64), crops narrower than the filter, crops on the image border, all output layouts."""
     from cvpce_b200 import _lib
     img = synth.shelf_image(77, 700, 900)
     gimg = dev(img)
@@ -192,12 +192,6 @@ def test_crops_band_kernel_paths(ops):
         with _lib.tuning(crop_kernel=3):
             direct = ops.crop_resize(table, 1, dev(boxes), None, S, True)
         np.testing.assert_allclose(direct.cpu().numpy(), out.cpu().numpy(), rtol=0, atol=2e-6)
-        with _lib.tuning(crop_kernel=1):
-            band = ops.crop_resize(table, 1, dev(boxes), None, S, True)
-            band16 = ops.crop_resize(table, 1, dev(boxes), None, S, True, out_dtype=torch.bfloat16, channels_last=True)
-        np.testing.assert_allclose(band.cpu().numpy(), want, rtol=0, atol=1e-5)
-        np.testing.assert_allclose(band.cpu().numpy(), out.cpu().numpy(), rtol=0, atol=2e-6)
-        np.testing.assert_allclose(band16.float().cpu().numpy(), b16.float().cpu().numpy(), rtol=1e-2, atol=1e-2)
         for rows in (8, 32, 256):
             with _lib.tuning(crop_band_rows=rows):
                 assert torch.equal(ops.crop_resize(table, 1, dev(boxes), None, S, True), out)

@@ -200,6 +200,8 @@ def bench_sim(args):
     shapes = [(200, 180, 1024, 1), (6400, 8192, 1024, 5), (25000, 125000, 512, 5), (100000, 125000, 512, 5)]
     if args.quick:
         shapes = shapes[:3]
+    if args.shape:
+        shapes = [tuple(int(v) for v in args.shape.split(","))]
     for Q, G, D, k in shapes:
         q = torch.randn((Q, D), device=dev)
         g = torch.randn((G, D), device=dev)
@@ -255,6 +257,7 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--sizes", type=int, nargs="*", default=[256, 224])
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--shape", default=None, help="sim: one shape Q,G,D,k instead of the list")
     ap.add_argument("--tune", nargs="*", default=[], help="name=value overrides passed to cvpce_tuning_set")
     args = ap.parse_args()
     torch.cuda.set_device(0)
