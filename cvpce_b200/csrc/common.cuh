@@ -37,7 +37,8 @@ int set_err(int code, const char* fmt, ...);
 int require_sm100();  // CVPCE_OK or CVPCE_ERR_NO_DEVICE (cached per device)
 int sm_count();       // SM count of the current device (148 on B200)
 int tuning(const char* name);  // development override set through cvpce_tuning_set (0 = automatic)
-// Opt a kernel into `bytes` of dynamic shared memory on the CURRENT device (no-op while dynamic + static surely fit the 48 KB default).
+// Opt a kernel into `bytes` of dynamic shared memory on the CURRENT device (cached per (device, function); no-op while
+// dynamic + static surely fit the 48 KB default).
 int ensure_dynamic_smem(const void* func, size_t bytes);
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

@@ -205,8 +205,8 @@ extern "C" int cvpce_iou_match(const float* row_boxes, const int64_t* row_labels
   p.row_matched = row_matched;
   p.col_matched = col_matched;
   const size_t smem = (size_t)p.words_cap * (1 + kMatchPanel) * sizeof(uint32_t);
-  if (smem > 40 * 1024)  // per-device attribute: set on every launch that needs it
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(iou_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  if (smem > 40 * 1024)
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&iou_match_kernel), 96 * 1024)) return rc;
   iou_match_kernel<<<(unsigned)n_problems, kMatchThreads, smem, (cudaStream_t)stream>>>(p);
   CVPCE_LAUNCH_OK("iou_match_kernel");
   return CVPCE_OK;

@@ -404,8 +404,7 @@ static int launch_nms(NmsParams& p, const float* boxes, const float* scores, int
   int threads = cap / 2;
   if (threads < 128) threads = 128;
   if (threads > 1024) threads = 1024;
-  if (smem + 2048 > 48 * 1024)  // the 48 KB default limit counts the static part (~1.3 KB) too; per device, set per launch
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(nms_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&nms_batched_kernel), smem)) return rc;
   nms_batched_kernel<<<n_images, threads, smem, (cudaStream_t)stream>>>(p);
   CVPCE_LAUNCH_OK("nms_batched_kernel");
   return CVPCE_OK;

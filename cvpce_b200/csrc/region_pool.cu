@@ -782,7 +782,8 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
                     : (general ? region_pool_kernel<CVPCE_BF16, true, false> : region_pool_kernel<CVPCE_BF16, false, false>);
   }
   // the default 48 KB limit covers static + dynamic shared memory: opt in with a margin for the static part
-  if (smem_launch > 40 * 1024) CVPCE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_launch));
+  if (smem_launch > 40 * 1024)
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem_launch)) return rc;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(B * cluster_size));
   cfg.blockDim = dim3(kPoolThreads);

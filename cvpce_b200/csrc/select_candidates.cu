@@ -454,8 +454,7 @@ extern "C" int cvpce_select_candidates(const cvpce_fpn_level* levels, int n_leve
   p.seg_counts = seg_counts;
   p.level_counts = level_counts;
 
-  // per-device attribute: set on every launch (a cached flag would be stale after cudaSetDevice to a second GPU)
-  CVPCE_CUDA_OK(cudaFuncSetAttribute(select_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSelDynSmem));
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&select_candidates_kernel), kSelDynSmem)) return rc;
   // one CTA per level; if this device refuses a cluster of exactly n_levels CTAs, pad to the next power of two (the
   // padding CTAs only take part in the count exchange)
   // cached per (thread, device): 0 unknown, 1 yes, -1 no

@@ -297,8 +297,8 @@ extern "C" int cvpce_sim_topk_f32(const float* q, const float* g, int Q, int G, 
   const size_t smem = (size_t)F_BM * k * 8;
   const int grid = (Q + F_BM - 1) / F_BM;
   if (smem > 16 * 1024) {
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(sim_topk_f32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(sim_topk_f32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&sim_topk_f32_kernel<true>), 64 * 1024)) return rc;
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&sim_topk_f32_kernel<false>), 64 * 1024)) return rc;
   }
   if (normalize)
     sim_topk_f32_kernel<true><<<grid, F_THREADS, smem, (cudaStream_t)stream>>>(q, g, Q, G, D, k, idx_base, eps, out_scores,
@@ -323,7 +323,7 @@ extern "C" int cvpce_topk_merge(const float* scores, const int64_t* idx, int W, 
   int grid = (Q + warps - 1) / warps;
   if (grid > 148 * 16) grid = 148 * 16;
   if (smem > 48 * 1024)
-    CVPCE_CUDA_OK(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&topk_merge_kernel), smem)) return rc;
   topk_merge_kernel<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(scores, reinterpret_cast<const long long*>(idx), W, Q, k,
                                                                       out_scores, reinterpret_cast<long long*>(out_idx));
   CVPCE_LAUNCH_OK("topk_merge_kernel");

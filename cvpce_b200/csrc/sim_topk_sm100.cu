@@ -15,9 +15,8 @@
 //   grid = (query blocks of 128) x (gallery splits); each CTA writes its k' candidates per row to a small workspace.
 // Kernel 2  sim_select_kernel    (one warp per query row)
 //   merges the splits' candidate lists by rank (every candidate finds its overall rank with binary searches in the other
-//   sorted lists), re-scores the survivors in exact fp32 from the fp32 operands (parity mode) -- in approximate order, stopping
-//   as soon as the bf16 error bound proves that no remaining candidate can enter the top-k -- and writes the final top-k
-//   ordered by (similarity desc, gallery index asc).
+//   sorted lists), re-scores in exact fp32, from the fp32 operands (parity mode), the prefix of the survivors that the bf16
+//   error bound cannot exclude from the top-k, and writes the final top-k ordered by (similarity desc, gallery index asc).
 //
 // Round-2 measurements that shaped this file (profiles/r2*_kbench_sim_*.jsonl, r2p_sim_launches_ncu_*.csv):
 //   the MMA + TMA pipeline alone sustains 0.86-0.93 of the measured cuBLAS burst rate; what costs the rest is the epilogue's
@@ -546,59 +545,41 @@ __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float*
   }
   // ---- stage 2: exact fp32 re-score (one candidate at a time, the lanes split D: a (query, gallery row) score does not depend
   //      on which other candidates the row has, so the single-GPU and the sharded search agree bit for bit).
-  //      Lane j holds the candidate of approximate rank j.  The candidates are re-scored in approximate order, four at a time,
-  //      and the walk STOPS as soon as the result is certain: with eps an upper bound of |approximate - exact| (unit rows in
-  //      bf16: <= 2^-8 * sum|q_i g_i| <= 2^-8, plus the fp32 accumulation of D products), every candidate that has not been
-  //      re-scored -- and every gallery row that never made the list -- has an exact score <= (approximate score of the next
-  //      candidate) + eps; once that is below the k-th best exact score found so far, none of them can enter the top-k.
-  //      Sparse score distributions (the 1M-row gallery) stop after about half of the k' candidates; dense ones re-score all.
+  //      Lane j holds the candidate of approximate rank j.  Only a PREFIX of them can matter: with eps an upper bound of
+  //      |approximate - exact| (unit rows in bf16: <= 2^-8 * sum|q_i g_i| <= 2^-8, plus the fp32 accumulation of D products),
+  //      the k best approximate candidates all have exact scores >= a_k - eps (a_k = k-th approximate score), while a candidate
+  //      -- or a gallery row that never made the list -- with approximate score < a_k - 2 eps has an exact score < a_k - eps:
+  //      it cannot enter the top-k and is not re-scored.  Sparse score distributions (the 1M-row gallery) re-score ~10 of the
+  //      16 candidates; dense ones (8k rows, scores within 0.01 of each other) all of them, at no extra cost in the loop
+  //      (an a-posteriori test after every few candidates was measured 20 % slower there: it breaks up the load pipeline).
   if (q32 != nullptr) {
     const float* qr = q32 + (size_t)row * D;
     const float qi = q_inv ? q_inv[row] : 1.f;
     const float eps_bound = 0.00390625f * (1.f + 0.0009765625f) + (float)D * 1.1920929e-7f;
-    const float approx = my_s;  // kernel-1 score of this lane's candidate
-    int done = 0;
-    for (int c0 = 0; c0 < KP; c0 += 4) {
-      for (int c = c0; c < c0 + 4; ++c) {
-        const int gi = __shfl_sync(0xffffffffu, my_i, c);
-        if (gi < 0) continue;  // warp-uniform
-        const float* gr = g32 + (size_t)gi * D;
-        float acc = 0.f;
-        if ((D & 3) == 0) {
-          for (int d = lane * 4; d < D; d += 128) {
-            const float4 a = *reinterpret_cast<const float4*>(qr + d);
-            const float4 b = __ldg(reinterpret_cast<const float4*>(gr + d));
-            acc = fmaf(a.x, b.x, acc);
-            acc = fmaf(a.y, b.y, acc);
-            acc = fmaf(a.z, b.z, acc);
-            acc = fmaf(a.w, b.w, acc);
-          }
-        } else {
-          for (int d = lane; d < D; d += 32) acc = fmaf(qr[d], __ldg(gr + d), acc);
+    const float a_k = __shfl_sync(0xffffffffu, my_s, k - 1);  // -inf when the row has fewer than k candidates: everything stays
+    const bool keep = lane < KP && my_i >= 0 && (lane < k || !(my_s < a_k - 2.f * eps_bound));
+    const int n_rescore = __popc(__ballot_sync(0xffffffffu, keep));  // a prefix: the lanes are sorted by approximate score
+    if (!keep) my_i = -1;
+    for (int c = 0; c < n_rescore; ++c) {
+      const int gi = __shfl_sync(0xffffffffu, my_i, c);
+      const float* gr = g32 + (size_t)gi * D;
+      float acc = 0.f;
+      if ((D & 3) == 0) {
+        for (int d = lane * 4; d < D; d += 128) {
+          const float4 a = *reinterpret_cast<const float4*>(qr + d);
+          const float4 b = __ldg(reinterpret_cast<const float4*>(gr + d));
+          acc = fmaf(a.x, b.x, acc);
+          acc = fmaf(a.y, b.y, acc);
+          acc = fmaf(a.z, b.z, acc);
+          acc = fmaf(a.w, b.w, acc);
         }
-        acc = warp_sum(acc);
-        const float sc = acc * qi * (g_inv ? g_inv[gi] : 1.f);
-        if (lane == c) my_s = sc;
+      } else {
+        for (int d = lane; d < D; d += 32) acc = fmaf(qr[d], __ldg(gr + d), acc);
       }
-      done = c0 + 4;
-      if (done >= KP || done < k) continue;
-      // k-th best exact score among the re-scored candidates (lanes < done), and the best approximate score still pending
-      int better = 0;
-      for (int c = 0; c < done; ++c) {
-        const float os = __shfl_sync(0xffffffffu, my_s, c);
-        const int oi = __shfl_sync(0xffffffffu, my_i, c);
-        if (c != lane && before(os, oi, my_s, my_i)) ++better;
-      }
-      const unsigned kth_lane = __ballot_sync(0xffffffffu, lane < done && my_i >= 0 && better == k - 1);
-      const float next_approx = __shfl_sync(0xffffffffu, approx, done);
-      const int next_idx = __shfl_sync(0xffffffffu, my_i, done);
-      if (next_idx < 0) break;  // nothing pending
-      if (kth_lane) {
-        const float kth = __shfl_sync(0xffffffffu, my_s, __ffs(kth_lane) - 1);
-        if (next_approx + eps_bound < kth) break;  // warp-uniform: certified
-      }
+      acc = warp_sum(acc);
+      const float sc = acc * qi * (g_inv ? g_inv[gi] : 1.f);
+      if (lane == c) my_s = sc;
     }
-    if (lane >= done) my_i = -1;  // not re-scored: certainly outside the top-k
   }
   // ---- stage 3: final rank among the KP survivors by (score desc, index asc)
   int rank = 0;
