@@ -574,6 +574,157 @@ __global__ void __launch_bounds__(kPoolThreads, CVPCE_MAC_MIN_CTAS) mac_nhwc_pix
   cluster.sync();  // peers may still be reading pmax / fpart
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// MAC over dense channels-last maps, balanced streaming form (used when the caller provides a workspace).
+// The cluster kernel above gives every image its own cluster: B = 256 images are 512 CTAs on 148 SMs -- 3.46 per SM, the
+// slowest SM carries 4 -- and every cluster ends in two cluster barriers.  Here the whole batch is one linear space of
+// CHUNKS (16 KB runs of whole pixels of one map of one image, images outermost) cut into gridDim.x equal contiguous ranges,
+// gridDim.x = a multiple of the SM count: every CTA streams the same number of bytes whatever B is.  A CTA's range crosses
+// at most a few (image, map) boundaries; for each piece (a SEGMENT) it writes its per-channel maxima to a workspace row, and
+// the CTA that completes an image's LAST segment (a counter per image, release / acquire through __threadfence) reduces
+// that image's rows from L2, takes the L2 norm and writes the descriptor.  No CTA ever waits for another one.
+// The counters are left at zero, so a workspace zeroed once can be reused by every later launch on the same stream.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kMacChunkVecs = 1024;  // 16-byte vectors per chunk (a multiple of the block size: a thread keeps its channel group)
+
+struct MacStreamPlan {
+  long long total_chunks;                  // B * chunks_per_image
+  int chunks_per_image;
+  int chunk_pix[CVPCE_POOL_MAX_MAPS];      // pixels per chunk
+  int chunks[CVPCE_POOL_MAX_MAPS];         // chunks per (image, map)
+  int slots[CVPCE_POOL_MAX_MAPS];          // workspace rows per (image, map): an upper bound of its segment count
+  int slot_offset[CVPCE_POOL_MAX_MAPS];    // float offset of a map's rows inside an image's block
+  long long image_stride;                  // floats per image in the workspace
+  unsigned* counters;                      // [B], zero between launches
+  float* partial;                          // [B][image_stride]
+};
+
+// the CTA whose range [c*T/G, (c+1)*T/G) holds chunk x
+__device__ __forceinline__ long long mac_owner(long long x, long long G, long long T) { return ((x + 1) * G - 1) / T; }
+
+#ifndef CVPCE_MAC_STREAM_MIN_CTAS
+#define CVPCE_MAC_STREAM_MIN_CTAS 4
+#endif
+template <int DT>
+__global__ void __launch_bounds__(kPoolThreads, CVPCE_MAC_STREAM_MIN_CTAS) mac_nhwc_stream_kernel(const __grid_constant__ PoolParams p, const __grid_constant__ MacStreamPlan w) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr bool BF16 = DT != CVPCE_F32;
+  constexpr int E = BF16 ? 8 : 4;
+  __shared__ float red[kPoolThreads * E];
+  __shared__ float own[kMacMaxCols];
+  __shared__ float wsum[kPoolWarps];
+  __shared__ int s_last;
+  const long long G = gridDim.x, T = w.total_chunks;
+  long long x = (long long)blockIdx.x * T / G;
+  const long long x_end = ((long long)blockIdx.x + 1) * T / G;
+  while (x < x_end) {
+    const int n = (int)(x / w.chunks_per_image);
+    int j = (int)(x - (long long)n * w.chunks_per_image);
+    int m = 0;
+    while (j >= w.chunks[m]) j -= w.chunks[m++];
+    const PoolMap& mp = p.maps[m];
+    const int j_end = (int)min((long long)w.chunks[m], (long long)j + (x_end - x));
+    const long long map_first = x - j;  // chunk index of this (image, map)'s first chunk
+    const int V = mp.C / E;
+    const int npix = mp.H * mp.W;
+    const int lo = j * w.chunk_pix[m], hi = min(npix, j_end * w.chunk_pix[m]);
+    const uint4* base = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(mp.data) + (size_t)n * mp.sn * (BF16 ? 2 : 4)) + (size_t)lo * V;
+    const int total = (hi - lo) * V;
+    float acc[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) acc[e] = -INFINITY;
+    CVPCE_UNROLL(CVPCE_MAC_UNROLL)
+    for (int i = tid; i < total; i += kPoolThreads) {
+      const uint4 v = ldg_stream_u4(base + i);
+      if (DT == CVPCE_F16) {
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+        const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&v.z)), d = __half22float2(*reinterpret_cast<const __half2*>(&v.w));
+        acc[0] = fmaxf(acc[0], a.x); acc[1] = fmaxf(acc[1], a.y);
+        acc[2] = fmaxf(acc[2], b.x); acc[3] = fmaxf(acc[3], b.y);
+        acc[4 % E] = fmaxf(acc[4 % E], c.x); acc[5 % E] = fmaxf(acc[5 % E], c.y);
+        acc[6 % E] = fmaxf(acc[6 % E], d.x); acc[7 % E] = fmaxf(acc[7 % E], d.y);
+      } else if (BF16) {
+        acc[0] = fmaxf(acc[0], bf16lo(v.x)); acc[1] = fmaxf(acc[1], bf16hi(v.x));
+        acc[2] = fmaxf(acc[2], bf16lo(v.y)); acc[3] = fmaxf(acc[3], bf16hi(v.y));
+        acc[4 % E] = fmaxf(acc[4 % E], bf16lo(v.z)); acc[5 % E] = fmaxf(acc[5 % E], bf16hi(v.z));
+        acc[6 % E] = fmaxf(acc[6 % E], bf16lo(v.w)); acc[7 % E] = fmaxf(acc[7 % E], bf16hi(v.w));
+      } else {
+        acc[0] = fmaxf(acc[0], __uint_as_float(v.x)); acc[1] = fmaxf(acc[1], __uint_as_float(v.y));
+        acc[2] = fmaxf(acc[2], __uint_as_float(v.z)); acc[3] = fmaxf(acc[3], __uint_as_float(v.w));
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) red[tid * E + e] = acc[e];
+    __syncthreads();
+    // segment row of this CTA = its ordinal among the CTAs that touch this (image, map)
+    const int slot = (int)((long long)blockIdx.x - mac_owner(map_first, G, T));
+    if (tid < V) {  // threads tid, tid+V, .. saw the same channel group (segments start at multiples of the block size)
+      for (int g = tid + V; g < kPoolThreads; g += V) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] = fmaxf(acc[e], red[g * E + e]);
+      }
+      float* row = w.partial + (long long)n * w.image_stride + w.slot_offset[m] + (long long)slot * mp.C + tid * E;
+#pragma unroll
+      for (int e = 0; e < E; e += 4) __stcg(reinterpret_cast<float4*>(row + e), make_float4(acc[e], acc[e + 1], acc[e + 2], acc[e + 3]));
+      __threadfence();  // release: the row is visible device-wide before the counter moves
+    }
+    __syncthreads();
+    x += j_end - j;
+    if (tid == 0) {
+      // segments of image n, from the same arithmetic every CTA uses
+      unsigned expect = 0;
+      long long first = (long long)n * w.chunks_per_image;
+      for (int q = 0; q < p.n_maps; ++q) {
+        expect += (unsigned)(mac_owner(first + w.chunks[q] - 1, G, T) - mac_owner(first, G, T) + 1);
+        first += w.chunks[q];
+      }
+      const unsigned prev = atomicAdd(&w.counters[n], 1u);
+      s_last = prev + 1 == expect;
+      if (s_last) {
+        w.counters[n] = 0;  // nobody else touches this counter any more in this launch: leave it clean for the next one
+        __threadfence();    // acquire: the other CTAs' rows, released before their increments, are visible below
+      }
+    }
+    __syncthreads();
+    if (s_last) {
+      // ---- finish image n: maxima over its segments, L2 norm over all channels, store --------------------------------------
+      float sq = 0.f;
+      int col = 0;
+      long long first = (long long)n * w.chunks_per_image;
+      for (int q = 0; q < p.n_maps; ++q) {
+        const PoolMap& mq = p.maps[q];
+        const int nseg = (int)(mac_owner(first + w.chunks[q] - 1, G, T) - mac_owner(first, G, T) + 1);
+        const float* rows = w.partial + (long long)n * w.image_stride + w.slot_offset[q];
+        for (int c = tid; c < mq.C; c += kPoolThreads) {
+          float v = -INFINITY;
+          for (int sg = 0; sg < nseg; ++sg) v = fmaxf(v, __ldcg(rows + (long long)sg * mq.C + c));
+          own[col + c] = v;
+          sq = fmaf(v, v, sq);
+        }
+        col += mq.C;
+        first += w.chunks[q];
+      }
+      float denom = 1.f;
+      if (p.final_l2) {
+        sq = warp_sum(sq);
+        if (lane == 0) wsum[warp] = sq;
+        __syncthreads();
+        float t = 0.f;
+        for (int k = 0; k < kPoolWarps; ++k) t += wsum[k];
+        denom = fmaxf(sqrtf(t), p.eps);
+      }
+      col = 0;
+      for (int q = 0; q < p.n_maps; ++q) {
+        const PoolMap& mq = p.maps[q];
+        float* orow = p.out + (long long)n * p.out_stride + mq.out_offset;
+        for (int c = tid; c < mq.C; c += kPoolThreads) orow[c] = p.final_l2 ? own[col + c] / denom : own[col + c];
+        col += mq.C;
+      }
+      __syncthreads();  // own / wsum / s_last are reused by the next segment
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) l2norm_rows_kernel(float* x, int B, int D, long long stride, float eps) {
   __shared__ float wsum[8];
   __shared__ float s_denom;
@@ -653,9 +804,67 @@ static int seg_index(const unsigned char* b, int ns, int v) {
 }
 }  // namespace cvpce
 
-extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
-                                       const int32_t* regions, const int32_t* n_regions, int per_region_l2,
-                                       int final_l2, float eps, float* out, int64_t out_stride, void* stream) {
+namespace cvpce {
+
+// Whether the dense channels-last MAC kernels apply to these maps (whole-map regions and no per-region L2 are checked by the caller).
+static bool mac_dense_nhwc(const cvpce_feature_map* maps, int n_maps, int dtype) {
+  const int E = dtype == CVPCE_F32 ? 4 : 8;
+  int col = 0;
+  for (int m = 0; m < n_maps; ++m) {
+    const cvpce_feature_map& fm = maps[m];
+    if (!fm.data || fm.C <= 0 || fm.H <= 0 || fm.W <= 0) return false;
+    const int V = fm.C / E;
+    if (!(fm.C % E == 0 && V >= 1 && V <= kPoolThreads && kPoolThreads % V == 0 && fm.stride_c == 1 && fm.stride_w == fm.C &&
+          fm.stride_h == (int64_t)fm.W * fm.C && fm.stride_n % E == 0 && (reinterpret_cast<uintptr_t>(fm.data) & 15u) == 0))
+      return false;
+    col += fm.C;
+  }
+  return col <= kMacMaxCols;
+}
+
+// Chunking of the batch for mac_nhwc_stream_kernel and the workspace it needs; returns the grid size.
+static int mac_stream_plan(const cvpce_feature_map* maps, int n_maps, int dtype, int B, MacStreamPlan* w, size_t* counter_bytes, size_t* total_bytes) {
+  const int E = dtype == CVPCE_F32 ? 4 : 8;
+  int cpi = 0;
+  for (int m = 0; m < n_maps; ++m) {
+    const int V = maps[m].C / E;
+    w->chunk_pix[m] = kMacChunkVecs / V;
+    w->chunks[m] = (maps[m].H * maps[m].W + w->chunk_pix[m] - 1) / w->chunk_pix[m];
+    cpi += w->chunks[m];
+  }
+  w->chunks_per_image = cpi;
+  w->total_chunks = (long long)B * cpi;
+  const int per_sm = tuning("mac_ctas_per_sm") > 0 ? tuning("mac_ctas_per_sm") : 2;  // measured (tools/mac_ab.py, same box): 2 beats 1, 3, 4, 6
+  const long long G = std::max(1ll, std::min<long long>((long long)sm_count() * per_sm, w->total_chunks));
+  long long off = 0;
+  for (int m = 0; m < n_maps; ++m) {
+    const long long bound = ((long long)w->chunks[m] * G + w->total_chunks - 1) / w->total_chunks + 1;
+    w->slots[m] = (int)std::min<long long>(w->chunks[m], bound);
+    w->slot_offset[m] = (int)off;
+    off += (long long)w->slots[m] * maps[m].C;
+  }
+  w->image_stride = off;
+  // a fixed-size counter block for every realistic batch, so that one zeroed workspace serves launches of different B
+  *counter_bytes = std::max<size_t>(65536, (((size_t)B * sizeof(unsigned)) + 255) & ~(size_t)255);
+  *total_bytes = *counter_bytes + (size_t)B * (size_t)off * sizeof(float);
+  return (int)G;
+}
+
+}  // namespace cvpce
+
+extern "C" int64_t cvpce_region_pool_workspace_bytes(const cvpce_feature_map* maps, int n_maps, int dtype, int B) {
+  using namespace cvpce;
+  if (!maps || n_maps < 1 || n_maps > CVPCE_POOL_MAX_MAPS || B <= 0) return 0;
+  if (!(dtype == CVPCE_F32 || dtype == CVPCE_BF16 || dtype == CVPCE_F16) || !mac_dense_nhwc(maps, n_maps, dtype)) return 0;
+  MacStreamPlan w;
+  size_t cb = 0, tb = 0;
+  mac_stream_plan(maps, n_maps, dtype, B, &w, &cb, &tb);
+  return (int64_t)tb;
+}
+
+static int region_pool_impl(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                            const int32_t* regions, const int32_t* n_regions, int per_region_l2,
+                            int final_l2, float eps, float* out, int64_t out_stride, void* workspace, size_t workspace_bytes, void* stream) {
   using namespace cvpce;
   CVPCE_REQUIRE(maps && n_maps >= 1 && n_maps <= CVPCE_POOL_MAX_MAPS, CVPCE_ERR_INVALID_ARG, "region_pool: n_maps=%d out of [1,%d]", n_maps, CVPCE_POOL_MAX_MAPS);
   CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16 || dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG, "region_pool: bad dtype %d", dtype);
@@ -750,6 +959,21 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
                fm.stride_h == (int64_t)fm.W * fm.C && fm.stride_n % E == 0 && (reinterpret_cast<uintptr_t>(fm.data) & 15u) == 0 &&
                p.maps[m].slab * kPoolCluster == fm.C;
   }
+  if (pixsplit && workspace && tuning("mac_kernel") != 1) {
+    // balanced streaming kernel (needs the caller's workspace; its counters are zero on entry and on exit)
+    MacStreamPlan w;
+    size_t cb = 0, tb = 0;
+    const int G = mac_stream_plan(maps, n_maps, dtype, B, &w, &cb, &tb);
+    CVPCE_REQUIRE(workspace_bytes >= tb, CVPCE_ERR_INVALID_ARG, "region_pool: workspace of %zu bytes, %zu needed (cvpce_region_pool_workspace_bytes)", workspace_bytes, tb);
+    CVPCE_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, CVPCE_ERR_INVALID_ARG, "region_pool: workspace must be 256-byte aligned");
+    w.counters = reinterpret_cast<unsigned*>(workspace);
+    w.partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + cb);
+    auto sk = dtype == CVPCE_F32 ? mac_nhwc_stream_kernel<CVPCE_F32>
+                                 : (dtype == CVPCE_BF16 ? mac_nhwc_stream_kernel<CVPCE_BF16> : mac_nhwc_stream_kernel<CVPCE_F16>);
+    sk<<<G, kPoolThreads, 0, (cudaStream_t)stream>>>(p, w);
+    CVPCE_CUDA_OK(cudaGetLastError());
+    return CVPCE_OK;
+  }
   void (*kern)(PoolParams);
   size_t smem_launch = smem;
   int cluster_size = kPoolCluster;
@@ -798,6 +1022,20 @@ extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps
   cfg.numAttrs = 1;
   CVPCE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p));
   return CVPCE_OK;
+}
+
+extern "C" int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                                       const int32_t* regions, const int32_t* n_regions, int per_region_l2,
+                                       int final_l2, float eps, float* out, int64_t out_stride, void* stream) {
+  return region_pool_impl(maps, n_maps, dtype, B, regions, n_regions, per_region_l2, final_l2, eps, out, out_stride, nullptr, 0, stream);
+}
+
+extern "C" int cvpce_region_pool_embed_ws(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                                          const int32_t* regions, const int32_t* n_regions, int per_region_l2,
+                                          int final_l2, float eps, float* out, int64_t out_stride,
+                                          void* workspace, int64_t workspace_bytes, void* stream) {
+  return region_pool_impl(maps, n_maps, dtype, B, regions, n_regions, per_region_l2, final_l2, eps, out, out_stride, workspace,
+                          workspace_bytes > 0 ? (size_t)workspace_bytes : 0, stream);
 }
 
 extern "C" int cvpce_l2norm_rows(float* x, int B, int D, int64_t stride, float eps, void* stream) {

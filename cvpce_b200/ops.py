@@ -337,9 +337,22 @@ def rmac_regions(H, W, levels):
     return [tuple(buf[4 * i: 4 * i + 4]) for i in range(min(n, 64))]
 
 
+_POOL_WS = {}  # (device index, stream handle) -> zero-initialised workspace of the balanced MAC kernel (its counters stay zero between launches)
+
+
+def _pool_workspace(device, stream, need):
+    key = (device.index, stream.value or 0)
+    ws = _POOL_WS.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros((max(need, 1 << 20),), dtype=torch.uint8, device=device)
+        _POOL_WS[key] = ws
+    return ws
+
+
 def region_pool_embed(feats, regions=None, per_region_l2=False, final_l2=True, eps=1e-8, out=None):
     """feats: list of CUDA [B,C,H,W] maps (f32 or bf16, any strides) -> f32[B, sum C].
-    regions: None (MAC: whole map) or a list (per map) of lists of (y0,x0,y1,x1)."""
+    regions: None (MAC: whole map) or a list (per map) of lists of (y0,x0,y1,x1).
+    Dense channels-last MAC batches take the balanced streaming kernel through a cached per-(device, stream) workspace."""
     _need_cuda("region_pool_embed", *feats)
     B = feats[0].shape[0]
     dtype = feats[0].dtype
@@ -356,11 +369,18 @@ def region_pool_embed(feats, regions=None, per_region_l2=False, final_l2=True, e
         flat = [int(v) for per_map in regions for r in per_map for v in r]
         rg = (ctypes.c_int32 * len(flat))(*flat)
         nr = (ctypes.c_int32 * len(regions))(*[len(r) for r in regions])
-    rc = _lib.load().cvpce_region_pool_embed(maps, len(feats), _DTYPE_CODE[dtype], B,
-                                             ctypes.cast(rg, ctypes.c_void_p) if rg is not None else None,
-                                             ctypes.cast(nr, ctypes.c_void_p) if nr is not None else None,
-                                             1 if per_region_l2 else 0, 1 if final_l2 else 0, float(eps), _ptr(out),
-                                             out.stride(0), _stream())
+    lib = _lib.load()
+    stream = _stream()
+    ws, ws_bytes = None, 0
+    if regions is None and not per_region_l2 and B > 0:
+        ws_bytes = int(lib.cvpce_region_pool_workspace_bytes(maps, len(feats), _DTYPE_CODE[dtype], B))
+        if ws_bytes > 0:
+            ws = _pool_workspace(feats[0].device, stream, ws_bytes)
+    rc = lib.cvpce_region_pool_embed_ws(maps, len(feats), _DTYPE_CODE[dtype], B,
+                                        ctypes.cast(rg, ctypes.c_void_p) if rg is not None else None,
+                                        ctypes.cast(nr, ctypes.c_void_p) if nr is not None else None,
+                                        1 if per_region_l2 else 0, 1 if final_l2 else 0, float(eps), _ptr(out),
+                                        out.stride(0), _ptr(ws) if ws is not None else None, ws_bytes, stream)
     _lib.check(rc, "cvpce_region_pool_embed")
     return out
 

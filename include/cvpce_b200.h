@@ -184,6 +184,22 @@ CVPCE_API int cvpce_region_pool_embed(const cvpce_feature_map* maps, int n_maps,
                             const int32_t* regions, const int32_t* n_regions,
                             int per_region_l2, int final_l2, float eps,
                             float* out, int64_t out_stride, void* stream);
+/* Same operation with a caller-owned device workspace.  With a workspace, dense channels-last MAC batches (whole-map
+ * regions, no per-region L2 -- the reference's mode behind the fast trunk) run the balanced streaming kernel: the batch is
+ * cut into equal contiguous byte ranges over a grid that is a multiple of the SM count, instead of one cluster per image.
+ * workspace [device] >= cvpce_region_pool_workspace_bytes(...) bytes, 256-byte aligned.  Its first
+ *      max(65536, (4*B + 255) & ~255) bytes are per-image counters: they must be ZERO at the first launch and every
+ *      launch leaves them zero, so a buffer zeroed once can be reused by all later launches (of any B <= 16384) ordered
+ *      on the same stream -- not by concurrent launches on other streams.  The rest needs no initialisation.
+ * workspace null, or a case the streaming kernel does not cover (cvpce_region_pool_workspace_bytes returns 0):
+ *      identical to cvpce_region_pool_embed.  Results are the same in both forms (maxima exact; the L2 norm sums the
+ *      squares in a fixed channel order in each form). */
+CVPCE_API int64_t cvpce_region_pool_workspace_bytes(const cvpce_feature_map* maps, int n_maps, int dtype, int B);
+CVPCE_API int cvpce_region_pool_embed_ws(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                               const int32_t* regions, const int32_t* n_regions,
+                               int per_region_l2, int final_l2, float eps,
+                               float* out, int64_t out_stride,
+                               void* workspace, int64_t workspace_bytes, void* stream);
 /* [host] R-MAC region grid of Tolias et al. for an H x W map and `levels` scales; returns the region count and
  * writes up to max_regions (y0,x0,y1,x1) quadruples. */
 CVPCE_API int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, int max_regions);

@@ -666,6 +666,40 @@ def test_mac_channels_last_pixel_split_kernel(ops, shapes):
         np.testing.assert_allclose(ops.region_pool_embed(bf, final_l2=final).cpu().numpy(), want_bf, rtol=2e-6, atol=1e-7)
 
 
+@pytest.mark.parametrize("B", [1, 3, 37, 256, 300])
+def test_mac_balanced_streaming_kernel_equals_cluster_kernel(ops, B):
+    """The balanced streaming MAC kernel (workspace form, default behind ops.region_pool_embed) against the per-image cluster
+    kernel and the oracle: maxima bit-equal, descriptors within rounding of the norm; the workspace counters are left clean
+    (a second and third launch on the same workspace give the same bits); ragged pixel counts; tiny grids (B = 1: fewer chunks
+    than CTAs) and batches whose images straddle CTA ranges."""
+    from cvpce_b200 import _lib
+    rs = np.random.RandomState(B)
+    shapes = [(512, 16, 16), (512, 16, 16)] if B >= 256 else [(512, 9, 7), (256, 5, 3), (1024, 2, 2)]
+    feats = [rs.randn(B, c, h, w).astype(np.float32) for c, h, w in shapes]
+    dv = [dev(f).contiguous(memory_format=torch.channels_last) for f in feats]
+    for final in (False, True):
+        with _lib.tuning(mac_kernel=1):
+            want = ops.region_pool_embed(dv, final_l2=final)
+        got = [ops.region_pool_embed(dv, final_l2=final) for _ in range(3)]
+        assert torch.equal(got[0], got[1]) and torch.equal(got[0], got[2])
+        if final:
+            np.testing.assert_allclose(got[0].cpu().numpy(), want.cpu().numpy(), rtol=2e-6, atol=1e-7)
+        else:
+            assert torch.equal(got[0], want)
+            if B <= 37:
+                assert np.array_equal(got[0].cpu().numpy(), oracle.region_pool_embed(feats, final_l2=False))
+    raw = ops.region_pool_embed(dv, final_l2=False)
+    for per_sm in (1, 7):                                             # other grid sizes: other segmentations, same answer
+        with _lib.tuning(mac_ctas_per_sm=per_sm):
+            assert torch.equal(ops.region_pool_embed(dv, final_l2=False), raw)
+    hf = [d.half() for d in dv]
+    with _lib.tuning(mac_kernel=1):
+        want_h = ops.region_pool_embed(hf)
+    np.testing.assert_allclose(ops.region_pool_embed(hf).cpu().numpy(), want_h.cpu().numpy(), rtol=2e-6, atol=1e-7)
+    from cvpce_b200 import ops as _ops
+    assert all(int(w[:65536].view(torch.int32).abs().sum()) == 0 for w in _ops._POOL_WS.values())
+
+
 def test_mac_of_pooled_relu4_3_is_bit_identical(ops):
     """MACVGG.features(pooled_f4=True): max over pool4(relu4_3) == max over relu4_3 when the map has even sides."""
     from cvpce_b200 import classification

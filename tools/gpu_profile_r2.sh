@@ -11,7 +11,7 @@ $PROF > $OUT/plain_prof.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 9000 --csv --log-file $OUT/launches.csv $PROF > $OUT/ncu_launch.log 2>&1
 echo "ncu launches exit $?"
 $PROF > $OUT/plain_prof2.log 2>&1 &&
-ncu --set full --clock-control none -k 'regex:nms_batched_kernel|crop_resize_col_kernel|mac_nhwc_pixelsplit_kernel|rows_prepare_kernel|sim_topk_tc_kernel|sim_select_kernel' -c 16 -o $OUT/prof_own $PROF > $OUT/ncu_full.log 2>&1
+ncu --set full --clock-control none -k 'regex:nms_batched_kernel|crop_resize_col_kernel|mac_nhwc_pixelsplit_kernel|mac_nhwc_stream_kernel|rows_prepare_kernel|sim_topk_tc_kernel|sim_select_kernel' -c 16 -o $OUT/prof_own $PROF > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 $PROF > $OUT/plain_prof3.log 2>&1 &&
 ncu --set full --clock-control none -k 'regex:maxpool2x2_nhwc_kernel' -c 8 -o $OUT/prof_maxpool $PROF > $OUT/ncu_full_maxpool.log 2>&1

@@ -74,7 +74,7 @@ def full(path):
     print("\n# launches captured per kernel: " + ", ".join("%s x%d" % kv for kv in seen.items()))
 
 
-STAGE_OF = {"region_pool_kernel": "region_pool_embed", "mac_nhwc_pixelsplit_kernel": "region_pool_embed", "maxpool2x2_nhwc_kernel": "maxpool2x2", "crop_resize_sep_kernel": "crop_resize", "crop_resize_col_kernel": "crop_resize", "crop_resize_kernel": "crop_resize",
+STAGE_OF = {"region_pool_kernel": "region_pool_embed", "mac_nhwc_pixelsplit_kernel": "region_pool_embed", "mac_nhwc_stream_kernel": "region_pool_embed", "maxpool2x2_nhwc_kernel": "maxpool2x2", "crop_resize_sep_kernel": "crop_resize", "crop_resize_col_kernel": "crop_resize", "crop_resize_kernel": "crop_resize",
             "nms_batched_kernel": "nms", "select_candidates_kernel": "select_candidates", "rows_prepare_kernel": "rows_prepare",
             "sim_topk_tc_kernel": "sim_topk"}
 
