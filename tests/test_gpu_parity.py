@@ -375,6 +375,32 @@ def test_sim_topk_tensor_core_vs_oracle(ops, Q, G, D, k):
     np.testing.assert_allclose(simb[:, 0].cpu().numpy(), osim[:, 0], rtol=0, atol=2e-3)
 
 
+@pytest.mark.parametrize("Q,G,D,k", [(1300, 5000, 1024, 5), (2000, 3000, 512, 5), (700, 20000, 64, 1), (1500, 6000, 256, 20)])
+def test_sim_topk_gallery_split_counts_agree(ops, Q, G, D, k):
+    """The tcgen05 search gives the same bits whatever the number of gallery splits (candidate lists per row) the plan or a
+    tuning override selects; exact mode also equals the fp32 CUDA-core kernel."""
+    from cvpce_b200 import _lib
+    rs = np.random.RandomState(Q + G + D)
+    g = synth.unit_rows(rs, G, D, nonneg=(D == 1024))
+    q, _ = synth.planted_queries(rs, g, Q, frac=0.3)
+    gq, gg = dev(q), dev(g)
+    qb, qinv = ops.rows_prepare(gq)
+    gb, ginv = ops.rows_prepare(gg)
+    ref = None
+    for split in (0, 1, 2, 3, 7):
+        with _lib.tuning(sim_split=split):
+            exact = ops.sim_topk(qb, gb, k, 7, gq, gg, qinv, ginv)
+            approx = ops.sim_topk(qb, gb, k, 7)
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = (exact, approx)
+            s32, i32 = ops.sim_topk_f32(gq, gg, k, idx_base=7)
+            assert (i32 == exact[1]).float().mean().item() > 0.999
+        else:
+            assert torch.equal(exact[0], ref[0][0]) and torch.equal(exact[1], ref[0][1]), split
+            assert torch.equal(approx[0], ref[1][0]) and torch.equal(approx[1], ref[1][1]), split
+
+
 def test_sim_topk_shard_offsets_and_merge(ops):
     rs = np.random.RandomState(8)
     G, D, Q, k, W = 4096, 512, 200, 5, 4

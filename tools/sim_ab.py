@@ -3,7 +3,10 @@ CVPCE_B200_SO selects the library build."""
 import os, sys, json
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from cvpce_b200 import ops
+from cvpce_b200 import ops, _lib
+tune = sys.argv[sys.argv.index("--tune") + 1:] if "--tune" in sys.argv else []
+for t in tune:
+    _lib.tuning_set(t.split("=")[0], int(t.split("=")[1]))
 dev = torch.device("cuda", 0)
 gen = torch.Generator(device=dev).manual_seed(3)
 g = torch.randn((8192, 1024), generator=gen, device=dev).abs_(); g /= g.norm(dim=1, keepdim=True)
@@ -32,4 +35,4 @@ for nm, ex in (("c5q_exact", True), ("c5q_bf16", False)):
         s, i = ops.sim_topk(qb, gb, 5, 0, q5 if ex else None, g5 if ex else None, qi if ex else None, gi if ex else None)
         e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
     res[nm] = round(sorted(ts[1:])[len(ts[1:]) // 2], 4)
-print(json.dumps({"so": os.environ.get("CVPCE_B200_SO", "current"), **res}))
+print(json.dumps({"so": os.path.basename(os.environ.get("CVPCE_B200_SO") or "current"), "tune": tune, **res}))
