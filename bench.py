@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--e2e-serial", action="store_true", help="e2e leg: upload all images before the step instead of overlapping "
                     "the upload with the step's own compute")
     ap.add_argument("--upload-group", type=int, default=4, help="e2e leg: shelf images per upload group")
+    ap.add_argument("--e2e-prefetch", type=int, default=0, help="e2e leg: 1 = the next step's images are uploaded (second staging buffer) behind this step's compute; 0 = every step uploads its own images first")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extension-modes", action="store_true", help="skip the short extra pass that also reports the f16-trunk "
                     "extension mode next to the headline (N = 1, default trunk only)")
@@ -315,13 +316,18 @@ def run_ours_shelves(args, world, rank, local):
     h2d += (head_h[0].numel() + head_h[1].numel()) * 4 if args.from_head else (boxes_p.numel() + scores_p.numel() + seg_p.numel()) * 4
     del images
 
-    def e2e_step():
+    def e2e_upload():
         # the step's images go up on the library's copy stream in groups (HotPath.upload_images) and are consumed group by
-        # group, so this step's own transfer overlaps this step's convolutions; --e2e-serial uploads everything first
+        # group, so the transfer overlaps convolutions; --e2e-serial uploads everything first
         if args.e2e_serial:
-            imgs, ups = [im.to(device, non_blocking=True) for im in images_h], None
-        else:
-            imgs, ups = hp.upload_images(images_h, args.upload_group)
+            return [im.to(device, non_blocking=True) for im in images_h], None
+        return hp.upload_images(images_h, args.upload_group)
+
+    def e2e_step(up=None, prefetch=False):
+        imgs, ups = up if up is not None else e2e_upload()
+        # double-buffered staging: the NEXT step's images start moving now, behind this step's compute (a serving loop that
+        # knows its next batch, like the reference's DataLoader prefetch); every step's H2D copy is still inside the timed region
+        nxt = e2e_upload() if prefetch else None
         if args.from_head:
             o = run_step(imgs, head=(head_h[0].to(device, non_blocking=True), head_h[1].to(device, non_blocking=True)), uploads=ups)
         else:
@@ -329,15 +335,17 @@ def run_ours_shelves(args, world, rank, local):
                                      seg_p.to(device, non_blocking=True)), uploads=ups)
         idx = o["topk_idx"].cpu()
         bx = o["boxes"].cpu()
-        return idx, bx
+        return idx, bx, nxt
 
+    prefetch = bool(args.e2e_prefetch) and not args.e2e_serial
     for _ in range(max(1, min(args.warmup, 2))):
-        idx_h, bx_h = e2e_step()
+        idx_h, bx_h, _ = e2e_step()
     d2h = idx_h.numel() * 8 + bx_h.numel() * 4 + n_shelves * 4
     barrier(world)
     e0.record()
-    for _ in range(args.steps):
-        e2e_step()
+    up = None
+    for s_i in range(args.steps):
+        _, _, up = e2e_step(up, prefetch and s_i + 1 < args.steps)
     e1.record()
     barrier(world)
     ms_e2e_rank = e0.elapsed_time(e1)
@@ -421,7 +429,8 @@ def run_ours_shelves(args, world, rank, local):
                 "ms_per_step": round(ms_e2e / args.steps, 3),
                 "ms_per_step_per_rank": {"min": round(min(per_rank_e2e), 3), "max": round(max(per_rank_e2e), 3)},
                 "upload": "all images before the step" if args.e2e_serial else
-                          "copy stream, groups of %d shelves, overlapped with the step's own compute (HotPath.upload_images)" % args.upload_group},
+                          ("copy stream, groups of %d shelves, overlapped with compute (HotPath.upload_images); " % args.upload_group) +
+                          ("two staging buffers: step s+1's images go up behind step s" if args.e2e_prefetch else "each step uploads its own images first")},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,

@@ -49,6 +49,14 @@ class _NoTimer:
         return contextlib.nullcontext()
 
 
+class _Uploads(list):
+    """(event, first image, end image) per upload group, plus the staging buffer they went to."""
+
+    def __init__(self, slot):
+        super().__init__()
+        self.slot = slot
+
+
 class HotPath:
     def __init__(self, encoder, gallery_embedding, k=1, size=256, antialias=True, iou_threshold=0.5, detections_per_img=200,
                  min_score=None, trunk_batch=128, trunk_dtype=torch.float32, channels_last=False, exact=True, rmac_levels=0,
@@ -69,7 +77,8 @@ class HotPath:
         self.rmac_levels = rmac_levels
         self.n_streams = n_streams
         self._streams = None
-        self._copy_stream = self._stage = self._stage_key = self._stage_free = None
+        self._copy_stream = None
+        self._stage, self._stage_key, self._stage_free, self._stage_next = [None, None], [None, None], [None, None], 0
         self.affine = classification.tanh_normalize_affine()  # scale_to_tanh + MACVGG normalisation folded into the crop kernel
         self.launches = 0  # launches of OUR kernels (library calls), counted per call site
         self.timer = _NoTimer()
@@ -114,29 +123,35 @@ class HotPath:
         persistent staging buffer.  Returns (device images, uploads) for step(..., uploads=uploads) /
         step_from_head(..., uploads=uploads): the step then cuts the crops of a group as soon as its images have landed
         and runs the trunk on the crops that exist, so the transfer of the step's own images is hidden behind its
-        convolutions instead of preceding them."""
+        convolutions instead of preceding them.
+        There are TWO staging buffers, used alternately: a serving loop may call upload_images for step s+1 before it runs
+        step s, and the copy stream then moves the next step's images while this step computes (the buffer a call takes is
+        the one released two steps ago)."""
         dev = self.gallery.f32.device
         B = len(images_h)
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=dev)
+        slot = self._stage_next
+        self._stage_next ^= 1
         shapes = [tuple(im.shape) for im in images_h]
-        if self._stage is None or self._stage_key != shapes:
-            self._stage = [torch.empty(sh, dtype=torch.float32, device=dev) for sh in shapes]
-            self._stage_key = shapes
+        if self._stage[slot] is None or self._stage_key[slot] != shapes:
+            self._stage[slot] = [torch.empty(sh, dtype=torch.float32, device=dev) for sh in shapes]
+            self._stage_key[slot] = shapes
+        stage = self._stage[slot]
         cs = self._copy_stream
-        if self._stage_free is not None:
-            cs.wait_event(self._stage_free)  # the previous step's crop launches have finished reading the staging buffers
-            self._stage_free = None
-        uploads = []
+        if self._stage_free[slot] is not None:
+            cs.wait_event(self._stage_free[slot])  # the step that last used this buffer has finished reading it
+            self._stage_free[slot] = None
+        uploads = _Uploads(slot)
         with torch.cuda.stream(cs):
             for lo in range(0, B, upload_group):
                 hi = min(B, lo + upload_group)
                 for i in range(lo, hi):
-                    self._stage[i].copy_(images_h[i], non_blocking=True)
+                    stage[i].copy_(images_h[i], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(cs)
                 uploads.append((ev, lo, hi))
-        return self._stage, uploads
+        return stage, uploads
 
     @torch.no_grad()
     def step_host(self, images_h, cand_boxes_h, cand_scores_h, seg_offsets_h, max_n, upload_group=4):
@@ -193,9 +208,10 @@ class HotPath:
                             ops.crop_resize(table, B, boxes[a:b], image_idx32[a:b], S, self.antialias, 0.5, self.affine,
                                             self.trunk_dtype, self.channels_last, out=phys[a:b], pad_channel=pad4)
                         self.launches += 1
-                if not pending and self._stage_free is None:
-                    self._stage_free = torch.cuda.Event()
-                    self._stage_free.record(main_stream)
+                slot = getattr(uploads, "slot", 0)
+                if not pending and self._stage_free[slot] is None:
+                    self._stage_free[slot] = torch.cuda.Event()
+                    self._stage_free[slot].record(main_stream)
         D = self.encoder.embedding_size
         emb = torch.empty((K, D), dtype=torch.float32, device=dev)
         regions = None

@@ -949,9 +949,24 @@ def test_hot_path_step_host_overlapped_upload_equals_step(ops):
                 assert torch.equal(got["boxes"], want["boxes"])
                 assert torch.equal(got["embedding"], want["embedding"]), (kwargs, group)
                 assert torch.equal(got["topk_idx"], want["topk_idx"]) and torch.equal(got["topk_sim"], want["topk_sim"])
+        # prefetch: the next step's images (a DIFFERENT set: the order reversed) go up into the second staging buffer before this
+        # step runs; three steps in flight over two buffers
+        rev_h = images_h[::-1]
+        rev_seg = np.concatenate([[0], np.cumsum(np.diff(seg)[::-1])]).astype(np.int32)
+        rev_boxes = np.concatenate([boxes[seg[i]:seg[i + 1]] for i in range(n_img - 1, -1, -1)])
+        rev_scores = np.concatenate([scores[seg[i]:seg[i + 1]] for i in range(n_img - 1, -1, -1)])
+        want_rev = hp.step([im.cuda() for im in images[::-1]], dev(rev_boxes), dev(rev_scores), dev(rev_seg), max_n)
+        up_a = hp.upload_images(images_h, 2)
+        up_b = hp.upload_images(rev_h, 2)
+        got_a = hp.step(up_a[0], dev(boxes), dev(scores), dev(seg), max_n, uploads=up_a[1])
+        up_c = hp.upload_images(images_h, 3)      # reuses the first buffer: waits for step A's crops
+        got_b = hp.step(up_b[0], dev(rev_boxes), dev(rev_scores), dev(rev_seg), max_n, uploads=up_b[1])
+        got_c = hp.step(up_c[0], dev(boxes), dev(scores), dev(seg), max_n, uploads=up_c[1])
+        for got, w in ((got_a, want), (got_b, want_rev), (got_c, want)):
+            assert torch.equal(got["boxes"], w["boxes"]) and torch.equal(got["embedding"], w["embedding"]) and torch.equal(got["topk_idx"], w["topk_idx"])
     # a step with no detections at all releases the staging buffers too
     empty = hp.step_host(images_h, bh[:0], sh[:0], torch.zeros(n_img + 1, dtype=torch.int32).pin_memory(), 1, upload_group=2)
-    assert int(empty["counts"].sum()) == 0 and hp._stage_free is not None
+    assert int(empty["counts"].sum()) == 0 and any(e is not None for e in hp._stage_free)
 
 
 def test_patch_layer_on_a_reference_shaped_package(ops):
