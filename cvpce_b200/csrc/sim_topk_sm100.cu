@@ -217,19 +217,205 @@ struct TopList {
   }
 };
 
+// ------------------------------------------------------------------------------------------------------------------------
+// Key lists (short pieces: at most 16 gallery tiles = 4096 columns per list lifetime).
+// A candidate is ONE float: the similarity with its low 12 mantissa bits replaced by the column inside the piece, encoded so
+// that among similarities of the same 2^-11-relative bucket the lower column is the larger key.  A sorted list of keys is
+// then maintained with min / max alone (no index array, no compare + select pairs): inserting costs 31 FMNMX instead of
+// ~100 compare / select instructions, and a whole 32-column chunk can be merged by a sorting network (~480 FMNMX, the same
+// for every lane) while a list warms up, instead of one warp-wide insert per event of any lane.  The price is that
+// candidates are ranked by similarities truncated to 11 mantissa bits (2^-12 relative, 1/16 of the bf16 operand rounding the
+// re-score margin already covers); the selection kernel adds it to its error bound.
+// ------------------------------------------------------------------------------------------------------------------------
+constexpr int kKeyColBits = 12;
+constexpr uint32_t kKeyColMask = (1u << kKeyColBits) - 1u;
+constexpr int kKeyMaxTiles = (1 << kKeyColBits) / BN;  // 16
+constexpr int kKeyNetworkMin = 6;  // survivors of some lane in a chunk from which the sorting network is cheaper than the inserts
+
+__device__ __forceinline__ float make_key(uint32_t bits, uint32_t col) {
+  // positive floats grow with their low bits, negative ones shrink: store (4095 - col) resp. col so that a lower column wins
+  const uint32_t low = (bits & 0x80000000u) ? col : (kKeyColMask - col);
+  return __uint_as_float((bits & ~kKeyColMask) | low);
+}
+// smallest float of the key's similarity bucket: every similarity that could produce a key above `key` is >= it
+__device__ __forceinline__ float key_bucket_floor(float key) {
+  if (key == -INFINITY) return key;
+  const uint32_t b = __float_as_uint(key);
+  return __uint_as_float((b & 0x80000000u) ? (b | kKeyColMask) : (b & ~kKeyColMask));
+}
+__device__ __forceinline__ void key_decode(float key, int col_base, float& score, int& idx) {
+  if (key == -INFINITY) {
+    score = -INFINITY;
+    idx = -1;
+    return;
+  }
+  const uint32_t b = __float_as_uint(key);
+  const uint32_t low = b & kKeyColMask;
+  idx = col_base + (int)((b & 0x80000000u) ? low : (kKeyColMask - low));
+  score = __uint_as_float(b & ~kKeyColMask);  // the bucket's representative: independent of where the piece started
+}
+
+// compare-exchange, larger first
+__device__ __forceinline__ void ce_desc(float& a, float& b) {
+  const float hi = fmaxf(a, b), lo = fminf(a, b);
+  a = hi;
+  b = lo;
+}
+// in-register bitonic sort, descending; N a power of two, every index a compile-time constant
+template <int N>
+__device__ __forceinline__ void bitonic_sort_desc(float (&a)[N]) {
+#pragma unroll
+  for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const int l = i ^ j;
+        if (l > i) {
+          if ((i & k) == 0) ce_desc(a[i], a[l]);
+          else ce_desc(a[l], a[i]);
+        }
+      }
+    }
+  }
+}
+// bitonic sequence -> sorted descending
+template <int N>
+__device__ __forceinline__ void bitonic_merge_desc(float (&a)[N]) {
+#pragma unroll
+  for (int j = N >> 1; j > 0; j >>= 1) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const int l = i ^ j;
+      if (l > i) ce_desc(a[i], a[l]);
+    }
+  }
+}
+
+struct KeyList {  // 16 keys, sorted descending; empty slots are -inf
+  float s[16];
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s[j] = -INFINITY;
+  }
+  __device__ __forceinline__ float threshold() const { return s[15]; }
+  // keys are unique, so the sorted insert is min / max only; a key below the last entry falls off
+  __device__ __forceinline__ void insert(float key) {
+    float n[16];
+    n[0] = fmaxf(s[0], key);
+#pragma unroll
+    for (int j = 1; j < 16; ++j) n[j] = fminf(s[j - 1], fmaxf(s[j], key));
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s[j] = n[j];
+  }
+  // the 16 best of (list, 32 keys): sort the halves, keep the upper half of each merge
+  __device__ __forceinline__ void merge32(float (&k)[32]) {
+    float a[16], b[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      a[j] = k[j];
+      b[j] = k[16 + j];
+    }
+    bitonic_sort_desc<16>(a);
+    bitonic_sort_desc<16>(b);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) a[j] = fmaxf(a[j], b[15 - j]);  // bitonic, holds the chunk's 16 best
+    bitonic_merge_desc<16>(a);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s[j] = fmaxf(s[j], a[15 - j]);  // bitonic, holds the 16 best of list and chunk
+    bitonic_merge_desc<16>(s);
+  }
+};
+
+// One 32-column chunk against a key list.  col = column of r[0] inside the piece (< 4096 - 31); n_valid < 32 on the tail tile.
+__device__ __forceinline__ void scan_chunk_keys(KeyList& top, const uint32_t (&r)[32], uint32_t col, int n_valid) {
+  const float floor_ = key_bucket_floor(top.threshold());
+  uint32_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) m |= (__uint_as_float(r[j]) >= floor_) ? (1u << j) : 0u;  // NaN never passes
+  if (n_valid < 32) m &= (1u << n_valid) - 1u;
+  const unsigned most = __reduce_max_sync(0xffffffffu, (unsigned)__popc(m));
+  if (most == 0) return;
+  if (most >= (unsigned)kKeyNetworkMin) {
+    float k[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) k[j] = ((m >> j) & 1u) ? make_key(r[j], col + j) : -INFINITY;
+    top.merge32(k);
+    return;
+  }
+  while (m) {
+    const int j = __ffs(m) - 1;
+    m &= m - 1;
+    top.insert(make_key(pick32(r, j), col + j));
+  }
+}
+
+// Work distribution.  An ITEM is (query block of 128 rows, gallery tile of 256 rows), numbered m_blk * n_tiles + tile.
+//   grid   (LINEAR = false): CTA b = (m_blk = b % m_blocks, split = b / m_blocks) takes tiles [split*tps, (split+1)*tps) of ONE
+//          query block; the CTAs of a wave stream the same gallery range in step (a gallery larger than L2 is read from HBM
+//          about once per wave).  The row's list of this CTA goes to slot `split`.
+//   linear (LINEAR = true):  CTA b takes items [b*N/G, (b+1)*N/G), G = gridDim.x = the SM count: every SM gets the same number
+//          of tiles (+-1) whatever m_blocks is (C3: 50 query blocks x 32 tiles = 10.8 tiles on each of 148 SMs instead of 16
+//          tiles on 100 of them).  The range is cut into PIECES at the query-block boundaries, one list lifetime each; the
+//          list of a piece goes to slot b - (first CTA that touches the query block).  Pays only with the key lists (a list
+//          restart costs ~17 us with the compare / select lists) and when both operands stay L2-resident.
 struct TcParams {
   int Q, G, D;
   int n_tiles;          // ceil(G / BN)
   int m_blocks;         // ceil(Q / BM)
-  int n_split;          // gallery splits (gridDim.x = m_blocks * n_split, m fastest)
-  int tiles_per_split;  // ceil(n_tiles / n_split)
-  float* cand_s;        // [Q, n_split, KP]
+  int n_split;          // grid: gallery splits (gridDim.x = m_blocks * n_split, m fastest)
+  int tiles_per_split;  // grid: ceil(n_tiles / n_split)
+  long long n_items;    // linear: m_blocks * n_tiles
+  int max_lists;        // lists per row in the workspace (grid: n_split)
+  float* cand_s;        // [Q, max_lists, KP]
   int* cand_i;
 };
 
-template <bool RESIDENT_A, int KP>
+// first CTA of a linear launch whose range [c*N/G, (c+1)*N/G) holds item x
+__host__ __device__ __forceinline__ long long tc_owner(long long x, long long G, long long N) { return ((x + 1) * G - 1) / N; }
+
+// the pieces of a CTA's item range, in order (the three roles walk them independently and identically)
+template <bool LINEAR>
+struct PieceWalk {
+  long long it, end;
+  int n_tiles;
+  bool first;
+  __device__ __forceinline__ PieceWalk(const TcParams& p) : n_tiles(p.n_tiles), first(true) {
+    if (LINEAR) {
+      it = (long long)blockIdx.x * p.n_items / gridDim.x;
+      end = ((long long)blockIdx.x + 1) * p.n_items / gridDim.x;
+    } else {
+      const int m_blk = blockIdx.x % p.m_blocks, split = blockIdx.x / p.m_blocks;
+      it = (long long)m_blk * p.n_tiles + min(p.n_tiles, split * p.tiles_per_split);
+      end = (long long)m_blk * p.n_tiles + min(p.n_tiles, (split + 1) * p.tiles_per_split);
+    }
+  }
+  // next piece: tiles [tb, te) of query block m_blk.  The grid form yields exactly one piece, even an empty one (empty
+  // gallery: the row's list must still be written).
+  __device__ __forceinline__ bool next(const TcParams& p, int& m_blk, int& tb, int& te) {
+    if (!LINEAR) {
+      if (!first) return false;
+      first = false;
+      m_blk = blockIdx.x % p.m_blocks;
+      tb = (int)(it - (long long)m_blk * n_tiles);
+      te = (int)(end - (long long)m_blk * n_tiles);
+      return true;
+    }
+    if (it >= end) return false;
+    m_blk = (int)(it / n_tiles);
+    tb = (int)(it - (long long)m_blk * n_tiles);
+    te = (int)min((long long)n_tiles, (long long)tb + (end - it));
+    it += te - tb;
+    return true;
+  }
+};
+
+// KEYS: key lists in the epilogue (KP == 16 and at most kKeyMaxTiles tiles per piece; the host guarantees both)
+// LINEAR: linear item ranges (see TcParams); the query tiles stream (a range changes query blocks)
+template <bool RESIDENT_A, int KP, bool KEYS, bool LINEAR>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_g, const TcParams p) {
+  static_assert(!(LINEAR && RESIDENT_A), "a linear range changes query blocks: the query tiles must stream");
   constexpr int kStages = RESIDENT_A ? kStagesResident : kStagesStream;
   constexpr int kStageBytes = RESIDENT_A ? B_TILE_BYTES : (A_TILE_BYTES + B_TILE_BYTES);
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
@@ -246,12 +432,7 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_blk = blockIdx.x % p.m_blocks;
-  const int split = blockIdx.x / p.m_blocks;
-  const int t0 = split * p.tiles_per_split;
-  const int t1 = min(p.n_tiles, t0 + p.tiles_per_split);
   const int KB = p.D / BK;
-  const int m0 = m_blk * BM;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -279,11 +460,16 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     // ===================================================== TMA producer =====================================================
     if (lane == 0) {
       if (RESIDENT_A) {
+        const int m0 = (int)(blockIdx.x % p.m_blocks) * BM;
         mbar_expect_tx(&a_full_bar, (uint32_t)(KB * A_TILE_BYTES));
         for (int kb = 0; kb < KB; ++kb) tma_load_2d(a_res + kb * A_TILE_BYTES, &tmap_q, &a_full_bar, kb * BK, m0);
       }
       int stage = 0;
       uint32_t phase = 0;
+      PieceWalk<LINEAR> walk(p);
+      int m_blk, t0, t1;
+      while (walk.next(p, m_blk, t0, t1)) {
+      const int m0 = m_blk * BM;
       for (int t = t0; t < t1; ++t) {
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -301,6 +487,7 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
           }
         }
       }
+      }
     }
   } else if (warp == 1) {
     // ====================================================== MMA issuer ======================================================
@@ -312,8 +499,11 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_phase = 0;  // bit a = phase of accumulator a
-      for (int t = t0; t < t1; ++t) {
-        const int acc = (t - t0) & 1;
+      int acc = 0;             // the accumulators alternate over the CTA's whole range, across pieces
+      PieceWalk<LINEAR> walk(p);
+      int m_blk, t0, t1;
+      while (walk.next(p, m_blk, t0, t1)) {
+      for (int t = t0; t < t1; ++t, acc ^= 1) {
         mbar_wait(&tmem_empty_bar[acc], ((acc_phase >> acc) & 1u) ^ 1u);  // epilogue has drained this accumulator
         acc_phase ^= 1u << acc;
         tc_fence_after();
@@ -339,16 +529,22 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         }
         umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
       }
+      }
     }
   } else if (warp >= kEpilogueWarp0) {
     // ======================================================= epilogue =======================================================
     const int ew = warp - kEpilogueWarp0;      // == warp % 4: the TMEM lane quadrant this warp may read
-    const int row = m0 + ew * 32 + lane;       // query row owned by this thread
-    TopList<KP> top;
-    top.init();
+    TopList<KEYS ? 1 : KP> top;
+    KeyList ktop;
     uint32_t acc_phase = 0;
-    for (int t = t0; t < t1; ++t) {
-      const int acc = (t - t0) & 1;
+    int acc = 0;
+    PieceWalk<LINEAR> walk(p);
+    int m_blk, t0, t1;
+    while (walk.next(p, m_blk, t0, t1)) {
+    const int row = m_blk * BM + ew * 32 + lane;  // query row owned by this thread in this piece
+    if constexpr (KEYS) ktop.init();
+    else top.init();
+    for (int t = t0; t < t1; ++t, acc ^= 1) {
       mbar_wait(&tmem_full_bar[acc], (acc_phase >> acc) & 1u);
       acc_phase ^= 1u << acc;
       tc_fence_after();
@@ -361,18 +557,22 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         uint32_t r[32];
         tmem_ld_32x32(taddr + (uint32_t)c0, r);
         tmem_ld_wait();
-        // common case: one compare per similarity against the row's current k'-th score; the (rare) survivors are
-        // collected in a bitmask and inserted below in ascending column order, so equal scores keep the lower index
-        const float thr = top.threshold();
-        uint32_t m = 0;
+        if constexpr (KEYS) {
+          scan_chunk_keys(ktop, r, (uint32_t)((t - t0) * BN + c0), valid - c0);
+        } else {
+          // common case: one compare per similarity against the row's current k'-th score; the (rare) survivors are
+          // collected in a bitmask and inserted below in ascending column order, so equal scores keep the lower index
+          const float thr = top.threshold();
+          uint32_t m = 0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) m |= (__uint_as_float(r[j]) > thr) ? (1u << j) : 0u;
-        if (c0 + 32 > valid) m &= (1u << (valid - c0)) - 1u;  // tail tile: drop the zero-filled columns
-        while (m) {
-          const int j = __ffs(m) - 1;
-          m &= m - 1;
-          const float v = __uint_as_float(pick32(r, j));
-          if (v > top.threshold()) top.insert(v, n0 + c0 + j);
+          for (int j = 0; j < 32; ++j) m |= (__uint_as_float(r[j]) > thr) ? (1u << j) : 0u;
+          if (c0 + 32 > valid) m &= (1u << (valid - c0)) - 1u;  // tail tile: drop the zero-filled columns
+          while (m) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            const float v = __uint_as_float(pick32(r, j));
+            if (v > top.threshold()) top.insert(v, n0 + c0 + j);
+          }
         }
       }
       tc_fence_before();
@@ -380,13 +580,30 @@ sim_topk_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
       if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
     }
     if (row < p.Q) {
-      float* cs = p.cand_s + ((size_t)row * p.n_split + split) * KP;
-      int* ci = p.cand_i + ((size_t)row * p.n_split + split) * KP;
+      const int slot = LINEAR ? (int)((long long)blockIdx.x - tc_owner((long long)m_blk * p.n_tiles, gridDim.x, p.n_items))
+                              : (int)(blockIdx.x / p.m_blocks);
+      float* cs = p.cand_s + ((size_t)row * p.max_lists + slot) * KP;
+      int* ci = p.cand_i + ((size_t)row * p.max_lists + slot) * KP;
+      if constexpr (KEYS) {
 #pragma unroll
-      for (int j = 0; j < KP; j += 4) {
-        *reinterpret_cast<float4*>(cs + j) = make_float4(top.s[j], top.s[j + 1], top.s[j + 2], top.s[j + 3]);
-        *reinterpret_cast<int4*>(ci + j) = make_int4(top.i[j], top.i[j + 1], top.i[j + 2], top.i[j + 3]);
+        for (int j = 0; j < 16; j += 4) {
+          float4 sc;
+          int4 ix;
+          key_decode(ktop.s[j], t0 * BN, sc.x, ix.x);
+          key_decode(ktop.s[j + 1], t0 * BN, sc.y, ix.y);
+          key_decode(ktop.s[j + 2], t0 * BN, sc.z, ix.z);
+          key_decode(ktop.s[j + 3], t0 * BN, sc.w, ix.w);
+          *reinterpret_cast<float4*>(cs + j) = sc;
+          *reinterpret_cast<int4*>(ci + j) = ix;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < KP; j += 4) {
+          *reinterpret_cast<float4*>(cs + j) = make_float4(top.s[j], top.s[j + 1], top.s[j + 2], top.s[j + 3]);
+          *reinterpret_cast<int4*>(ci + j) = make_int4(top.i[j], top.i[j + 1], top.i[j + 2], top.i[j + 3]);
+        }
       }
+    }
     }
   }
   tc_fence_before();
@@ -422,9 +639,50 @@ struct OutTargets {
 constexpr int kSelWarps = 4;
 constexpr int kSelMaxCand = 512;  // candidates of a row staged in shared memory (more take the serial merge)
 
+// exact fp32 re-score of the first n_rescore candidates of a row (lane c holds candidate c in my_i and receives its score)
+template <bool FULL>
+__device__ __forceinline__ void rescore_rows(const float* __restrict__ qr, const float* __restrict__ g32, const float* __restrict__ g_inv,
+                                             float qi, int D, int n_rescore, int my_i, float& my_s, int lane) {
+  float4 qv[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int d = u * 128 + lane * 4;
+    qv[u] = (FULL || d < D) ? *reinterpret_cast<const float4*>(qr + d) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int c = 0; c < n_rescore; ++c) {
+    const int gi = __shfl_sync(0xffffffffu, my_i, c);
+    const float* gr = g32 + (size_t)gi * D + lane * 4;
+    const float ginv = g_inv ? __ldg(g_inv + gi) : 1.f;
+    float4 gv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      gv[u] = (FULL || u * 128 + lane * 4 < D) ? __ldg(reinterpret_cast<const float4*>(gr + u * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float ax = 0.f, ay = 0.f, az = 0.f, aw = 0.f;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      ax = fmaf(qv[u].x, gv[u].x, ax);
+      ay = fmaf(qv[u].y, gv[u].y, ay);
+      az = fmaf(qv[u].z, gv[u].z, az);
+      aw = fmaf(qv[u].w, gv[u].w, aw);
+    }
+    const float acc = warp_sum((ax + ay) + (az + aw));
+    const float sc = acc * qi * ginv;
+    if (lane == c) my_s = sc;
+  }
+}
+
+// which lists of the workspace belong to a row (see TcParams)
+struct SelLists {
+  int linear;       // 0: every row has n_lists0 lists; 1: one list per CTA of the linear launch that touches the row's query block
+  int stride;       // lists per row in the workspace
+  int n_lists0;
+  int n_tiles, n_ctas;
+  long long n_items;
+};
+
 template <int KP>
 __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float* __restrict__ cand_s, const int* __restrict__ cand_i, int Q,
-                                                                    int n_split, int k, long long idx_base, int D,
+                                                                    const SelLists sl, int k, long long idx_base, int D, float approx_slack,
                                                                     const float* __restrict__ q32, const float* __restrict__ g32,
                                                                     const float* __restrict__ q_inv, const float* __restrict__ g_inv,
                                                                     const OutTargets out) {
@@ -435,10 +693,14 @@ __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float*
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int row = blockIdx.x * kSelWarps + wib;
   if (row >= Q) return;
-  const int n_lists = n_split;
+  int n_lists = sl.n_lists0;
+  if (sl.linear) {
+    const long long first = (long long)(row / BM) * sl.n_tiles;
+    n_lists = (int)(tc_owner(first + sl.n_tiles - 1, sl.n_ctas, sl.n_items) - tc_owner(first, sl.n_ctas, sl.n_items) + 1);
+  }
   const int C = n_lists * KP;
-  const float* cs = cand_s + (size_t)row * n_split * KP;
-  const int* ci = cand_i + (size_t)row * n_split * KP;
+  const float* cs = cand_s + (size_t)row * sl.stride * KP;
+  const int* ci = cand_i + (size_t)row * sl.stride * KP;
   // ---- stage 1: the KP best candidates by kernel-1 score; lane j ends up holding the j-th
   float my_s = -INFINITY;
   int my_i = -1;
@@ -555,11 +817,20 @@ __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float*
   if (q32 != nullptr) {
     const float* qr = q32 + (size_t)row * D;
     const float qi = q_inv ? q_inv[row] : 1.f;
-    const float eps_bound = 0.00390625f * (1.f + 0.0009765625f) + (float)D * 1.1920929e-7f;
+    const float eps_bound = 0.00390625f * (1.f + 0.0009765625f) + (float)D * 1.1920929e-7f + approx_slack;  // slack: key lists rank truncated scores
     const float a_k = __shfl_sync(0xffffffffu, my_s, k - 1);  // -inf when the row has fewer than k candidates: everything stays
     const bool keep = lane < KP && my_i >= 0 && (lane < k || !(my_s < a_k - 2.f * eps_bound));
     const int n_rescore = __popc(__ballot_sync(0xffffffffu, keep));  // a prefix: the lanes are sorted by approximate score
     if (!keep) my_i = -1;
+    if ((D & 3) == 0 && D <= 1024) {
+      // The query row stays in registers (8 float4 per lane cover D <= 1024); per candidate: 8 independent 128-bit loads of
+      // the gallery row and four independent FMA chains (one per float4 component; a single 32-long chain was the kernel's
+      // main stall), summed (x + y) + (z + w), one butterfly.  D == 1024 (the VGG descriptor) runs without the d < D predicates.
+      // A (query, gallery row) score depends only on the two rows and D.  The general loop below re-read the query slice for
+      // every candidate and spent ~150 instructions per candidate: 46-66 us for 6400 rows, 40 % of the search at the C3 shape.
+      if (D == 1024) rescore_rows<true>(qr, g32, g_inv, qi, D, n_rescore, my_i, my_s, lane);
+      else rescore_rows<false>(qr, g32, g_inv, qi, D, n_rescore, my_i, my_s, lane);
+    } else
     for (int c = 0; c < n_rescore; ++c) {
       const int gi = __shfl_sync(0xffffffffu, my_i, c);
       const float* gr = g32 + (size_t)gi * D;
@@ -680,6 +951,9 @@ static int kp_for(int k, bool rescore) {
 
 struct TcPlan {
   int m_blocks, n_tiles, n_split, tiles_per_split, kp;
+  bool linear;   // linear item ranges over n_ctas CTAs (key lists only)
+  int n_ctas, slots;
+  long long n_items;
 };
 
 static TcPlan make_plan(int Q, int G, int D, int k, bool rescore) {
@@ -717,16 +991,36 @@ static TcPlan make_plan(int Q, int G, int D, int k, bool rescore) {
   pl.n_split = best;
   pl.tiles_per_split = (pl.n_tiles + best - 1) / best;
   pl.n_split = (pl.n_tiles + pl.tiles_per_split - 1) / pl.tiles_per_split;
+  pl.linear = false;
+  pl.n_ctas = pl.m_blocks * pl.n_split;
+  pl.slots = pl.n_split;
+  pl.n_items = (long long)pl.m_blocks * pl.n_tiles;
+  // Linear ranges: the same number of tiles (+-1) on every SM.  Conditions: key lists (16 candidates, pieces of at most 16
+  // tiles -- with them a list restart is cheap), both operands L2-resident (the CTAs no longer sweep the gallery in step),
+  // no forced split, and the grid leaves SMs idle or its last wave ragged.
+  const int want = tuning("sim_plan");  // 0: automatic; 1: grid; 2: linear whenever it is legal
+  const long long per_cta = (pl.n_items + sms - 1) / sms;
+  const double operand_mb = ((double)Q + (double)G) * D * 2 / (1024.0 * 1024.0);
+  const bool legal = pl.kp == 16 && tuning("sim_keys") != 1 && forced == 0 && pl.n_items >= sms && per_cta <= kKeyMaxTiles;
+  if (legal && want != 1) {
+    const long long waves = ((long long)pl.n_ctas + sms - 1) / sms;
+    const double grid_tiles = (double)waves * pl.tiles_per_split;  // tiles on the busiest SM with the grid
+    if (want == 2 || (operand_mb <= 64.0 && grid_tiles > 1.15 * (double)per_cta)) {
+      pl.linear = true;
+      pl.n_ctas = sms;
+      pl.slots = (int)(((long long)pl.n_tiles * sms + pl.n_items - 1) / pl.n_items) + 1;  // CTAs that can touch one query block
+    }
+  }
   return pl;
 }
 
-template <bool RES, int KP>
-static int launch_tc(const CUtensorMap& tq, const CUtensorMap& tg, const TcParams& p, cudaStream_t st) {
+template <bool RES, int KP, bool KEYS, bool LINEAR = false>
+static int launch_tc(const CUtensorMap& tq, const CUtensorMap& tg, const TcParams& p, int n_ctas, cudaStream_t st) {
   constexpr int stages = RES ? kStagesResident : kStagesStream;
   constexpr int stage_bytes = RES ? B_TILE_BYTES : (A_TILE_BYTES + B_TILE_BYTES);
   const size_t smem = 1024 + (RES ? (size_t)kMaxResidentKB * A_TILE_BYTES : 0) + (size_t)stages * stage_bytes;
-  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&sim_topk_tc_kernel<RES, KP>), smem)) return rc;
-  sim_topk_tc_kernel<RES, KP><<<(unsigned)(p.m_blocks * p.n_split), kTcThreads, smem, st>>>(tq, tg, p);
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(&sim_topk_tc_kernel<RES, KP, KEYS, LINEAR>), smem)) return rc;
+  sim_topk_tc_kernel<RES, KP, KEYS, LINEAR><<<(unsigned)n_ctas, kTcThreads, smem, st>>>(tq, tg, p);
   CVPCE_LAUNCH_OK("sim_topk_tc_kernel");
   return CVPCE_OK;
 }
@@ -738,9 +1032,9 @@ extern "C" size_t cvpce_sim_topk_workspace_bytes(int Q, int G, int D, int k) {
   if (Q <= 0 || G <= 0 || D <= 0 || k <= 0 || k > 32) return 0;
   // sized for k' = 32 and for whichever split count a tuning override may select
   const TcPlan a = make_plan(Q, G, D, k, true);
-  size_t lists = (size_t)(a.n_split > 64 ? a.n_split : 64);  // any forced split count
-  if (lists > (size_t)a.n_tiles) lists = (size_t)a.n_tiles;
-  if (lists < (size_t)a.n_split) lists = (size_t)a.n_split;
+  size_t lists = (size_t)(a.slots > 64 ? a.slots : 64);  // any forced split count
+  if (lists > (size_t)a.n_tiles + 1) lists = (size_t)a.n_tiles + 1;
+  if (lists < (size_t)a.slots) lists = (size_t)a.slots;
   return (size_t)Q * lists * 32 * 8 + 256;
 }
 
@@ -763,34 +1057,50 @@ static int sim_topk_impl(const void* q_bf16, const void* g_bf16, int Q, int G, i
                 "sim_topk: the exact re-score keeps k + 8 <= 32 candidates per row, so k=%d > 24 is not served (use cvpce_sim_topk_f32)", k);
   if (int rc = require_sm100()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const bool resident = D <= kMaxResidentKB * BK;
   uintptr_t ws = (reinterpret_cast<uintptr_t>(workspace) + 127) & ~(uintptr_t)127;
   CUtensorMap tq, tg;
   if (int rc = make_tmap(q_bf16, Q, D, BM, &tq)) return rc;
   const TcPlan pl = make_plan(Q, G > 0 ? G : 1, D, k, rescore);
   const int kp = pl.kp;
-  const size_t need = (size_t)Q * pl.n_split * pl.kp * 8 + 256;
+  const bool linear = pl.linear && G > 0;
+  const bool resident = D <= kMaxResidentKB * BK && !linear;
+  const size_t need = (size_t)Q * pl.slots * pl.kp * 8 + 256;
   CVPCE_REQUIRE(workspace && workspace_bytes >= need, CVPCE_ERR_WORKSPACE, "sim_topk: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
   float* cand_s = reinterpret_cast<float*>(ws);
-  int* cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.n_split * pl.kp * 4);
+  int* cand_i = reinterpret_cast<int*>(ws + (size_t)Q * pl.slots * pl.kp * 4);
   TcParams p;
   p.Q = Q; p.G = G; p.D = D;
   p.n_tiles = G > 0 ? pl.n_tiles : 0;
   p.m_blocks = pl.m_blocks;
   p.n_split = pl.n_split;
   p.tiles_per_split = pl.tiles_per_split;
+  p.n_items = pl.n_items;
+  p.max_lists = pl.slots;
   p.cand_s = cand_s;
   p.cand_i = cand_i;
   if (int rc = make_tmap(G > 0 ? g_bf16 : q_bf16, G > 0 ? G : Q, D, BN, &tg)) return rc;
   int rc;
-  if (pl.kp == 16) rc = resident ? launch_tc<true, 16>(tq, tg, p, st) : launch_tc<false, 16>(tq, tg, p, st);
-  else             rc = resident ? launch_tc<true, 32>(tq, tg, p, st) : launch_tc<false, 32>(tq, tg, p, st);
+  const int n_ctas = linear ? pl.n_ctas : pl.m_blocks * pl.n_split;
+  // key lists (cheap list warm-up) where a list lives for at most 16 tiles: the small problems whose time is set by the warm-up
+  const bool keys = pl.kp == 16 && tuning("sim_keys") != 1 && (linear || pl.tiles_per_split <= kKeyMaxTiles);
+  if (linear)                   rc = launch_tc<false, 16, true, true>(tq, tg, p, n_ctas, st);
+  else if (pl.kp == 16 && keys) rc = resident ? launch_tc<true, 16, true>(tq, tg, p, n_ctas, st) : launch_tc<false, 16, true>(tq, tg, p, n_ctas, st);
+  else if (pl.kp == 16)         rc = resident ? launch_tc<true, 16, false>(tq, tg, p, n_ctas, st) : launch_tc<false, 16, false>(tq, tg, p, n_ctas, st);
+  else                          rc = resident ? launch_tc<true, 32, false>(tq, tg, p, n_ctas, st) : launch_tc<false, 32, false>(tq, tg, p, n_ctas, st);
   if (rc) return rc;
+  if (tuning("sim_debug") == 3) return CVPCE_OK;  // TEMPORARY experiment: time the search without the selection kernel
+  SelLists sl;
+  sl.linear = linear ? 1 : 0;
+  sl.stride = pl.slots;
+  sl.n_lists0 = pl.n_split;
+  sl.n_tiles = p.n_tiles;
+  sl.n_ctas = n_ctas;
+  sl.n_items = p.n_items;
   const int grid = (Q + kSelWarps - 1) / kSelWarps;
   if (kp == 16)
-    sim_select_kernel<16><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
+    sim_select_kernel<16><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, sl, k, idx_base, D, keys ? 0.00049f : 0.f, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
   else
-    sim_select_kernel<32><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, pl.n_split, k, idx_base, D, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
+    sim_select_kernel<32><<<grid, kSelWarps * 32, 0, st>>>(cand_s, cand_i, Q, sl, k, idx_base, D, 0.f, q_f32, g_f32, q_inv_norm, g_inv_norm, targets);
   CVPCE_LAUNCH_OK("sim_select_kernel");
   return CVPCE_OK;
 }

@@ -377,8 +377,10 @@ def test_sim_topk_tensor_core_vs_oracle(ops, Q, G, D, k):
 
 @pytest.mark.parametrize("Q,G,D,k", [(1300, 5000, 1024, 5), (2000, 3000, 512, 5), (700, 20000, 64, 1), (1500, 6000, 256, 20)])
 def test_sim_topk_gallery_split_counts_agree(ops, Q, G, D, k):
-    """The tcgen05 search gives the same bits whatever the number of gallery splits (candidate lists per row) the plan or a
-    tuning override selects; exact mode also equals the fp32 CUDA-core kernel."""
+    """The tcgen05 search gives the same bits in exact mode whatever distributes the work: the number of gallery splits
+    (candidate lists per row) the plan or a tuning override selects, the (query block, split) grid or linear item ranges over
+    all SMs (a CTA's range crosses query blocks: several list lifetimes per CTA, a varying number of lists per row), key lists
+    or compare / select lists; exact mode also equals the fp32 CUDA-core kernel."""
     from cvpce_b200 import _lib
     rs = np.random.RandomState(Q + G + D)
     g = synth.unit_rows(rs, G, D, nonneg=(D == 1024))
@@ -387,8 +389,8 @@ def test_sim_topk_gallery_split_counts_agree(ops, Q, G, D, k):
     qb, qinv = ops.rows_prepare(gq)
     gb, ginv = ops.rows_prepare(gg)
     ref = None
-    for split in (0, 1, 2, 3, 7):
-        with _lib.tuning(sim_split=split):
+    for split in ({}, {"sim_split": 1}, {"sim_split": 2}, {"sim_split": 3}, {"sim_split": 7}, {"sim_plan": 1}, {"sim_plan": 2}):
+        with _lib.tuning(**split):
             exact = ops.sim_topk(qb, gb, k, 7, gq, gg, qinv, ginv)
             approx = ops.sim_topk(qb, gb, k, 7)
         torch.cuda.synchronize()
@@ -398,7 +400,13 @@ def test_sim_topk_gallery_split_counts_agree(ops, Q, G, D, k):
             assert (i32 == exact[1]).float().mean().item() > 0.999
         else:
             assert torch.equal(exact[0], ref[0][0]) and torch.equal(exact[1], ref[0][1]), split
-            assert torch.equal(approx[0], ref[1][0]) and torch.equal(approx[1], ref[1][1]), split
+            # bf16-only scores: lists that live for <= 16 tiles are kept as keys (scores truncated to 11 mantissa bits, ties
+            # by column), longer ones in full precision: the same rows up to near-ties below that resolution
+            assert (approx[1] == ref[1][1]).float().mean().item() > 0.98, split
+            np.testing.assert_allclose(approx[0].cpu().numpy(), ref[1][0].cpu().numpy(), rtol=6e-4, atol=1e-6)
+    with _lib.tuning(sim_keys=1):                                     # key lists off: the full-precision lists everywhere
+        exact = ops.sim_topk(qb, gb, k, 7, gq, gg, qinv, ginv)
+    assert torch.equal(exact[0], ref[0][0]) and torch.equal(exact[1], ref[0][1])
 
 
 def test_sim_topk_shard_offsets_and_merge(ops):
