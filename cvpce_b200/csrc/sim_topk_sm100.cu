@@ -637,6 +637,7 @@ struct OutTargets {
 // index asc); indices are unique across the lists of a row.
 
 constexpr int kSelWarps = 4;
+constexpr int kSelBitonicLists = 8;  // up to this many lists per row are folded in by bitonic merges
 constexpr int kSelMaxCand = 512;  // candidates of a row staged in shared memory (more take the serial merge)
 
 // exact fp32 re-score of the first n_rescore candidates of a row (lane c holds candidate c in my_i and receives its score)
@@ -649,25 +650,48 @@ __device__ __forceinline__ void rescore_rows(const float* __restrict__ qr, const
     const int d = u * 128 + lane * 4;
     qv[u] = (FULL || d < D) ? *reinterpret_cast<const float4*>(qr + d) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  for (int c = 0; c < n_rescore; ++c) {
-    const int gi = __shfl_sync(0xffffffffu, my_i, c);
-    const float* gr = g32 + (size_t)gi * D + lane * 4;
-    const float ginv = g_inv ? __ldg(g_inv + gi) : 1.f;
-    float4 gv[8];
+  // 16 candidates per pass, fully unrolled: the per-lane partial sums of all of them are then reduced together by a
+  // reduce-scatter butterfly (16 shuffles for 16 candidates instead of 5 each; the same pairing order 16-8-4-2-1 as warp_sum,
+  // so every score has the bits a per-candidate butterfly gives).  Candidate c of the pass ends up in lanes 2c and 2c+1.
+  for (int base = 0; base < n_rescore; base += 16) {  // warp-uniform (a second pass only with 32-entry lists)
+    float part[16];
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      gv[u] = (FULL || u * 128 + lane * 4 < D) ? __ldg(reinterpret_cast<const float4*>(gr + u * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    float ax = 0.f, ay = 0.f, az = 0.f, aw = 0.f;
+    for (int c = 0; c < 16; ++c) {
+      part[c] = 0.f;
+      if (base + c < n_rescore) {
+        const int gi = __shfl_sync(0xffffffffu, my_i, base + c);
+        const float* gr = g32 + (size_t)gi * D + lane * 4;
+        float4 gv[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      ax = fmaf(qv[u].x, gv[u].x, ax);
-      ay = fmaf(qv[u].y, gv[u].y, ay);
-      az = fmaf(qv[u].z, gv[u].z, az);
-      aw = fmaf(qv[u].w, gv[u].w, aw);
+        for (int u = 0; u < 8; ++u)
+          gv[u] = (FULL || u * 128 + lane * 4 < D) ? __ldg(reinterpret_cast<const float4*>(gr + u * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float ax = 0.f, ay = 0.f, az = 0.f, aw = 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          ax = fmaf(qv[u].x, gv[u].x, ax);
+          ay = fmaf(qv[u].y, gv[u].y, ay);
+          az = fmaf(qv[u].z, gv[u].z, az);
+          aw = fmaf(qv[u].w, gv[u].w, aw);
+        }
+        part[c] = (ax + ay) + (az + aw);
+      }
     }
-    const float acc = warp_sum((ax + ay) + (az + aw));
-    const float sc = acc * qi * ginv;
-    if (lane == c) my_s = sc;
+#pragma unroll
+    for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+#pragma unroll
+      for (int j = 0; j < half; ++j) {
+        const bool up = (lane & bit) != 0;
+        const float send = up ? part[j] : part[j + half];
+        const float keep = up ? part[j + half] : part[j];
+        part[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+      }
+    }
+    part[0] += __shfl_xor_sync(0xffffffffu, part[0], 1);
+    const float tot = __shfl_sync(0xffffffffu, part[0], (2 * (lane - base)) & 31);
+    if (lane >= base && lane < base + 16 && lane < n_rescore) {
+      const float ginv = g_inv ? __ldg(g_inv + my_i) : 1.f;
+      my_s = tot * qi * ginv;
+    }
   }
 }
 
@@ -709,6 +733,41 @@ __global__ void __launch_bounds__(kSelWarps * 32) sim_select_kernel(const float*
       my_s = cs[lane];
       my_i = ci[lane];
     }
+  } else if (n_lists <= kSelBitonicLists) {
+    // few lists: fold them in one after the other.  The running best-KP sits in lanes 0..KP-1 in descending order; lane j takes
+    // entry KP-1-j of the next list, the element-wise maximum of the two is a bitonic sequence holding the KP best of both, and
+    // log2(KP) shuffle stages sort it again (~50 instructions per list; ranking every candidate in every other list by binary
+    // search cost ~600 per row with four lists)
+    float rs = -INFINITY;
+    int ri = -1;
+    if (lane < KP) {
+      rs = cs[lane];
+      ri = ci[lane];
+    }
+    for (int l = 1; l < n_lists; ++l) {
+      float bs = -INFINITY;
+      int bi = -1;
+      if (lane < KP) {
+        bs = cs[l * KP + (KP - 1 - lane)];
+        bi = ci[l * KP + (KP - 1 - lane)];
+      }
+      if (before(bs, bi, rs, ri)) {
+        rs = bs;
+        ri = bi;
+      }
+#pragma unroll
+      for (int j = KP / 2; j > 0; j >>= 1) {
+        const float os = __shfl_xor_sync(0xffffffffu, rs, j);
+        const int oi = __shfl_xor_sync(0xffffffffu, ri, j);
+        const bool take = (lane & j) == 0 ? before(os, oi, rs, ri) : before(rs, ri, os, oi);
+        if (take) {
+          rs = os;
+          ri = oi;
+        }
+      }
+    }
+    my_s = rs;
+    my_i = ri;
   } else if (C <= kSelMaxCand) {
     // merge by rank: all candidates into shared memory (coalesced), then every candidate finds its overall rank = its position
     // in its own list + the number of entries of every other list that precede it (binary search: the lists are sorted in
