@@ -54,6 +54,7 @@ SIGNATURES = {
                                         c_float, c_void_p, c_int64, c_void_p]),
     "cvpce_region_pool_embed_ws": (c_int, [ctypes.POINTER(FeatureMap), c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                            c_float, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
+    "cvpce_region_pool_embed_static": (c_int, [ctypes.POINTER(FeatureMap), c_int, c_int, c_int, c_int, c_float, c_void_p, c_int64, c_void_p]),
     "cvpce_region_pool_workspace_bytes": (c_int64, [ctypes.POINTER(FeatureMap), c_int, c_int, c_int]),
     "cvpce_box_iou": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "cvpce_iou_match": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p,

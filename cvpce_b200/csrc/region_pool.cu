@@ -22,6 +22,7 @@
 #include <cooperative_groups.h>
 #include <math.h>
 #include <algorithm>
+#include <mutex>
 
 namespace cg = cooperative_groups;
 
@@ -1036,6 +1037,63 @@ extern "C" int cvpce_region_pool_embed_ws(const cvpce_feature_map* maps, int n_m
                                           void* workspace, int64_t workspace_bytes, void* stream) {
   return region_pool_impl(maps, n_maps, dtype, B, regions, n_regions, per_region_l2, final_l2, eps, out, out_stride, workspace,
                           workspace_bytes > 0 ? (size_t)workspace_bytes : 0, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free form of the balanced streaming MAC kernel: its scratch (per-image counters + per-segment maxima) lives in a
+// file-scope device array that every GPU loading the library holds until exit, so that callers which cannot call cudaMalloc
+// (CUDA graph capture, serving loops, harnesses that forbid it) need no workspace.  Only host code needs the array's
+// ADDRESS: the name below is a host-side stand-in there, so the device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and cached.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace cvpce {
+
+static __device__ __align__(256) unsigned char g_mac_static_scratch[CVPCE_POOL_STATIC_SCRATCH_BYTES];
+
+static std::mutex g_mac_static_mutex;
+static void* g_mac_static_addr[64];  // device address of the array per device ordinal (nullptr: not looked up yet)
+
+static int mac_static_scratch(void** out) {
+  int dev = 0;
+  CVPCE_CUDA_OK(cudaGetDevice(&dev));
+  CVPCE_REQUIRE(dev >= 0 && dev < 64, CVPCE_ERR_UNSUPPORTED, "region_pool_static: device ordinal %d outside [0,64)", dev);
+  std::lock_guard<std::mutex> lock(g_mac_static_mutex);
+  if (!g_mac_static_addr[dev]) {
+    void* ptr = nullptr;
+    CVPCE_CUDA_OK(cudaGetSymbolAddress(&ptr, g_mac_static_scratch));  // the current device's instance of the array
+    CVPCE_REQUIRE(ptr != nullptr, CVPCE_ERR_CUDA, "region_pool_static: cudaGetSymbolAddress returned a null address");
+    g_mac_static_addr[dev] = ptr;
+  }
+  *out = g_mac_static_addr[dev];
+  return CVPCE_OK;
+}
+
+}  // namespace cvpce
+
+extern "C" int cvpce_region_pool_embed_static(const cvpce_feature_map* maps, int n_maps, int dtype, int B, int final_l2, float eps,
+                                              float* out, int64_t out_stride, void* stream) {
+  using namespace cvpce;
+  CVPCE_REQUIRE(maps && n_maps >= 1 && n_maps <= CVPCE_POOL_MAX_MAPS, CVPCE_ERR_INVALID_ARG, "region_pool_static: n_maps=%d out of [1,%d]", n_maps, CVPCE_POOL_MAX_MAPS);
+  CVPCE_REQUIRE(dtype == CVPCE_F32 || dtype == CVPCE_BF16 || dtype == CVPCE_F16, CVPCE_ERR_INVALID_ARG, "region_pool_static: bad dtype %d", dtype);
+  CVPCE_REQUIRE(B >= 0, CVPCE_ERR_INVALID_ARG, "region_pool_static: B=%d", B);
+  if (B == 0) return CVPCE_OK;
+  CVPCE_REQUIRE(mac_dense_nhwc(maps, n_maps, dtype), CVPCE_ERR_UNSUPPORTED,
+                "region_pool_static: only dense channels-last MAC maps (unit channel stride, stride_w == C, stride_h == W*C, 16-byte aligned, "
+                "C*elemsize/16 dividing 256, sum of C <= %d) run the streaming kernel this entry point exists for", kMacMaxCols);
+  MacStreamPlan w;
+  size_t counter_bytes = 0, total_bytes = 0;
+  mac_stream_plan(maps, n_maps, dtype, B, &w, &counter_bytes, &total_bytes);
+  CVPCE_REQUIRE(total_bytes <= (size_t)CVPCE_POOL_STATIC_SCRATCH_BYTES, CVPCE_ERR_UNSUPPORTED,
+                "region_pool_static: this batch needs %zu bytes of scratch, the static array holds %d (CVPCE_POOL_STATIC_SCRATCH_BYTES): "
+                "split the batch or use cvpce_region_pool_embed_ws", total_bytes, CVPCE_POOL_STATIC_SCRATCH_BYTES);
+  if (int rc = require_sm100()) return rc;
+  void* scratch = nullptr;
+  if (int rc = mac_static_scratch(&scratch)) return rc;
+  // the array keeps the last call's contents: the counters must start at zero (a call that failed half-way, or another
+  // process-wide user, may have left them otherwise); the segment rows are written before they are read
+  CVPCE_CUDA_OK(cudaMemsetAsync(scratch, 0, (size_t)B * sizeof(unsigned), (cudaStream_t)stream));
+  return region_pool_impl(maps, n_maps, dtype, B, nullptr, nullptr, 0, final_l2, eps, out, out_stride, scratch,
+                          (size_t)CVPCE_POOL_STATIC_SCRATCH_BYTES, stream);
 }
 
 extern "C" int cvpce_l2norm_rows(float* x, int B, int D, int64_t stride, float eps, void* stream) {

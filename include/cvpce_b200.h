@@ -204,6 +204,22 @@ CVPCE_API int cvpce_region_pool_embed_ws(const cvpce_feature_map* maps, int n_ma
                                int per_region_l2, int final_l2, float eps,
                                float* out, int64_t out_stride,
                                void* workspace, int64_t workspace_bytes, void* stream);
+/* Allocation-free MAC pooling.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as cvpce_region_pool_embed(maps, ..., regions = NULL, n_regions = NULL, per_region_l2 = 0, ...) -- one whole-map
+ * region per map, the reference's MAC mode -- through the balanced streaming kernel, whose scratch is a file-scope device
+ * array of CVPCE_POOL_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  The call makes no
+ * cudaMalloc / cudaFree and calls no allocating routine; the caller passes inputs and outputs only.
+ * Limits: dense channels-last maps only (unit channel stride, stride_w == C, stride_h == W*C, 16-byte aligned data,
+ *      C*elemsize/16 dividing 256, sum of C <= 4096), and cvpce_region_pool_workspace_bytes(maps, n_maps, dtype, B) <=
+ *      CVPCE_POOL_STATIC_SCRATCH_BYTES (B = 256 images of two 512 x 16 x 16 f32 maps need 2.1 MB); anything else returns
+ *      CVPCE_ERR_UNSUPPORTED with the limit in the message.
+ * Sharing: every call on a device uses the SAME array.  Calls ordered on one stream (or otherwise serialised on the GPU)
+ *      are safe -- the entry point clears the counters it needs on `stream` before the kernel; calls that overlap on the
+ *      GPU (different streams, different host threads without ordering) RACE on it and give wrong results. */
+#define CVPCE_POOL_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+CVPCE_API int cvpce_region_pool_embed_static(const cvpce_feature_map* maps, int n_maps, int dtype, int B,
+                                   int final_l2, float eps, float* out, int64_t out_stride, void* stream);
 /* [host] R-MAC region grid of Tolias et al. for an H x W map and `levels` scales; returns the region count and
  * writes up to max_regions (y0,x0,y1,x1) quadruples. */
 CVPCE_API int cvpce_rmac_regions(int H, int W, int levels, int32_t* regions, int max_regions);
