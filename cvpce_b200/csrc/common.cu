@@ -72,7 +72,6 @@ static TuningEntry g_tuning[] = {
     {"crop_band_rows", {0}},    // 0: automatic; else output rows per CTA of the antialias kernels (power of two, 8..256; column-marching kernel)
     {"sim_split", {0}},         // tcgen05 search: forced gallery split count (0: cost model)
     {"sim_plan", {0}},          // tcgen05 search: 0 automatic; 1: (query block, split) grid; 2: linear item ranges whenever legal
-    {"sim_debug", {0}},
     {"sim_keys", {0}},          // tcgen05 search: 0 automatic (key lists when a list lives for <= 16 tiles); 1: never
     {"mac_cluster", {0}},       // 0: automatic; 2 / 4 / 8: cluster size of the dense channels-last MAC cluster kernel
     {"mac_kernel", {0}},        // 0: automatic (balanced streaming kernel when a workspace is given); 1: always the cluster kernel

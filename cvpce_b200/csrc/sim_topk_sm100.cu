@@ -11,19 +11,26 @@
 //   warp 2      TMEM allocator
 //   warps 4-7   epilogue: tcgen05.ld gives every thread one complete query row of the tile (lane == row), so each thread
 //               keeps its row's running top-k' (sorted, in registers) with NO cross-thread traffic; a value is compared
-//               against the current k'-th score first, so the common case costs one compare per similarity
-//   grid = (query blocks of 128) x (gallery splits); each CTA writes its k' candidates per row to a small workspace.
+//               against the current k'-th score first, so the common case costs one compare per similarity.
+//               Two list forms: KEY lists (k' = 16 and list lifetimes of <= 16 tiles: a candidate is one float -- the score
+//               with the column in its low 12 mantissa bits -- kept sorted with min / max alone, a whole 32-column chunk
+//               merged by a sorting network while the list warms up) and compare / select (score, index) lists otherwise.
+//   work        grid form: CTA = (query block, gallery split); linear form (key lists, operands L2-resident): the
+//               (query block, tile) items are cut into equal contiguous ranges over all SMs, a range crossing query blocks
+//               restarts its lists (cheap with key lists).  Each CTA writes k' candidates per row and piece to a workspace slot.
 // Kernel 2  sim_select_kernel    (one warp per query row)
-//   merges the splits' candidate lists by rank (every candidate finds its overall rank with binary searches in the other
-//   sorted lists), re-scores in exact fp32, from the fp32 operands (parity mode), the prefix of the survivors that the bf16
-//   error bound cannot exclude from the top-k, and writes the final top-k ordered by (similarity desc, gallery index asc).
+//   merges the row's candidate lists (few lists: bitonic folding through shuffles; more: rank by binary search in shared
+//   memory), re-scores in exact fp32, from the fp32 operands (parity mode), the prefix of the survivors that the bf16 (+ key
+//   truncation) error bound cannot exclude from the top-k -- query row in registers, 16 candidates per pass, their partial sums
+//   reduced together by a reduce-scatter butterfly -- and writes the final top-k ordered by (similarity desc, index asc).
 //
-// Round-2 measurements that shaped this file (profiles/r2*_kbench_sim_*.jsonl, r2p_sim_launches_ncu_*.csv):
-//   the MMA + TMA pipeline alone sustains 0.86-0.93 of the measured cuBLAS burst rate; what costs the rest is the epilogue's
-//   per-row list maintenance (one warp per scheduler executing a long dependent instruction stream at every list warm-up).
-//   A persistent CTA-pair variant (tcgen05 cta_group::2, each CTA holding half of the gallery tile) and a cluster-multicast
-//   variant were built, validated bit-identical and measured: no faster, because operand feed is not the limiter; they are
-//   kept as evidence under profiles/r2_experiments/, not in the product.
+// Measurements that shaped this file (profiles/r2*_sim_*, r3*_sim_*):
+//   a single-CTA tcgen05.mma reads 96 of the SM's 128 B/clk of shared memory: 75 % tensor-pipe ceiling, reached at the
+//   1M-gallery shard shape (0.95 of the sustained cuBLAS rate).  At the small C3 shape the time was list warm-up (~17 us per
+//   list restart with compare / select lists), 100 of 148 SMs busy, and a selection kernel as long as half the search: key
+//   lists + linear ranges + the re-score rewrite took it from 0.1506 to 0.1157 ms on the same box, results bit-identical.
+//   CTA pairs (cta_group::2), TMA multicast, a persistent pair grid, 8 / 16 epilogue warps, pipelined TMEM loads and a deferred
+//   insert queue were built, validated and measured without gain; they are kept under profiles/r2_experiments/, not here.
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>
@@ -1147,7 +1154,6 @@ static int sim_topk_impl(const void* q_bf16, const void* g_bf16, int Q, int G, i
   else if (pl.kp == 16)         rc = resident ? launch_tc<true, 16, false>(tq, tg, p, n_ctas, st) : launch_tc<false, 16, false>(tq, tg, p, n_ctas, st);
   else                          rc = resident ? launch_tc<true, 32, false>(tq, tg, p, n_ctas, st) : launch_tc<false, 32, false>(tq, tg, p, n_ctas, st);
   if (rc) return rc;
-  if (tuning("sim_debug") == 3) return CVPCE_OK;  // TEMPORARY experiment: time the search without the selection kernel
   SelLists sl;
   sl.linear = linear ? 1 : 0;
   sl.stride = pl.slots;

@@ -7,6 +7,5 @@ OLD=$PWD/cvpce_b200/variants/libold.so
 for rep in 1 2; do
   CVPCE_B200_SO=$OLD timeout 300 python tools/sim_ab.py >> $OUT/sim_ab.jsonl 2>> $OUT/sim_ab.err
   timeout 300 python tools/sim_ab.py >> $OUT/sim_ab.jsonl 2>> $OUT/sim_ab.err
-  timeout 300 python tools/sim_ab.py --tune sim_debug=3 >> $OUT/sim_ab.jsonl 2>> $OUT/sim_ab.err
 done
 cat $OUT/sim_ab.jsonl
