@@ -66,6 +66,32 @@ def test_argument_validation_on_host(lib):
     assert lib.cvpce_topk_merge(None, None, 0, 4, 1, None, None, None) == 1
 
 
+def test_workspace_planners_on_host(lib):
+    """The workspace-size entry points are pure host arithmetic (the launch plans): exercised here without a GPU."""
+    from cvpce_b200 import _lib
+    # tcgen05 search: grows with Q, covers the linear-range plan's slots at the C3 shape and the split plan of the 1M-gallery shard
+    c3 = lib.cvpce_sim_topk_workspace_bytes(6400, 8192, 1024, 5)
+    c5 = lib.cvpce_sim_topk_workspace_bytes(100000, 125000, 512, 5)
+    assert c3 >= 6400 * 16 * 8 and c5 >= 100000 * 16 * 8 and c5 > c3
+    assert lib.cvpce_sim_topk_workspace_bytes(0, 10, 64, 1) == 0 and lib.cvpce_sim_topk_workspace_bytes(10, 10, 64, 33) == 0
+    # MAC streaming kernel: only dense channels-last maps have a streaming plan; the size grows with the batch
+    def fmap(C, H, W, nhwc=True, ptr=0x10000):
+        return _lib.FeatureMap(ptr, C, H, W, C * H * W, 1 if nhwc else H * W, W * C if nhwc else W, C if nhwc else 1)
+    maps = (_lib.FeatureMap * 2)(fmap(512, 16, 16), fmap(512, 16, 16))
+    w256 = lib.cvpce_region_pool_workspace_bytes(maps, 2, 0, 256)
+    w512 = lib.cvpce_region_pool_workspace_bytes(maps, 2, 0, 512)
+    assert 65536 < w256 < w512 <= 8 * 1024 * 1024            # both fit the static scratch of cvpce_region_pool_embed_static
+    assert lib.cvpce_region_pool_workspace_bytes((_lib.FeatureMap * 1)(fmap(512, 16, 16, nhwc=False)), 1, 0, 256) == 0
+    assert lib.cvpce_region_pool_workspace_bytes((_lib.FeatureMap * 1)(fmap(512, 16, 16, ptr=0x10004)), 1, 0, 256) == 0   # misaligned
+    assert lib.cvpce_region_pool_workspace_bytes((_lib.FeatureMap * 1)(fmap(6, 3, 3)), 1, 0, 4) == 0                     # C not a vector multiple
+    assert lib.cvpce_region_pool_workspace_bytes(maps, 2, 0, 0) == 0
+    # the allocation-free entry point validates on the host before touching the device
+    assert lib.cvpce_region_pool_embed_static(None, 1, 0, 4, 1, 1e-8, None, 0, None) == 1
+    assert lib.cvpce_region_pool_embed_static(maps, 2, 0, 0, 1, 1e-8, None, 0, None) == 0
+    assert lib.cvpce_region_pool_embed_static((_lib.FeatureMap * 1)(fmap(512, 16, 16, nhwc=False)), 1, 0, 4, 1, 1e-8, None, 0, None) == 2
+    assert lib.cvpce_region_pool_embed_static(maps, 2, 0, 100000, 1, 1e-8, None, 0, None) == 2 and "static array" in _lib.last_error()
+
+
 def test_threshold_rounding_helper():
     import numpy as np
     assert ops.threshold_as_cpu_op(0.5) == 0.5
