@@ -159,6 +159,88 @@ def test_search_kernels_stay_inside_their_outputs(guarded):
     ops.l2norm_rows_(x)
 
 
+def test_streaming_mac_stays_inside_an_exactly_sized_workspace(guarded):
+    """cvpce_region_pool_embed_ws with a workspace of EXACTLY cvpce_region_pool_workspace_bytes between guard zones (the Python
+    wrapper's cached workspace is rounded up, which would hide an overrun of the per-segment rows): batch sizes from one image
+    (fewer chunks than CTAs) to images straddling many CTA ranges, other grid sizes, ragged pixel counts."""
+    import ctypes
+    from cvpce_b200 import _lib
+    ops, g = guarded
+    lib = _lib.load()
+    gen = torch.Generator(device="cuda").manual_seed(4)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for B, shapes in ((1, [(512, 16, 16), (512, 16, 16)]), (2, [(1024, 3, 3)]), (37, [(512, 9, 7), (256, 5, 3), (1024, 2, 2)]),
+                      (300, [(512, 16, 16), (512, 8, 8)]), (1000, [(64, 5, 5)])):
+        feats = [torch.randn((B, c, h, w), device="cuda", generator=gen).contiguous(memory_format=torch.channels_last) for c, h, w in shapes]
+        maps = (_lib.FeatureMap * len(feats))()
+        for i, f in enumerate(feats):
+            maps[i] = _lib.FeatureMap(f.data_ptr(), f.shape[1], f.shape[2], f.shape[3], f.stride(0), f.stride(1), f.stride(2), f.stride(3))
+        want = torch.cat([f.amax(dim=(2, 3)) for f in feats], dim=1)
+        for per_sm in (0, 1, 5):
+            with _lib.tuning(mac_ctas_per_sm=per_sm):
+                need = int(lib.cvpce_region_pool_workspace_bytes(maps, len(feats), 0, B))
+                assert need > 0
+                ws = g.zeros((need,), dtype=torch.uint8, device="cuda")
+                out = g.empty((B, want.shape[1]), dtype=torch.float32, device="cuda")
+                for _ in range(2):                            # the counters are left at zero: a second launch on the same workspace
+                    rc = lib.cvpce_region_pool_embed_ws(maps, len(feats), 0, B, None, None, 0, 0, 1e-8, ctypes.c_void_p(out.data_ptr()),
+                                                        out.stride(0), ctypes.c_void_p(ws.data_ptr()), need, stream)
+                    assert rc == 0, _lib.last_error()
+                    torch.cuda.synchronize()
+                    assert torch.equal(out, want), (B, shapes, per_sm)
+                assert int(ws[:4 * B].view(torch.int32).abs().sum()) == 0
+                g.check("streaming MAC B=%d %s ctas/sm=%d" % (B, shapes, per_sm))
+                rc = lib.cvpce_region_pool_embed_ws(maps, len(feats), 0, B, None, None, 0, 0, 1e-8, ctypes.c_void_p(out.data_ptr()),
+                                                    out.stride(0), ctypes.c_void_p(ws.data_ptr()), need - 1, stream)
+                assert rc == 1 and "workspace" in _lib.last_error()      # one byte short: refused, nothing launched
+
+
+def test_tcgen05_search_stays_inside_the_smallest_workspace_it_accepts(guarded):
+    """cvpce_sim_topk_workspace_bytes is a generous upper bound (any tuning override must fit), which would hide a candidate list
+    written past the slots the launch plan really uses.  The entry point refuses a workspace smaller than its plan needs, so the
+    smallest accepted size is found by bisection and the search then runs in exactly that much memory between guard zones:
+    linear item ranges (several slots per row, a varying number per query block), split grids, both list forms."""
+    import ctypes
+    from cvpce_b200 import _lib
+    ops, g = guarded
+    gen = torch.Generator(device="cuda").manual_seed(6)
+    for Q, G, D, k, knobs in ((1300, 5000, 1024, 5, {}), (700, 3000, 256, 3, {"sim_plan": 2}), (2000, 3000, 512, 5, {}), (257, 40000, 512, 5, {}),
+                              (900, 9000, 128, 5, {"sim_split": 5}), (1500, 6000, 256, 20, {})):
+        q = torch.randn((Q, D), device="cuda", generator=gen)
+        gal = torch.randn((G, D), device="cuda", generator=gen)
+        qb, qi = ops.rows_prepare(q)
+        gb, gi = ops.rows_prepare(gal)
+        g.check("rows_prepare")
+        lib = _lib.load()
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        P = lambda t: ctypes.c_void_p(t.data_ptr())
+
+        def call(ws_tensor, nbytes, out_s, out_i):
+            return lib.cvpce_sim_topk(P(qb), P(gb), Q, G, D, k, 3, P(q), P(gal), P(qi), P(gi), P(out_s), P(out_i), P(ws_tensor), nbytes, stream)
+
+        with _lib.tuning(**knobs):
+            hi = ops.sim_topk_workspace_bytes(Q, G, D, k)
+            big = torch.empty(hi, dtype=torch.uint8, device="cuda")
+            ws_s, ws_i = torch.empty((Q, k), device="cuda"), torch.empty((Q, k), dtype=torch.int64, device="cuda")
+            assert call(big, hi, ws_s, ws_i) == 0, _lib.last_error()
+            lo = 0                                             # invariant: lo bytes are refused, hi bytes are accepted
+            while hi - lo > 1:
+                mid = (lo + hi) // 2
+                rc = call(big, mid, ws_s, ws_i)
+                assert rc in (0, 5), _lib.last_error()         # CVPCE_ERR_WORKSPACE: refused before any launch
+                if rc == 0:
+                    hi = mid
+                else:
+                    lo = mid
+            torch.cuda.synchronize()
+            ws = g.empty((hi,), dtype=torch.uint8, device="cuda")
+            got_s, got_i = g.empty((Q, k), dtype=torch.float32, device="cuda"), g.empty((Q, k), dtype=torch.int64, device="cuda")
+            assert call(ws, hi, got_s, got_i) == 0, _lib.last_error()
+            torch.cuda.synchronize()
+            assert torch.equal(got_s, ws_s) and torch.equal(got_i, ws_i)
+            g.check("sim_topk in its smallest workspace (%d bytes) Q=%d G=%d D=%d k=%d %s" % (hi, Q, G, D, k, knobs))
+
+
 def test_guard_zones_do_detect_an_overrun(guarded):
     _, g = guarded
     v = g.empty((5, 3), dtype=torch.float32, device="cuda")
