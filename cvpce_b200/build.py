@@ -11,7 +11,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libcvpce_b200.so")
-SOURCES = ["common.cu", "nms.cu", "select_candidates.cu", "iou_match.cu", "crop_resize.cu", "region_pool.cu", "maxpool.cu", "sim_topk_f32.cu", "sim_topk_sm100.cu"]
+SOURCES = ["common.cu", "nms.cu", "select_candidates.cu", "iou_match.cu", "crop_resize.cu", "region_pool.cu", "rmac_staged.cu", "maxpool.cu", "sim_topk_f32.cu", "sim_topk_sm100.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",

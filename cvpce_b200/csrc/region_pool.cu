@@ -948,6 +948,12 @@ static int region_pool_impl(const cvpce_feature_map* maps, int n_maps, int dtype
   CVPCE_REQUIRE((long long)B * kPoolCluster < 2147483647ll, CVPCE_ERR_UNSUPPORTED, "region_pool: B too large");
 
   const bool general = !all_whole || per_region_l2;
+  if (general) {
+    // region lists / per-region L2 (R-MAC): the persistent TMA-staged kernel (rmac_staged.cu) when the maps are dense and the
+    // batch is large enough to give every SM whole images; the cluster kernel below otherwise
+    const int rc = rmac_staged_launch(maps, n_maps, dtype, B, regions, n_regions, per_region_l2, final_l2, eps, out, out_stride, stream);
+    if (rc != kRmacNotApplicable) return rc;
+  }
   bool all_nhwc = true;
   for (int m = 0; m < n_maps; ++m) all_nhwc = all_nhwc && p.maps[m].nhwc;
   // dense channels-last MAC: the pixel-split streaming kernel

@@ -291,6 +291,86 @@ def test_rmac_vgg_shapes_layouts_dtypes(ops, hw):
                                    rtol=1e-5, atol=1e-7)
 
 
+def _rmac_both_kernels(ops, feats, **kw):
+    """The same call through the persistent TMA-staged kernel (forced) and through the cluster kernel."""
+    from cvpce_b200 import _lib
+    with _lib.tuning(rmac_kernel=2):
+        staged = ops.region_pool_embed(feats, **kw).cpu().numpy()
+    with _lib.tuning(rmac_kernel=1):
+        cluster = ops.region_pool_embed(feats, **kw).cpu().numpy()
+    return staged, cluster
+
+
+@pytest.mark.parametrize("hw", [(32, 16), (28, 14)])
+def test_rmac_staged_kernel_vgg_shapes_layouts_dtypes(ops, hw):
+    """rmac_staged.cu (ring of cp.async.bulk stages, one persistent CTA per image) against the oracle and against the cluster
+    kernel on the VGG maps: NCHW, channels-last and mixed layouts, f32 and bf16, R-MAC levels 3 and 4, raw sums."""
+    rs = np.random.RandomState(100 + hw[0])
+    B = 7
+    f4 = rs.randn(B, 512, hw[0], hw[0]).astype(np.float32)  # signed values: nothing relies on ReLU outputs
+    f5 = np.maximum(rs.randn(B, 512, hw[1], hw[1]), 0).astype(np.float32)
+    g4, g5 = dev(f4), dev(f5)
+    c4, c5 = g4.contiguous(memory_format=torch.channels_last), g5.contiguous(memory_format=torch.channels_last)
+    for levels in (3, 4):
+        regions = [oracle.rmac_regions(hw[0], hw[0], levels).tolist(), oracle.rmac_regions(hw[1], hw[1], levels).tolist()]
+        want = oracle.region_pool_embed([f4, f5], regions, per_region_l2=True)
+        want_raw = oracle.region_pool_embed([f4, f5], regions, per_region_l2=False, final_l2=False)
+        for a, b in ((g4, g5), (c4, c5), (g4, c5), (c4, g5)):
+            staged, cluster = _rmac_both_kernels(ops, [a, b], regions=regions, per_region_l2=True)
+            np.testing.assert_allclose(staged, want, rtol=1e-5, atol=1e-7)
+            np.testing.assert_allclose(staged, cluster, rtol=1e-5, atol=1e-7)
+            raw, raw_cluster = _rmac_both_kernels(ops, [a, b], regions=regions, per_region_l2=False, final_l2=False)
+            np.testing.assert_allclose(raw, want_raw, rtol=1e-6, atol=0)
+            assert np.array_equal(raw, raw_cluster)  # sums of exact maxima in the same region order
+    regions = [oracle.rmac_regions(hw[0], hw[0], 3).tolist(), oracle.rmac_regions(hw[1], hw[1], 3).tolist()]
+    b4, b5 = g4.bfloat16(), g5.bfloat16()
+    want_bf = oracle.region_pool_embed([b4.float().cpu().numpy(), b5.float().cpu().numpy()], regions, per_region_l2=True)
+    if (hw[1] * hw[1] * 2) % 16 == 0:  # bf16 NCHW planes must be whole 16-byte units for the bulk copies (else: cluster kernel)
+        layouts = ((b4, b5), (b4.contiguous(memory_format=torch.channels_last), b5.contiguous(memory_format=torch.channels_last)))
+    else:
+        layouts = ((b4.contiguous(memory_format=torch.channels_last), b5.contiguous(memory_format=torch.channels_last)),)
+    for a, b in layouts:
+        staged, cluster = _rmac_both_kernels(ops, [a, b], regions=regions, per_region_l2=True)
+        np.testing.assert_allclose(staged, want_bf, rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(staged, cluster, rtol=1e-5, atol=1e-7)
+    # a region list that leaves rows and columns uncovered, plus a whole-map second map with per-region L2
+    partial = [[(2, 3, 9, 11), (5, 1, hw[0] - 1, 8), (4, 4, 12, hw[0] - 2)], [(0, 0, hw[1], hw[1])]]
+    want_p = oracle.region_pool_embed([f4, f5], partial, per_region_l2=True)
+    for a, b in ((g4, g5), (c4, c5)):
+        staged, _ = _rmac_both_kernels(ops, [a, b], regions=partial, per_region_l2=True)
+        np.testing.assert_allclose(staged, want_p, rtol=1e-5, atol=1e-7)
+
+
+def test_rmac_staged_kernel_many_images_per_cta_and_odd_maps(ops):
+    """More images than SMs (every CTA walks several images and the ring runs across image boundaries), non-square maps,
+    narrow planes (two and four NCHW planes per warp pass), pixels smaller than a ring stage (chunks spanning rows),
+    three maps, an output row stride, and the automatic choice (staged kernel from B >= SMs/2)."""
+    from cvpce_b200 import _lib
+    rs = np.random.RandomState(5)
+    B = 333
+    feats = [rs.randn(B, 128, 14, 20).astype(np.float32), rs.randn(B, 256, 7, 12).astype(np.float32), rs.randn(B, 128, 5, 4).astype(np.float32)]
+    regions = [oracle.rmac_regions(f.shape[2], f.shape[3], 3).tolist() for f in feats]
+    want = oracle.region_pool_embed(feats, regions, per_region_l2=True)
+    nchw = [dev(f) for f in feats]
+    nhwc = [t.contiguous(memory_format=torch.channels_last) for t in nchw]
+    for maps in (nchw, nhwc, [nchw[0], nhwc[1], nchw[2]]):
+        staged, cluster = _rmac_both_kernels(ops, maps, regions=regions, per_region_l2=True)
+        np.testing.assert_allclose(staged, want, rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(staged, cluster, rtol=1e-5, atol=1e-7)
+        auto = ops.region_pool_embed(maps, regions=regions, per_region_l2=True).cpu().numpy()
+        assert np.array_equal(auto, staged)  # B >= SMs/2: the automatic choice is the staged kernel, which is deterministic
+        wide = torch.full((B, 600), -7.0, device="cuda")
+        with _lib.tuning(rmac_kernel=2):
+            ops.region_pool_embed(maps, regions=regions, per_region_l2=True, out=wide)
+        assert np.array_equal(wide[:, :512].cpu().numpy(), staged) and bool((wide[:, 512:] == -7.0).all())
+    # fewer ring stages than chunks per image, down to the minimum of two
+    base, _ = _rmac_both_kernels(ops, nhwc, regions=regions, per_region_l2=True)
+    for stages in (2, 3, 5):
+        with _lib.tuning(rmac_kernel=2, rmac_stages=stages):
+            out = ops.region_pool_embed(nhwc, regions=regions, per_region_l2=True).cpu().numpy()
+        assert np.array_equal(out, base)
+
+
 def test_l2norm_rows(ops):
     x = np.random.RandomState(1).randn(77, 1000).astype(np.float32)
     x[5] = 0

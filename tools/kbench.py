@@ -187,6 +187,42 @@ def bench_pool(args):
             report("region_pool R-MAC L=3 B=%d %s" % (B, "nhwc" if cl else "nchw"), ms, best, nb)
 
 
+def bench_rmac(args):
+    """R-MAC (3 levels, per-region L2) on the VGG maps: the cluster kernel (rmac_kernel=1) against the persistent TMA-staged kernel
+    (rmac_kernel=2) over batch sizes, layouts, dtypes and ring depths."""
+    from cvpce_b200 import _lib
+    dev = "cuda"
+    for B in (32, 64, 96, 128, 256):
+        for cl in (True, False):
+            for dt in (torch.float32, torch.bfloat16):
+                f4 = torch.rand((B, 512, 32, 32), device=dev).to(dt)
+                f5 = torch.rand((B, 512, 16, 16), device=dev).to(dt)
+                if cl:
+                    f4, f5 = f4.contiguous(memory_format=torch.channels_last), f5.contiguous(memory_format=torch.channels_last)
+                out = torch.empty((B, 1024), device=dev)
+                nb = f4.element_size() * (f4.numel() + f5.numel()) + 4.0 * 1024 * B
+                regs = [ops.rmac_regions(32, 32, 3), ops.rmac_regions(16, 16, 3)]
+                name = "R-MAC L=3 B=%d %s %s" % (B, "nhwc" if cl else "nchw", "f32" if dt == torch.float32 else "bf16")
+                for kern, stages in ((1, 0), (2, 0), (2, 4)):
+                    if stages and not (B in (128, 256) and dt == torch.float32):
+                        continue
+                    with _lib.tuning(rmac_kernel=kern, rmac_stages=stages):
+                        ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
+                    report(name + (" cluster kernel" if kern == 1 else " staged kernel" + (" %d stages" % stages if stages else "")), ms, best, nb)
+                del f4, f5
+    # the fast trunk's hand-off: pool4(relu4_3) and relu5_3, both 16 x 16, channels-last f32
+    for B in (128, 256):
+        p4 = torch.rand((B, 512, 16, 16), device=dev).contiguous(memory_format=torch.channels_last)
+        f5 = torch.rand((B, 512, 16, 16), device=dev).contiguous(memory_format=torch.channels_last)
+        out = torch.empty((B, 1024), device=dev)
+        nb = 4.0 * (p4.numel() + f5.numel()) + 4.0 * 1024 * B
+        regs = [ops.rmac_regions(16, 16, 3), ops.rmac_regions(16, 16, 3)]
+        for kern in (1, 2):
+            with _lib.tuning(rmac_kernel=kern):
+                ms, best = timeit(lambda: ops.region_pool_embed([p4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
+            report("R-MAC L=3 B=%d nhwc f32, two 16x16 maps (fast-trunk hand-off) %s" % (B, "cluster kernel" if kern == 1 else "staged kernel"), ms, best, nb)
+
+
 def bench_prep(args):
     dev = "cuda"
     for R, D in ((6400, 1024), (125000, 512), (1000000, 512)):
@@ -268,7 +304,7 @@ def main():
     if args.tune:
         print(json.dumps({"tuning": args.tune}), flush=True)
     for w in args.which:
-        {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "match": bench_match, "crop": bench_crop, "pool": bench_pool, "prep": bench_prep, "sim": bench_sim}[w](args)
+        {"nms": bench_nms, "select": bench_select, "maxpool": bench_maxpool, "match": bench_match, "crop": bench_crop, "pool": bench_pool, "rmac": bench_rmac, "prep": bench_prep, "sim": bench_sim}[w](args)
 
 
 if __name__ == "__main__":
