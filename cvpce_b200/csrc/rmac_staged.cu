@@ -6,36 +6,53 @@
 // Why a second kernel: the cluster kernel of region_pool.cu gives every CTA 1/8 of one image (128 KB at the VGG shapes)
 // between barriers -- 0.48-0.51 of HBM channels-last, 0.17 NCHW (4-byte loads).  Here ONE persistent CTA per SM owns whole
 // images, and the loads are taken off the threads entirely:
-//  * a producer warp streams the image's maps, 16 KB at a time, into a shared-memory ring with cp.async.bulk (the TMA
-//    engine, mbarrier complete_tx) and runs ahead across map and image boundaries -- up to 8 stages = 128 KB in flight per
-//    SM, so the finishing phase of image n (norms, descriptor store) overlaps the loads of image n + 1;
-//  * channels-last maps: a consumer thread owns one 16-byte channel group of every pixel (LDS.128 + 4 FMNMX per pixel) and
-//    walks the pixels in raster order with CTA-uniform control flow: the running maximum of the current column segment is
-//    folded into rs[column segment][channel] when the segment ends, and when a ROW segment ends every region that contains
-//    it takes the maximum of its column segments.  Every shared-memory word is touched by one thread only: no atomics, no
-//    barrier inside a map;
-//  * NCHW maps: a consumer warp owns a plane (two or four planes for narrow maps, lane = (plane, column)): column maxima
-//    per row segment -> cell maxima -> region maxima, all out of the staged plane in shared memory;
+//  * a producer thread streams the image's maps, 16 KB at a time, into a shared-memory ring with cp.async.bulk (the TMA
+//    engine, mbarrier complete_tx) and runs ahead across map and image boundaries, so the finishing phase of image n
+//    (norms, descriptor store) overlaps the loads of image n + 1;
+//  * channels-last maps: within a ROW SEGMENT (the rows between two region boundaries) the rows are folded into one row
+//    of running maxima element by element -- no boundary inside a row matters yet, so the streaming part is branch-free:
+//    each of the 512 consumer threads owns up to two 16-byte vectors of every 16 KB chunk of a row, keeps their maxima in
+//    registers (LDS.128 + 4 FMNMX / HMNMX2 per vector) and the whole CTA writes that row of column maxima to shared
+//    memory when the row segment ends; only then -- 6 times per map for three R-MAC levels -- are the regions that
+//    contain the row segment updated from it (a group of threads per region, a thread per 16-byte channel group).
+//    The first versions walked the pixels with one boundary test per pixel, then per run of pixels: with one warp per
+//    scheduler that bookkeeping cost 280 cycles per run and 520 per chunk (cycle counters below, tools/rmac_prof.py),
+//    0.13 ms per image whatever the bytes;
+//  * NCHW maps: a consumer warp owns a group of staged planes, a lane one 16-byte strip of columns of one plane: it walks
+//    down the rows (LDS.128 per row), the strip's maxima of a row segment are written back in place over the plane,
+//    then one lane per (plane, cell) and one per (plane, region) finish the plane;
 //  * all channels of an image are in one CTA, so the per-region L2 norms and the final L2 norm are block reductions (no
 //    cluster, no workspace, no second launch).
-// Every feature value is read from HBM exactly once.  Elementary segments = the intervals between the distinct region
-// boundaries (plus 0 and the map size), as in region_pool.cu.
+// Every feature value is read from HBM exactly once.
 #include "common.cuh"
+#include <cuda_bf16.h>
 #include <math.h>
 #include <string.h>
 #include <algorithm>
 
 namespace cvpce {
 
-constexpr int kRmacConsWarps = 16;                        // consumer warps (channels-last maps use C*elemsize/16 threads of them)
+constexpr int kRmacConsWarps = 16;                        // consumer warps
 constexpr int kRmacCons = kRmacConsWarps * 32;
 constexpr int kRmacThreads = kRmacCons + 32;              // + the producer warp
 constexpr int kRmacMaxSegs = 24;                          // elementary segments per axis
 constexpr int kRmacMaxStages = 8;
 constexpr int kRmacStageBytes = 16384;
-constexpr int kRmacCmPitch = 33;
+constexpr int kRmacStageVecs = kRmacStageBytes / 16;
+constexpr int kRmacFullBars = 16;                         // "full" barriers are tied to the chunk index mod 16 (see the NCHW consumer)
 constexpr int kRmacMaxRegions = CVPCE_POOL_MAX_REGIONS;   // per map
 constexpr int kRmacMaxRegionsTotal = 64;
+constexpr int kRmacMaxRowParts = 4;                       // channels-last rows of up to 4 chunks (64 KB)
+
+// development aid (build with -DCVPCE_RMAC_PROF, tools/rmac_prof.py): cycle counts of block 0 (producer thread; thread 0 of the consumers)
+#ifdef CVPCE_RMAC_PROF
+__device__ long long g_rmac_prof[16];
+#define RM_PROF_ADD(k, v) do { if (blockIdx.x == 0) g_rmac_prof[k] += (v); } while (0)
+#define RM_CLOCK() clock64()
+#else
+#define RM_PROF_ADD(k, v) do { } while (0)
+#define RM_CLOCK() 0ll
+#endif
 
 struct RmacMap {
   const void* data;
@@ -43,16 +60,19 @@ struct RmacMap {
   int C, H, W;
   int nhwc;          // 1: dense channels-last; 0: dense NCHW
   int n_regions, region_begin, out_offset;
-  int nxs, nys;
-  int n_units;       // pixels (channels-last) or planes (NCHW) per image
-  int unit_bytes;    // bytes of one pixel (all channels) / of one plane
-  int upc;           // units per chunk
+  int nys;           // row segments (both layouts)
   int n_chunks;      // per image
+  // channels-last: a chunk is `rows_per_chunk` whole rows (row_parts == 1) or one of the `row_parts` 16 KB parts of a row
+  int row_bytes, row_parts, rows_per_chunk;
+  int pix_vecs;      // 16-byte vectors per pixel
+  // NCHW: a chunk is `upc` whole planes; a warp pass handles `ppp` planes, `lpr` lanes per row (16 bytes per lane)
+  int plane_bytes, upc, lpr, ppp, nxs;
   unsigned char xb[kRmacMaxSegs + 2], yb[kRmacMaxSegs + 2];  // segment s = [b[s], b[s+1]), b[0] = 0, b[n] = W / H (one spare entry: the walkers read b[n+1])
 };
 
 struct RmacParams {
   RmacMap maps[CVPCE_POOL_MAX_MAPS];
+  int4 regions[kRmacMaxRegionsTotal]; // (y0, x0, y1, x1)
   uchar4 segs[kRmacMaxRegionsTotal];  // (first row segment, end row segment, first column segment, end column segment)
   int n_maps, B;
   int per_region_l2, final_l2;
@@ -60,8 +80,8 @@ struct RmacParams {
   float* out;
   long long out_stride;
   int nstages;
-  int off_rs, off_vals, off_desc, off_wscr, off_bar;  // byte offsets into dynamic shared memory (the ring is at 0)
-  int wscr_floats;                                    // per consumer warp (NCHW maps)
+  int off_cm, off_vals, off_desc, off_wscr, off_bar;  // byte offsets into dynamic shared memory (the ring is at 0)
+  int wscr_floats;                                    // per consumer warp (NCHW maps: cell maxima)
 };
 
 __device__ __forceinline__ uint32_t rm_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -71,8 +91,8 @@ __device__ __forceinline__ void rm_mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void rm_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rm_smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void rm_mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rm_smem_u32(bar)) : "memory");
+__device__ __forceinline__ void rm_mbar_arrive_n(uint64_t* bar, uint32_t n) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(rm_smem_u32(bar)), "r"(n) : "memory");
 }
 __device__ __forceinline__ bool rm_mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -86,8 +106,11 @@ __device__ __forceinline__ bool rm_mbar_try_wait(uint64_t* bar, uint32_t parity)
   return ok != 0;
 }
 __device__ __forceinline__ void rm_mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!rm_mbar_try_wait(bar, parity)) {
-  }
+  while (!rm_mbar_try_wait(bar, parity)) __nanosleep(20);
+}
+// the producer is ahead by the depth of the ring: it can afford to sleep between polls
+__device__ __forceinline__ void rm_mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  while (!rm_mbar_try_wait(bar, parity)) __nanosleep(100);
 }
 // global -> shared bulk copy by the TMA engine; completion is counted in bytes on `bar`.  The maps are read once: evict-first.
 __device__ __forceinline__ void rm_bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
@@ -98,119 +121,181 @@ __device__ __forceinline__ void rm_bulk_load(void* smem_dst, const void* gsrc, u
 }
 __device__ __forceinline__ void rm_cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kRmacCons) : "memory"); }
 
-template <int E>
-__device__ __forceinline__ void rm_ld(float (&v)[E], const float* p) {
-#pragma unroll
-  for (int e = 0; e < E; e += 4) {
-    const float4 t = *reinterpret_cast<const float4*>(p + e);
-    v[e] = t.x; v[e + 1] = t.y; v[e + 2] = t.z; v[e + 3] = t.w;
+// Position in the ring: stage `st` (0 .. nstages-1, any count) and the running chunk counter `it`; the chunk's "full" barrier
+// is full[it % 16] in phase it / 16.
+struct RmacRing {
+  uint32_t it;
+  int st;
+  __device__ __forceinline__ void advance(int nst) {
+    ++it;
+    st = (st + 1 == nst) ? 0 : st + 1;
   }
+  __device__ __forceinline__ int bar() const { return (int)(it & (kRmacFullBars - 1)); }
+  __device__ __forceinline__ uint32_t parity() const { return (it >> 4) & 1u; }
+};
+
+// element-wise maximum of two 16-byte vectors of the map's element type
+template <int DTYPE>
+__device__ __forceinline__ uint4 rm_vmax(const uint4 a, const uint4 b) {
+  uint4 r;
+  if (DTYPE == CVPCE_F32) {
+    r.x = __float_as_uint(fmaxf(__uint_as_float(a.x), __uint_as_float(b.x)));
+    r.y = __float_as_uint(fmaxf(__uint_as_float(a.y), __uint_as_float(b.y)));
+    r.z = __float_as_uint(fmaxf(__uint_as_float(a.z), __uint_as_float(b.z)));
+    r.w = __float_as_uint(fmaxf(__uint_as_float(a.w), __uint_as_float(b.w)));
+  } else {
+    __nv_bfloat162 t;
+    t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.x), *reinterpret_cast<const __nv_bfloat162*>(&b.x)); r.x = *reinterpret_cast<uint32_t*>(&t);
+    t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.y), *reinterpret_cast<const __nv_bfloat162*>(&b.y)); r.y = *reinterpret_cast<uint32_t*>(&t);
+    t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.z), *reinterpret_cast<const __nv_bfloat162*>(&b.z)); r.z = *reinterpret_cast<uint32_t*>(&t);
+    t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.w), *reinterpret_cast<const __nv_bfloat162*>(&b.w)); r.w = *reinterpret_cast<uint32_t*>(&t);
+  }
+  return r;
 }
-template <int E>
-__device__ __forceinline__ void rm_st(float* p, const float (&v)[E]) {
-#pragma unroll
-  for (int e = 0; e < E; e += 4) *reinterpret_cast<float4*>(p + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+template <int DTYPE>
+__device__ __forceinline__ uint4 rm_vneg_inf() {
+  const uint32_t w = (DTYPE == CVPCE_F32) ? 0xff800000u : 0xff80ff80u;
+  return make_uint4(w, w, w, w);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// channels-last map: region maxima -> vals[r][C].  `it` is the running chunk counter of the CTA (ring position).
+// channels-last map: region maxima -> vals[r][C].  P = 16 KB parts per row (1: a chunk holds whole rows).
 // ---------------------------------------------------------------------------------------------------------------------
-template <int DTYPE>
+template <int DTYPE, int P>
 __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const RmacMap& mp, const unsigned char* ring, uint64_t* full,
-                                                  uint64_t* empty, float* rs, float* vals, uint32_t& it, int ctid, int lane) {
-  constexpr int E = (DTYPE == CVPCE_F32) ? 4 : 8;  // channels per 16 bytes
-  const int V = mp.C / E;
-  const bool active = ctid < V;
+                                                  uint64_t* empty, uint4* cm, float* vals, RmacRing& rg, int tid, int lane) {
+  constexpr int E = (DTYPE == CVPCE_F32) ? 4 : 8;  // channels per 16-byte vector
   const int nst = p.nstages;
-  const int W = mp.W, nxs = mp.nxs;
-  float* rs_own = rs + ctid * E;
-  float* vals_own = vals + ctid * E;
-  float acc[E];
+  const int C = mp.C, H = mp.H, row_bytes = mp.row_bytes, R = mp.rows_per_chunk, nq = mp.pix_vecs;
+  const int n_regions = mp.n_regions, region_begin = mp.region_begin;
+  const int RV = row_bytes >> 4;  // vectors per row
+  uint4 acc[P][2];
 #pragma unroll
-  for (int e = 0; e < E; ++e) acc[e] = -INFINITY;
-  if (active)
-    for (int s = 0; s < nxs; ++s) rm_st<E>(rs_own + s * mp.C, acc);
-  int x = 0, y = 0, xs = 0, ys = 0;
-  int xnext = mp.xb[1], ynext = mp.yb[1];
-  for (int k = 0; k < mp.n_chunks; ++k, ++it) {
-    const int st = it % nst;
-    rm_mbar_wait(&full[st], (it / nst) & 1);
-    if (active) {
-      const int nu = min(mp.upc, mp.n_units - k * mp.upc);
-      const unsigned char* buf = ring + (size_t)st * kRmacStageBytes + ctid * 16;
-      for (int u0 = 0; u0 < nu; u0 += 4) {
-        uint4 v[4];
+  for (int pc = 0; pc < P; ++pc) acc[pc][0] = acc[pc][1] = rm_vneg_inf<DTYPE>();
+  // the region stage: thread (g, q) = (region group, channel vector)
+  const int n_groups = kRmacCons / nq;
+  const int g = tid / nq, q = tid - g * nq;
+  int y = 0, ys = 0, ynext = mp.yb[1];
+
+  // the row segment ends: its row of column maxima goes to shared memory, every region that contains it is updated
+  auto row_segment_end = [&]() {
+    const long long tr0 = RM_CLOCK();
+    rm_cons_sync();  // the previous row segment's regions are done with cm
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (u0 + j < nu) v[j] = *reinterpret_cast<const uint4*>(buf + (size_t)(u0 + j) * mp.unit_bytes);
+    for (int pc = 0; pc < P; ++pc) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (u0 + j < nu) {  // CTA-uniform
-            if (DTYPE == CVPCE_F32) {
-              acc[0] = fmaxf(acc[0], __uint_as_float(v[j].x));
-              acc[1] = fmaxf(acc[1], __uint_as_float(v[j].y));
-              acc[2] = fmaxf(acc[2], __uint_as_float(v[j].z));
-              acc[3] = fmaxf(acc[3], __uint_as_float(v[j].w));
-            } else {
-              acc[0] = fmaxf(acc[0], __uint_as_float(v[j].x << 16)); acc[1] = fmaxf(acc[1], __uint_as_float(v[j].x & 0xffff0000u));
-              acc[2] = fmaxf(acc[2], __uint_as_float(v[j].y << 16)); acc[3] = fmaxf(acc[3], __uint_as_float(v[j].y & 0xffff0000u));
-              acc[4 % E] = fmaxf(acc[4 % E], __uint_as_float(v[j].z << 16)); acc[5 % E] = fmaxf(acc[5 % E], __uint_as_float(v[j].z & 0xffff0000u));
-              acc[6 % E] = fmaxf(acc[6 % E], __uint_as_float(v[j].w << 16)); acc[7 % E] = fmaxf(acc[7 % E], __uint_as_float(v[j].w & 0xffff0000u));
-            }
-            ++x;
-            if (x == xnext) {  // CTA-uniform: the column segment ends here (the last one ends with the row)
-              float cur[E];
-              rm_ld<E>(cur, rs_own + xs * mp.C);
+      for (int j = 0; j < 2; ++j) {
+        const int v = pc * kRmacStageVecs + tid + j * kRmacCons;
+        if (v < RV) cm[v] = acc[pc][j];
+        acc[pc][j] = rm_vneg_inf<DTYPE>();
+      }
+    }
+    rm_cons_sync();
+    if (g < n_groups) {
+      for (int r = g; r < n_regions; r += n_groups) {
+        const uchar4 sg = p.segs[region_begin + r];
+        if (ys < sg.x || ys >= sg.y) continue;
+        const int4 box = p.regions[region_begin + r];
+        const uint4* src = cm + box.y * nq + q;
+        uint4 m0 = rm_vneg_inf<DTYPE>(), m1 = m0;
+        int x = box.y;
+        for (; x + 2 <= box.w; x += 2, src += 2 * nq) {
+          m0 = rm_vmax<DTYPE>(m0, src[0]);
+          m1 = rm_vmax<DTYPE>(m1, src[nq]);
+        }
+        if (x < box.w) m0 = rm_vmax<DTYPE>(m0, src[0]);
+        m0 = rm_vmax<DTYPE>(m0, m1);
+        float f[E];
+        if (DTYPE == CVPCE_F32) {
+          f[0] = __uint_as_float(m0.x); f[1] = __uint_as_float(m0.y); f[2] = __uint_as_float(m0.z); f[3] = __uint_as_float(m0.w);
+        } else {
+          f[0] = __uint_as_float(m0.x << 16); f[1] = __uint_as_float(m0.x & 0xffff0000u);
+          f[2] = __uint_as_float(m0.y << 16); f[3] = __uint_as_float(m0.y & 0xffff0000u);
+          f[4 % E] = __uint_as_float(m0.z << 16); f[5 % E] = __uint_as_float(m0.z & 0xffff0000u);
+          f[6 % E] = __uint_as_float(m0.w << 16); f[7 % E] = __uint_as_float(m0.w & 0xffff0000u);
+        }
+        float* dst = vals + r * C + q * E;
 #pragma unroll
-              for (int e = 0; e < E; ++e) {
-                cur[e] = fmaxf(cur[e], acc[e]);
-                acc[e] = -INFINITY;
-              }
-              rm_st<E>(rs_own + xs * mp.C, cur);
-              ++xs;
-              if (x == W) {
-                x = 0;
-                xs = 0;
-                ++y;
-                if (y == ynext) {  // the row segment ends: every region that contains it takes its column segments
-                  for (int r = 0; r < mp.n_regions; ++r) {
-                    const uchar4 sg = p.segs[mp.region_begin + r];
-                    if (ys >= sg.x && ys < sg.y) {
-                      float m[E];
-                      rm_ld<E>(m, rs_own + sg.z * mp.C);
-                      for (int s = sg.z + 1; s < sg.w; ++s) {
-                        float t[E];
-                        rm_ld<E>(t, rs_own + s * mp.C);
-#pragma unroll
-                        for (int e = 0; e < E; ++e) m[e] = fmaxf(m[e], t[e]);
-                      }
-                      if (ys > sg.x) {
-                        float t[E];
-                        rm_ld<E>(t, vals_own + r * mp.C);
-#pragma unroll
-                        for (int e = 0; e < E; ++e) m[e] = fmaxf(m[e], t[e]);
-                      }
-                      rm_st<E>(vals_own + r * mp.C, m);
-                    }
-                  }
-                  for (int s = 0; s < nxs; ++s) rm_st<E>(rs_own + s * mp.C, acc);  // acc is -inf here
-                  ++ys;
-                  ynext = mp.yb[ys + 1];
-                }
-              }
-              xnext = mp.xb[xs + 1];
-            }
+        for (int e = 0; e < E; e += 4) {
+          float4 o = make_float4(f[e], f[e + 1], f[e + 2], f[e + 3]);
+          if (ys > sg.x) {
+            const float4 old = *reinterpret_cast<const float4*>(dst + e);
+            o.x = fmaxf(o.x, old.x); o.y = fmaxf(o.y, old.y); o.z = fmaxf(o.z, old.z); o.w = fmaxf(o.w, old.w);
           }
+          *reinterpret_cast<float4*>(dst + e) = o;
         }
       }
     }
-    __syncwarp();
-    if (lane == 0) rm_mbar_arrive(&empty[st]);
+    ++ys;
+    ynext = mp.yb[ys + 1];
+    if (tid == 0) RM_PROF_ADD(3, RM_CLOCK() - tr0);
+  };
+
+  if (P == 1) {
+    while (y < H) {
+      const long long tw0 = RM_CLOCK();
+      rm_mbar_wait(&full[rg.bar()], rg.parity());
+      if (tid == 0) RM_PROF_ADD(2, RM_CLOCK() - tw0);
+      const uint4* buf = reinterpret_cast<const uint4*>(ring + (size_t)rg.st * kRmacStageBytes);
+      const int nrows = min(R, H - y);
+      bool released = false;
+      for (int rr = 0; rr < nrows; ++rr, buf += RV) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int v = tid + j * kRmacCons;
+          if (v < RV) acc[0][j] = rm_vmax<DTYPE>(acc[0][j], buf[v]);
+        }
+        ++y;
+        if (y == ynext) {
+          if (rr + 1 == nrows) {  // the stage is not needed any more: hand it back before the region stage
+            __syncwarp();
+            if (lane == 0) rm_mbar_arrive_n(&empty[rg.st], 1);
+            released = true;
+          }
+          row_segment_end();
+        }
+      }
+      if (!released) {
+        __syncwarp();
+        if (lane == 0) rm_mbar_arrive_n(&empty[rg.st], 1);
+      }
+      rg.advance(nst);
+    }
+  } else {
+    while (y < H) {
+#pragma unroll
+      for (int pc = 0; pc < P; ++pc) {
+        const long long tw0 = RM_CLOCK();
+        rm_mbar_wait(&full[rg.bar()], rg.parity());
+        if (tid == 0) RM_PROF_ADD(2, RM_CLOCK() - tw0);
+        const uint4* buf = reinterpret_cast<const uint4*>(ring + (size_t)rg.st * kRmacStageBytes);
+        const int nvec = min(kRmacStageVecs, RV - pc * kRmacStageVecs);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int v = tid + j * kRmacCons;
+          if (v < nvec) acc[pc][j] = rm_vmax<DTYPE>(acc[pc][j], buf[v]);
+        }
+        __syncwarp();
+        if (lane == 0) rm_mbar_arrive_n(&empty[rg.st], 1);
+        rg.advance(nst);
+      }
+      ++y;
+      if (y == ynext) row_segment_end();
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// NCHW map (W <= 32): a warp pass handles 32/Wp staged planes (Wp = W rounded up to 8, 16 or 32), lane = (plane, column).
+// NCHW map: a warp pass handles `ppp` staged planes; a lane owns one 16-byte strip of columns of one plane (lane = (plane,
+// strip)) and walks down the rows: one LDS.128 and 4 (f32) / 8 (bf16) FMNMX per row, the strip's maxima of a row segment are
+// written back IN PLACE over row `segment index` of the plane (a lane only ever touches its own strip, and that row has
+// been read by then) -- no scratch for the column maxima.  Then one lane per (plane, cell) reduces the cell's columns and
+// one lane per (plane, region) the region's cells.
+// A chunk holds up to `gpc` plane groups; its work is dealt to `nslots` = min(gpc, warps) warps, rotating from chunk to
+// chunk, and ONLY those warps touch the chunk's barriers (they share out the arrivals the stage's "empty" barrier expects).
+// A warp therefore skips chunks; that is safe with one-bit phase parities because the "full" barrier of chunk k is
+// full[k % 16]: a warp's slot pattern repeats every 16 chunks, so it meets consecutive phases of the barriers it uses, and the
+// consumer barrier between maps puts all warps behind every chunk of the previous map.
 // ---------------------------------------------------------------------------------------------------------------------
 template <int DTYPE>
 __device__ __forceinline__ float rm_ld_elem(const unsigned char* base, int idx) {
@@ -219,66 +304,97 @@ __device__ __forceinline__ float rm_ld_elem(const unsigned char* base, int idx) 
 }
 
 template <int DTYPE>
-__device__ __forceinline__ void rmac_consume_nchw(const RmacParams& p, const RmacMap& mp, const unsigned char* ring, uint64_t* full,
-                                                  uint64_t* empty, float* wscr, float* vals, uint32_t& it, int warp, int lane) {
+__device__ __forceinline__ void rmac_consume_nchw(const RmacParams& p, const RmacMap& mp, unsigned char* ring, uint64_t* full,
+                                                  uint64_t* empty, float* cells, float* vals, RmacRing& rg, int warp, int lane) {
+  constexpr int VW = (DTYPE == CVPCE_F32) ? 4 : 8;  // elements per 16 bytes
+  constexpr int ESZ = (DTYPE == CVPCE_F32) ? 4 : 2;
   const int nst = p.nstages;
-  const int H = mp.H, W = mp.W, nxs = mp.nxs, nys = mp.nys;
-  const int Wp = W > 16 ? 32 : (W > 8 ? 16 : 8);
-  const int ppw = 32 / Wp;
-  const int x = lane % Wp, psub = lane / Wp;
+  const int C = mp.C, H = mp.H, W = mp.W, nxs = mp.nxs, nys = mp.nys, upc = mp.upc, lpr = mp.lpr, ppp = mp.ppp;
+  const int n_chunks = mp.n_chunks, n_regions = mp.n_regions, region_begin = mp.region_begin, plane_bytes = mp.plane_bytes;
+  const int row_bytes = W * ESZ;
+  const int pp = lane / lpr, xv = lane - pp * lpr;
   const int ncell = nys * nxs;
-  const int HW = H * W;
-  float* cm = wscr;                          // [nys][kRmacCmPitch]
-  float* cells = wscr + nys * kRmacCmPitch;  // [ppw][nys][nxs]
-  int rot = 0;
-  for (int k = 0; k < mp.n_chunks; ++k, ++it) {
-    const int st = it % nst;
-    rm_mbar_wait(&full[st], (it / nst) & 1);
-    const int u0 = k * mp.upc;
-    const int nu = min(mp.upc, mp.n_units - u0);
-    const int ngroups = (nu + ppw - 1) / ppw;
-    const unsigned char* buf = ring + (size_t)st * kRmacStageBytes;
-    // plane group g of this chunk goes to warp (g + rot) % warps, so that chunks of few planes still spread over the warps
-    for (int g = (warp - rot + kRmacConsWarps) % kRmacConsWarps; g < ngroups; g += kRmacConsWarps) {
-      const int pl = g * ppw + psub;
-      const bool live = x < W && pl < nu;
-      const int base = pl * HW + x;
+  const int gpc = (upc + ppp - 1) / ppp;
+  const int nslots = min(gpc, kRmacConsWarps);
+  for (int k = 0; k < n_chunks; ++k, rg.advance(nst)) {
+    const int slot = (warp - (int)((rg.it * (uint32_t)nslots) & (kRmacConsWarps - 1)) + kRmacConsWarps) & (kRmacConsWarps - 1);
+    if (slot >= nslots) continue;
+    const uint32_t arrivals = kRmacConsWarps / nslots + (slot < kRmacConsWarps % nslots ? 1 : 0);
+    const long long tw0 = RM_CLOCK();
+    rm_mbar_wait(&full[rg.bar()], rg.parity());
+    if (warp == 0 && lane == 0) RM_PROF_ADD(2, RM_CLOCK() - tw0);
+    const int u0 = k * upc;
+    const int nu = min(upc, C - u0);
+    const int ngroups = (nu + ppp - 1) / ppp;
+    unsigned char* buf = ring + (size_t)rg.st * kRmacStageBytes;
+    bool wrote = false;
+    for (int g = slot; g < ngroups; g += nslots) {
+      wrote = true;
+      const int pl = g * ppp + pp;
+      const bool live = pp < ppp && pl < nu;
       {
+        unsigned char* strip = buf + (size_t)pl * plane_bytes + xv * 16;
+        float acc[VW];
+#pragma unroll
+        for (int e = 0; e < VW; ++e) acc[e] = -INFINITY;
         int ysr = 0, next = mp.yb[1];
-        float v0 = -INFINITY;
 #pragma unroll 4
         for (int y = 0; y < H; ++y) {
-          const float e = live ? rm_ld_elem<DTYPE>(buf, base + y * W) : -INFINITY;
-          v0 = fmaxf(v0, e);
-          if (y + 1 == next) {  // warp-uniform: row-segment boundary
-            cm[ysr * kRmacCmPitch + lane] = v0;
-            v0 = -INFINITY;
+          if (live) {
+            const uint4 w = *reinterpret_cast<const uint4*>(strip + y * row_bytes);
+            if (DTYPE == CVPCE_F32) {
+              acc[0] = fmaxf(acc[0], __uint_as_float(w.x)); acc[1] = fmaxf(acc[1], __uint_as_float(w.y));
+              acc[2] = fmaxf(acc[2], __uint_as_float(w.z)); acc[3] = fmaxf(acc[3], __uint_as_float(w.w));
+            } else {
+              acc[0] = fmaxf(acc[0], __uint_as_float(w.x << 16)); acc[1] = fmaxf(acc[1], __uint_as_float(w.x & 0xffff0000u));
+              acc[2] = fmaxf(acc[2], __uint_as_float(w.y << 16)); acc[3] = fmaxf(acc[3], __uint_as_float(w.y & 0xffff0000u));
+              acc[4 % VW] = fmaxf(acc[4 % VW], __uint_as_float(w.z << 16)); acc[5 % VW] = fmaxf(acc[5 % VW], __uint_as_float(w.z & 0xffff0000u));
+              acc[6 % VW] = fmaxf(acc[6 % VW], __uint_as_float(w.w << 16)); acc[7 % VW] = fmaxf(acc[7 % VW], __uint_as_float(w.w & 0xffff0000u));
+            }
+          }
+          if (y + 1 == next) {  // warp-uniform: the row segment ends; its column maxima replace row `ysr` of the strip
+            if (live) {
+              uint4 o;
+              if (DTYPE == CVPCE_F32) {
+                o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+              } else {  // maxima of bf16 values are bf16 values: the upper halves are exact
+                o.x = (__float_as_uint(acc[0]) >> 16) | (__float_as_uint(acc[1]) & 0xffff0000u);
+                o.y = (__float_as_uint(acc[2]) >> 16) | (__float_as_uint(acc[3]) & 0xffff0000u);
+                o.z = (__float_as_uint(acc[4 % VW]) >> 16) | (__float_as_uint(acc[5 % VW]) & 0xffff0000u);
+                o.w = (__float_as_uint(acc[6 % VW]) >> 16) | (__float_as_uint(acc[7 % VW]) & 0xffff0000u);
+              }
+              *reinterpret_cast<uint4*>(strip + ysr * row_bytes) = o;
+            }
+#pragma unroll
+            for (int e = 0; e < VW; ++e) acc[e] = -INFINITY;
             ++ysr;
             next = mp.yb[ysr + 1];
           }
         }
       }
       __syncwarp();
-      for (int c = lane; c < ncell * ppw; c += 32) {
+      for (int c = lane; c < ncell * ppp; c += 32) {
         const int ps = c / ncell, cc = c - ps * ncell;
+        const int plr = g * ppp + ps;
+        if (plr >= nu) continue;
         const int ysr = cc / nxs, xsr = cc - ysr * nxs;
-        const float* row = cm + ysr * kRmacCmPitch + ps * Wp;
+        const unsigned char* row = buf + (size_t)plr * plane_bytes + ysr * row_bytes;
         float v0 = -INFINITY, v1 = -INFINITY;
         int xx = mp.xb[xsr];
         const int xe = mp.xb[xsr + 1];
         for (; xx + 1 < xe; xx += 2) {
-          v0 = fmaxf(v0, row[xx]);
-          v1 = fmaxf(v1, row[xx + 1]);
+          v0 = fmaxf(v0, rm_ld_elem<DTYPE>(row, xx));
+          v1 = fmaxf(v1, rm_ld_elem<DTYPE>(row, xx + 1));
         }
-        if (xx < xe) v0 = fmaxf(v0, row[xx]);
+        if (xx < xe) v0 = fmaxf(v0, rm_ld_elem<DTYPE>(row, xx));
         cells[c] = fmaxf(v0, v1);
       }
       __syncwarp();
-      for (int q = lane; q < mp.n_regions * ppw; q += 32) {
-        const int ps = q / mp.n_regions, r = q - ps * mp.n_regions;
-        const int plr = g * ppw + ps;
+      for (int q = lane; q < n_regions * ppp; q += 32) {
+        const int ps = q / n_regions, r = q - ps * n_regions;
+        const int plr = g * ppp + ps;
         if (plr >= nu) continue;
-        const uchar4 sg = p.segs[mp.region_begin + r];
+        const uchar4 sg = p.segs[region_begin + r];
         float v0 = -INFINITY, v1 = -INFINITY;
         for (int ysr = sg.x; ysr < sg.y; ++ysr) {
           const float* crow = cells + ps * ncell + ysr * nxs;
@@ -289,37 +405,39 @@ __device__ __forceinline__ void rmac_consume_nchw(const RmacParams& p, const Rma
           }
           if (xsr < sg.w) v0 = fmaxf(v0, crow[xsr]);
         }
-        vals[r * mp.C + u0 + plr] = fmaxf(v0, v1);
+        vals[r * C + u0 + plr] = fmaxf(v0, v1);
       }
-      __syncwarp();  // cm / cells are reused by this warp's next pass
+      __syncwarp();  // the cell scratch is reused by this warp's next pass
     }
-    rot = (rot + ngroups) % kRmacConsWarps;
+    // the stage was written with ordinary stores and will next be written by the TMA engine (async proxy)
+    if (wrote) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    if (lane == 0) rm_mbar_arrive(&empty[st]);
+    if (lane == 0) rm_mbar_arrive_n(&empty[rg.st], arrivals);
   }
 }
 
 template <int DTYPE>
-__global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __grid_constant__ RmacParams p) {
+__global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __grid_constant__ RmacParams gp) {
   extern __shared__ __align__(128) unsigned char rm_smem[];
-  unsigned char* ring = rm_smem;
-  float* rs = reinterpret_cast<float*>(rm_smem + p.off_rs);
-  float* vals = reinterpret_cast<float*>(rm_smem + p.off_vals);
-  float* desc = reinterpret_cast<float*>(rm_smem + p.off_desc);
-  float* wscr_all = reinterpret_cast<float*>(rm_smem + p.off_wscr);
-  uint64_t* full = reinterpret_cast<uint64_t*>(rm_smem + p.off_bar);
-  uint64_t* empty = full + kRmacMaxStages;
+  // control data is read out of shared memory (the parameter block is 3 KB: indexed loads through the constant cache are slow)
+  __shared__ __align__(16) RmacParams p;
   __shared__ float s_part[kRmacMaxRegions][kRmacConsWarps];
   __shared__ float s_denom[kRmacMaxRegions];
   __shared__ float s_wsum[kRmacConsWarps];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nst = p.nstages;
+  for (int i = tid; i < (int)(sizeof(RmacParams) / 4); i += kRmacThreads) reinterpret_cast<int*>(&p)[i] = reinterpret_cast<const int*>(&gp)[i];
+  unsigned char* ring = rm_smem;
+  uint4* cm = reinterpret_cast<uint4*>(rm_smem + gp.off_cm);
+  float* vals = reinterpret_cast<float*>(rm_smem + gp.off_vals);
+  float* desc = reinterpret_cast<float*>(rm_smem + gp.off_desc);
+  float* wscr_all = reinterpret_cast<float*>(rm_smem + gp.off_wscr);
+  uint64_t* full = reinterpret_cast<uint64_t*>(rm_smem + gp.off_bar);
+  uint64_t* empty = full + kRmacFullBars;
+  const int nst = gp.nstages;
   if (tid == 0) {
-    for (int s = 0; s < nst; ++s) {
-      rm_mbar_init(&full[s], 1);
-      rm_mbar_init(&empty[s], kRmacConsWarps);
-    }
+    for (int s = 0; s < kRmacFullBars; ++s) rm_mbar_init(&full[s], 1);
+    for (int s = 0; s < nst; ++s) rm_mbar_init(&empty[s], kRmacConsWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -329,66 +447,104 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
     if (lane == 0) {
       uint64_t policy;
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-      uint32_t it = 0;
+      RmacRing rg = {0u, 0};
+      uint32_t rev = 0;  // revolutions of the ring (parity of the stage's "empty" phase)
+      const long long tp0 = RM_CLOCK();
       for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
         for (int m = 0; m < p.n_maps; ++m) {
           const RmacMap& mp = p.maps[m];
           const unsigned char* src = reinterpret_cast<const unsigned char*>(mp.data) + (long long)n * mp.image_bytes;
-          for (int k = 0; k < mp.n_chunks; ++k, ++it) {
-            const int st = it % nst;
-            rm_mbar_wait(&empty[st], ((it / nst) & 1) ^ 1);
-            const int u0 = k * mp.upc;
-            const uint32_t bytes = (uint32_t)min(mp.upc, mp.n_units - u0) * (uint32_t)mp.unit_bytes;
-            rm_mbar_expect_tx(&full[st], bytes);
-            rm_bulk_load(ring + (size_t)st * kRmacStageBytes, src + (long long)u0 * mp.unit_bytes, bytes, &full[st], policy);
+          const int n_chunks = mp.n_chunks;
+          const int H = mp.H, C = mp.C, P = mp.row_parts, R = mp.rows_per_chunk, upc = mp.upc, row_bytes = mp.row_bytes, plane_bytes = mp.plane_bytes;
+          const bool nhwc = mp.nhwc != 0;
+          int row = 0, part = 0;
+          for (int k = 0; k < n_chunks; ++k) {
+            long long off;
+            uint32_t bytes;
+            if (!nhwc) {  // whole planes
+              off = (long long)k * upc * plane_bytes;
+              bytes = (uint32_t)min(upc, C - k * upc) * (uint32_t)plane_bytes;
+            } else if (P == 1) {  // whole rows
+              off = (long long)row * row_bytes;
+              const int nr = min(R, H - row);
+              bytes = (uint32_t)nr * (uint32_t)row_bytes;
+              row += nr;
+            } else {  // one 16 KB part of a row
+              off = (long long)row * row_bytes + (long long)part * kRmacStageBytes;
+              bytes = (uint32_t)min(kRmacStageBytes, row_bytes - part * kRmacStageBytes);
+              if (++part == P) {
+                part = 0;
+                ++row;
+              }
+            }
+            const long long t0 = RM_CLOCK();
+            rm_mbar_wait_relaxed(&empty[rg.st], (rev & 1) ^ 1);
+            RM_PROF_ADD(0, RM_CLOCK() - t0);
+            rm_mbar_expect_tx(&full[rg.bar()], bytes);
+            rm_bulk_load(ring + (size_t)rg.st * kRmacStageBytes, src + off, bytes, &full[rg.bar()], policy);
+            rg.advance(nst);
+            if (rg.st == 0) ++rev;
           }
         }
       }
+      RM_PROF_ADD(1, RM_CLOCK() - tp0);
     }
     return;  // the consumers wait for every copy that was issued, so nothing is in flight when the CTA ends
   }
 
   // ---- consumers -----------------------------------------------------------------------------------------------------------
-  const int ctid = tid;
-  uint32_t it = 0;
+  RmacRing rg = {0u, 0};
+  const long long tc0 = RM_CLOCK();
   for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
     float sq = 0.f;
     for (int m = 0; m < p.n_maps; ++m) {
       const RmacMap& mp = p.maps[m];
-      if (mp.nhwc) rmac_consume_nhwc<DTYPE>(p, mp, ring, full, empty, rs, vals, it, ctid, lane);
-      else rmac_consume_nchw<DTYPE>(p, mp, ring, full, empty, wscr_all + warp * p.wscr_floats, vals, it, warp, lane);
-      rm_cons_sync();  // vals[r][C] of this map is complete
+      if (mp.nhwc) {
+        if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
+        else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
+        else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
+        else rmac_consume_nhwc<DTYPE, 4>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
+      } else {
+        rmac_consume_nchw<DTYPE>(p, mp, ring, full, empty, wscr_all + warp * p.wscr_floats, vals, rg, warp, lane);
+      }
+      const long long ts0 = RM_CLOCK();
+      rm_cons_sync();  // vals[r][C] of this map is complete, every chunk of the map has been consumed
+      if (tid == 0) RM_PROF_ADD(6, RM_CLOCK() - ts0);
+      const long long tf0 = RM_CLOCK();
+      const int C = mp.C, n_regions = mp.n_regions;
       if (p.per_region_l2) {
-        for (int r = 0; r < mp.n_regions; ++r) {
+        for (int r = 0; r < n_regions; ++r) {
           float s = 0.f;
-          for (int c = ctid; c < mp.C; c += kRmacCons) {
-            const float v = vals[r * mp.C + c];
+          for (int c = tid; c < C; c += kRmacCons) {
+            const float v = vals[r * C + c];
             s = fmaf(v, v, s);
           }
           s = warp_sum(s);
           if (lane == 0) s_part[r][warp] = s;
         }
         rm_cons_sync();
-        if (ctid < mp.n_regions) {
+        if (tid < n_regions) {
           float t = 0.f;
 #pragma unroll
-          for (int w = 0; w < kRmacConsWarps; ++w) t += s_part[ctid][w];
-          s_denom[ctid] = fmaxf(sqrtf(t), p.eps);
+          for (int w = 0; w < kRmacConsWarps; ++w) t += s_part[tid][w];
+          s_denom[tid] = fmaxf(sqrtf(t), p.eps);
         }
         rm_cons_sync();
       }
-      for (int c = ctid; c < mp.C; c += kRmacCons) {
+      for (int c = tid; c < C; c += kRmacCons) {
         float d = 0.f;
-        for (int r = 0; r < mp.n_regions; ++r) {
-          float v = vals[r * mp.C + c];
+        for (int r = 0; r < n_regions; ++r) {
+          float v = vals[r * C + c];
           if (p.per_region_l2) v = v / s_denom[r];
           d = (r == 0) ? v : d + v;
         }
         desc[mp.out_offset + c] = d;
         sq = fmaf(d, d, sq);
       }
-      rm_cons_sync();  // vals, rs and s_denom are reused by the next map
+      rm_cons_sync();  // vals, cm and s_denom are reused by the next map
+      if (tid == 0) RM_PROF_ADD(4, RM_CLOCK() - tf0);
     }
+    const long long tg0 = RM_CLOCK();
     float denom = 1.f;
     if (p.final_l2) {
       sq = warp_sum(sq);
@@ -402,9 +558,11 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
     const RmacMap& last = p.maps[p.n_maps - 1];
     const int D = last.out_offset + last.C;
     float* orow = p.out + (long long)n * p.out_stride;
-    for (int c = ctid; c < D; c += kRmacCons) orow[c] = p.final_l2 ? desc[c] / denom : desc[c];
+    for (int c = tid; c < D; c += kRmacCons) orow[c] = p.final_l2 ? desc[c] / denom : desc[c];
     rm_cons_sync();  // desc / s_wsum are reused by the next image
+    if (tid == 0) RM_PROF_ADD(7, RM_CLOCK() - tg0);
   }
+  if (tid == 0) RM_PROF_ADD(5, RM_CLOCK() - tc0);
 }
 
 // Elementary segments of [0, dim) between the distinct boundaries of the intervals; returns the count (0: too many).
@@ -448,7 +606,7 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
   p.out = out;
   p.out_stride = out_stride;
   int rbeg = 0, col = 0;
-  size_t rs_floats = 0, vals_floats = 0, wscr_floats = 0;
+  size_t cm_bytes = 0, vals_floats = 0, wscr_floats = 0;
   const int32_t* rg = regions;
   for (int m = 0; m < n_maps; ++m) {
     const cvpce_feature_map& fm = maps[m];
@@ -458,10 +616,12 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
     pm.image_bytes = (long long)fm.stride_n * esz;
     if (!aligned16(fm.data) || pm.image_bytes % 16 != 0 || fm.H > 255 || fm.W > 255) return kRmacNotApplicable;
     const long long pix_bytes = (long long)fm.C * esz, plane_bytes = (long long)fm.H * fm.W * esz;
+    const long long cl_row_bytes = pix_bytes * fm.W, pl_row_bytes = (long long)fm.W * esz;
+    // channels-last: pixels of whole 16-byte vectors, at most one region-stage thread group's worth of them, rows of at most 4 chunks
     const bool dense_nhwc = fm.stride_c == 1 && fm.stride_w == fm.C && fm.stride_h == (int64_t)fm.W * fm.C && pix_bytes % 16 == 0 &&
-                            (pix_bytes / 16) % 32 == 0 && pix_bytes / 16 <= kRmacCons && pix_bytes <= kRmacStageBytes;
-    const bool dense_nchw = fm.stride_w == 1 && fm.stride_h == fm.W && fm.stride_c == (int64_t)fm.H * fm.W && fm.W <= 32 &&
-                            plane_bytes % 16 == 0 && plane_bytes <= kRmacStageBytes;
+                            pix_bytes / 16 <= kRmacCons && cl_row_bytes <= (long long)kRmacMaxRowParts * kRmacStageBytes;
+    const bool dense_nchw = fm.stride_w == 1 && fm.stride_h == fm.W && fm.stride_c == (int64_t)fm.H * fm.W && pl_row_bytes % 16 == 0 &&
+                            pl_row_bytes / 16 <= 32 && plane_bytes <= kRmacStageBytes;
     if (!dense_nhwc && !dense_nchw) return kRmacNotApplicable;
     pm.nhwc = dense_nhwc ? 1 : 0;
     pm.n_regions = n_regions ? n_regions[m] : 1;
@@ -475,6 +635,7 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
       } else {
         y0[r] = 0; x0[r] = 0; y1[r] = fm.H; x1[r] = fm.W;
       }
+      p.regions[rbeg + r] = make_int4(y0[r], x0[r], y1[r], x1[r]);
     }
     pm.nxs = rmac_segments(x0, x1, pm.n_regions, fm.W, pm.xb);
     pm.nys = rmac_segments(y0, y1, pm.n_regions, fm.H, pm.yb);
@@ -482,42 +643,49 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
     for (int r = 0; r < pm.n_regions; ++r)
       p.segs[rbeg + r] = make_uchar4((unsigned char)rmac_seg_index(pm.yb, pm.nys, y0[r]), (unsigned char)rmac_seg_index(pm.yb, pm.nys, y1[r]),
                                      (unsigned char)rmac_seg_index(pm.xb, pm.nxs, x0[r]), (unsigned char)rmac_seg_index(pm.xb, pm.nxs, x1[r]));
+    pm.row_parts = 1;
+    pm.rows_per_chunk = 1;
+    if (pm.nhwc) {
+      pm.row_bytes = (int)cl_row_bytes;
+      pm.pix_vecs = (int)(pix_bytes / 16);
+      if (pm.row_bytes <= kRmacStageBytes) {
+        pm.rows_per_chunk = kRmacStageBytes / pm.row_bytes;
+        pm.n_chunks = (fm.H + pm.rows_per_chunk - 1) / pm.rows_per_chunk;
+      } else {
+        pm.row_parts = (pm.row_bytes + kRmacStageBytes - 1) / kRmacStageBytes;
+        pm.n_chunks = fm.H * pm.row_parts;
+      }
+      cm_bytes = std::max(cm_bytes, (size_t)pm.row_bytes);
+    } else {
+      pm.plane_bytes = (int)plane_bytes;
+      pm.lpr = (int)(pl_row_bytes / 16);
+      pm.ppp = 32 / pm.lpr;
+      pm.upc = std::max(1, kRmacStageBytes / pm.plane_bytes);
+      if (pm.upc > pm.ppp) pm.upc -= pm.upc % pm.ppp;
+      pm.n_chunks = (fm.C + pm.upc - 1) / pm.upc;
+      wscr_floats = std::max(wscr_floats, (size_t)pm.ppp * pm.nys * pm.nxs);
+    }
     rbeg += pm.n_regions;
     pm.out_offset = col;
     col += fm.C;
-    if (pm.nhwc) {
-      pm.n_units = fm.H * fm.W;
-      pm.unit_bytes = (int)pix_bytes;
-      pm.upc = std::max(1, kRmacStageBytes / pm.unit_bytes);
-      rs_floats = std::max(rs_floats, (size_t)pm.nxs * fm.C);
-    } else {
-      const int Wp = fm.W > 16 ? 32 : (fm.W > 8 ? 16 : 8);
-      const int ppw = 32 / Wp;
-      pm.n_units = fm.C;
-      pm.unit_bytes = (int)plane_bytes;
-      pm.upc = std::max(1, kRmacStageBytes / pm.unit_bytes);
-      if (pm.upc > ppw) pm.upc -= pm.upc % ppw;
-      wscr_floats = std::max(wscr_floats, (size_t)pm.nys * kRmacCmPitch + (size_t)ppw * pm.nys * pm.nxs);
-    }
-    pm.n_chunks = (pm.n_units + pm.upc - 1) / pm.upc;
     vals_floats = std::max(vals_floats, (size_t)pm.n_regions * fm.C);
   }
   auto up128 = [](size_t v) { return (v + 127) & ~(size_t)127; };
   wscr_floats = (wscr_floats + 3) & ~(size_t)3;
-  const size_t rest = up128(rs_floats * 4) + up128(vals_floats * 4) + up128((size_t)col * 4) + up128(wscr_floats * 4 * kRmacConsWarps) +
-                      up128(2 * kRmacMaxStages * sizeof(uint64_t));
-  const size_t budget = 220 * 1024;  // of the 227 KB a CTA may use; the kernel's static shared memory is ~3 KB
-  if (rest + 2 * (size_t)kRmacStageBytes > budget) return kRmacNotApplicable;
+  const size_t bar_bytes = (kRmacFullBars + kRmacMaxStages) * sizeof(uint64_t);
+  const size_t rest = up128(cm_bytes) + up128(vals_floats * 4) + up128((size_t)col * 4) + up128(wscr_floats * 4 * kRmacConsWarps) + up128(bar_bytes);
+  const size_t budget = 216 * 1024;  // of the 227 KB a CTA may use; the kernel's static shared memory is ~6 KB
+  if (rest + 3 * (size_t)kRmacStageBytes > budget) return kRmacNotApplicable;
   int nst = (int)std::min<size_t>(kRmacMaxStages, (budget - rest) / kRmacStageBytes);
   const int forced = tuning("rmac_stages");
   if (forced >= 2 && forced < nst) nst = forced;
   p.nstages = nst;
   size_t off = (size_t)nst * kRmacStageBytes;
-  p.off_rs = (int)off;    off += up128(rs_floats * 4);
+  p.off_cm = (int)off;    off += up128(cm_bytes);
   p.off_vals = (int)off;  off += up128(vals_floats * 4);
   p.off_desc = (int)off;  off += up128((size_t)col * 4);
   p.off_wscr = (int)off;  off += up128(wscr_floats * 4 * kRmacConsWarps);
-  p.off_bar = (int)off;   off += up128(2 * kRmacMaxStages * sizeof(uint64_t));
+  p.off_bar = (int)off;   off += up128(bar_bytes);
   p.wscr_floats = (int)wscr_floats;
   auto kern = dtype == CVPCE_F32 ? rmac_staged_kernel<CVPCE_F32> : rmac_staged_kernel<CVPCE_BF16>;
   if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), off)) return rc;
@@ -530,3 +698,15 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
 }
 
 }  // namespace cvpce
+
+#ifdef CVPCE_RMAC_PROF
+extern "C" __attribute__((visibility("default"))) int cvpce_debug_rmac_prof(long long* out16, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out16, cvpce::g_rmac_prof, sizeof(long long) * 16);
+  if (reset) {
+    long long z[16] = {0};
+    cudaMemcpyToSymbol(cvpce::g_rmac_prof, z, sizeof(z));
+  }
+  return 0;
+}
+#endif

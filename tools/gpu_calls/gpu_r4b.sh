@@ -1,0 +1,6 @@
+#!/bin/bash
+# staged R-MAC kernel, second version (control data in shared memory, runs, 4/8/16 bytes per thread): parity + A/B
+OUT=gpurun_out/r4b
+mkdir -p $OUT
+timeout 600 python -m pytest tests/test_gpu_parity.py -q -m gpu -x -k "rmac" > $OUT/pytest_rmac.log 2>&1; echo "rmac tests exit $?"; tail -15 $OUT/pytest_rmac.log
+timeout 300 python tools/kbench.py rmac --iters 7 > $OUT/kbench_rmac.jsonl 2> $OUT/kbench_rmac.err; echo "kbench exit $?"; grep -v "B=32\|B=96" $OUT/kbench_rmac.jsonl; tail -5 $OUT/kbench_rmac.err
