@@ -70,6 +70,8 @@ def parse():
     ap.add_argument("--upload-group", type=int, default=4, help="e2e leg: shelf images per upload group")
     ap.add_argument("--e2e-prefetch", type=int, default=0, help="e2e leg: 1 = the next step's images are uploaded (second staging buffer) behind this step's compute; 0 = every step uploads its own images first")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rmac-levels", type=int, default=0, help="0: MAC pooling (the reference's mode, the headline); L > 0: R-MAC with L scales "
+                    "(north-star extension: regions + per-region L2 over relu4_3 and relu5_3, the persistent TMA-staged kernel)")
     ap.add_argument("--no-extension-modes", action="store_true", help="skip the short extra pass that also reports the f16-trunk "
                     "extension mode next to the headline (N = 1, default trunk only)")
     ap.add_argument("--cpu-sample-crops", type=int, default=32)
@@ -247,7 +249,7 @@ def run_ours_shelves(args, world, rank, local):
     images, boxes_h, scores_h, seg_h, max_n = build_shelves(args, rank, n_shelves, device)
     hp = pipeline.HotPath(enc, gallery, k=args.k, trunk_batch=args.trunk_batch,
                           trunk_dtype={"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[args.trunk], channels_last=args.channels_last,
-                          n_streams=args.streams, pad_channel=not args.no_pad_channel)
+                          n_streams=args.streams, pad_channel=not args.no_pad_channel, rmac_levels=args.rmac_levels)
     if args.sim == "f32":  # CUDA-core similarity instead of the tcgen05 kernel (debug / cross-check)
         from cvpce_b200 import ops
         ops_sim = ops.sim_topk
@@ -412,7 +414,8 @@ def run_ours_shelves(args, world, rank, local):
         "data": "synthetic",
         "config": {"workload": ("%s: %d shelves 2048x1536 x ~%d products per GPU -> " + ("GLN head outputs (800x1066, 160956 anchors) -> "
                                 "sigmoid/top-1000/decode -> " if args.from_head else "") + "NMS(0.5, top200) -> 256x256 crops -> "
-                                "VGG16(random init)+MAC -> cosine top-%d vs %d x 1024 gallery") % (args.workload, n_shelves, args.products, args.k, G),
+                                "VGG16(random init)+%s -> cosine top-%d vs %d x 1024 gallery") % (args.workload, n_shelves, args.products,
+                                ("R-MAC(%d levels)" % args.rmac_levels) if args.rmac_levels else "MAC", args.k, G),
                    "crops_per_step_per_gpu": K_crops, "trunk": "torch cuDNN VGG16 convolutions, not rebuilt (%s%s%s, tf32 convs %s)%s" % (
                        args.trunk, ", channels_last" if args.channels_last else "",
                        "" if args.plain_trunk else ", torch.cudnn_convolution_relu", torch.backends.cudnn.allow_tf32,
@@ -805,6 +808,17 @@ def main():
             line["extension_modes"] = {"trunk_f16": {"value": l16["value"], "unit": l16["unit"], "ms_per_step": l16["ms_per_step"],
                                                      "e2e": l16["e2e"]["value"], "steps": a16.steps,
                                                      "note": "half weights/activations, fp32 accumulation; not the headline"}}
+            # the north-star's R-MAC pooling (3 scales, per-region L2) instead of the reference's MAC: the same step, the pooling
+            # kernel reads relu4_3 (32 x 32) and relu5_3 (16 x 16) channels-last through the persistent TMA-staged kernel
+            ar = copy.copy(args)
+            ar.rmac_levels, ar.no_cpu_baseline, ar.steps = 3, True, max(1, min(args.steps, 2))
+            torch.cuda.empty_cache()
+            lr = run_ours_shelves(ar, world, rank, local)
+            line["extension_modes"]["rmac_l3"] = {"value": lr["value"], "unit": lr["unit"], "ms_per_step": lr["ms_per_step"],
+                                                  "e2e": lr["e2e"]["value"], "steps": ar.steps,
+                                                  "region_pool_embed": lr["kernels"].get("region_pool_embed"),
+                                                  "note": "R-MAC (3 scales, 14 regions per map, per-region L2) over relu4_3 + relu5_3; not the headline "
+                                                          "(the reference pools with MAC)"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -37,8 +37,13 @@ constexpr int kRmacCons = kRmacConsWarps * 32;
 constexpr int kRmacThreads = kRmacCons + 32;              // + the producer warp
 constexpr int kRmacMaxSegs = 24;                          // elementary segments per axis
 constexpr int kRmacMaxStages = 8;
-constexpr int kRmacStageBytes = 16384;
+#ifndef CVPCE_RMAC_STAGE_BYTES
+#define CVPCE_RMAC_STAGE_BYTES 16384
+#endif
+constexpr int kRmacStageBytes = CVPCE_RMAC_STAGE_BYTES;   // one ring stage = one bulk copy (a multiple of 8 KB: whole vectors per consumer thread)
 constexpr int kRmacStageVecs = kRmacStageBytes / 16;
+constexpr int kRmacVecsPerThread = kRmacStageVecs / kRmacCons;  // 16-byte vectors of a chunk per consumer thread (channels-last maps)
+static_assert(kRmacVecsPerThread * kRmacCons == kRmacStageVecs, "a stage must be a whole number of vectors per consumer thread");
 constexpr int kRmacFullBars = 16;                         // "full" barriers are tied to the chunk index mod 16 (see the NCHW consumer)
 constexpr int kRmacMaxRegions = CVPCE_POOL_MAX_REGIONS;   // per map
 constexpr int kRmacMaxRegionsTotal = 64;
@@ -169,9 +174,12 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
   const int C = mp.C, H = mp.H, row_bytes = mp.row_bytes, R = mp.rows_per_chunk, nq = mp.pix_vecs;
   const int n_regions = mp.n_regions, region_begin = mp.region_begin;
   const int RV = row_bytes >> 4;  // vectors per row
-  uint4 acc[P][2];
+  constexpr int J = kRmacVecsPerThread;
+  uint4 acc[P][J];
 #pragma unroll
-  for (int pc = 0; pc < P; ++pc) acc[pc][0] = acc[pc][1] = rm_vneg_inf<DTYPE>();
+  for (int pc = 0; pc < P; ++pc)
+#pragma unroll
+    for (int j = 0; j < J; ++j) acc[pc][j] = rm_vneg_inf<DTYPE>();
   // the region stage: thread (g, q) = (region group, channel vector)
   const int n_groups = kRmacCons / nq;
   const int g = tid / nq, q = tid - g * nq;
@@ -184,7 +192,7 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
 #pragma unroll
     for (int pc = 0; pc < P; ++pc) {
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
+      for (int j = 0; j < J; ++j) {
         const int v = pc * kRmacStageVecs + tid + j * kRmacCons;
         if (v < RV) cm[v] = acc[pc][j];
         acc[pc][j] = rm_vneg_inf<DTYPE>();
@@ -241,7 +249,7 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
       bool released = false;
       for (int rr = 0; rr < nrows; ++rr, buf += RV) {
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int j = 0; j < J; ++j) {
           const int v = tid + j * kRmacCons;
           if (v < RV) acc[0][j] = rm_vmax<DTYPE>(acc[0][j], buf[v]);
         }
@@ -271,7 +279,7 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
         const uint4* buf = reinterpret_cast<const uint4*>(ring + (size_t)rg.st * kRmacStageBytes);
         const int nvec = min(kRmacStageVecs, RV - pc * kRmacStageVecs);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int j = 0; j < J; ++j) {
           const int v = tid + j * kRmacCons;
           if (v < nvec) acc[pc][j] = rm_vmax<DTYPE>(acc[pc][j], buf[v]);
         }

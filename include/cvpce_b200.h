@@ -167,9 +167,12 @@ CVPCE_API int cvpce_crop_resize(const int64_t* image_table, int n_images, const 
  * maps [host] n_maps (<= 4) feature maps of the same batch, each [B,C,H,W] with arbitrary element strides
  *      (NCHW-contiguous and channels-last are the fast cases), dtype f32 or bf16.
  *      Measured fractions of HBM bandwidth on B200 (two 512-channel maps, 128-256 images): MAC channels-last 0.75-0.87,
- *      MAC NCHW 0.74-0.80, R-MAC (3 levels) channels-last 0.48-0.51.  R-MAC on NCHW maps is SUPPORTED BUT NOT FAST
- *      (0.17: a per-plane column pass through shared memory); it is an extension mode on a legacy layout -- hand the
- *      maps over channels-last (what the fast trunk produces) when R-MAC throughput matters.
+ *      MAC NCHW 0.74-0.80.  Region lists / per-region L2 (R-MAC, 3 levels) on dense maps of at least SMs/2 images run a
+ *      persistent TMA-staged kernel (csrc/rmac_staged.cu: cp.async.bulk ring, one CTA per image): channels-last f32 0.62-0.69
+ *      (the cluster kernel it replaces there: 0.48-0.51), channels-last bf16 0.47-0.54 (0.17).  R-MAC on NCHW maps is SUPPORTED
+ *      BUT NOT FAST (0.27 f32 / 0.15 bf16 staged, 0.17 / 0.06 before): an extension mode on a legacy layout -- hand the maps
+ *      over channels-last (what the fast trunk produces) when R-MAC throughput matters.  Smaller batches, strided maps, maps
+ *      with rows that are not whole 16-byte units or more than 24 distinct region boundaries per axis take the cluster kernel.
  * regions [host] i32 [sum_m n_regions[m], 4] = (y0,x0,y1,x1), end exclusive, in feature-map cells;
  *      n_regions [host] i32 [n_maps]; both null => one whole-map region per map (MAC, the reference's mode).
  * per_region_l2 0: region maxima of a map are summed as they are (with one region: the plain MAC descriptor);

@@ -12,7 +12,8 @@ lib = _lib.load()
 buf = (ctypes.c_longlong * 16)()
 NAMES = ["producer: waiting for a free stage", "producer: total", "consumer: waiting for a full stage", "consumer: region updates",
          "consumer: per-map finish (norms, descriptor)", "consumer: total", "consumer: barrier after the walk (waiting for the slowest warp)",
-         "consumer: per-image finish (final norm, store)"]
+         "consumer: per-image finish (final norm, store)", "NCHW warp 0: column passes", "NCHW warp 0: cell maxima", "NCHW warp 0: region maxima",
+         "NCHW warp 0: plane groups processed"]
 
 
 def run(tag, feats, regs, **knobs):
