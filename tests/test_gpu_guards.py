@@ -129,6 +129,10 @@ def test_image_kernels_stay_inside_their_outputs(guarded):
         g.check("region_pool_embed MAC B=%d C=%d cl=%s" % (B, C, cl))
         ops.region_pool_embed([f4, f5], regions=[ops.rmac_regions(2 * hw, 2 * hw, 3), ops.rmac_regions(hw, hw, 3)], per_region_l2=True)
         g.check("region_pool_embed R-MAC B=%d C=%d cl=%s" % (B, C, cl))
+        from cvpce_b200 import _lib
+        with _lib.tuning(rmac_kernel=2):  # the persistent TMA-staged kernel (automatic only from B >= SMs/2)
+            ops.region_pool_embed([f4, f5], regions=[ops.rmac_regions(2 * hw, 2 * hw, 3), ops.rmac_regions(hw, hw, 3)], per_region_l2=True)
+        g.check("region_pool_embed R-MAC staged kernel B=%d C=%d cl=%s" % (B, C, cl))
 
 
 def test_search_kernels_stay_inside_their_outputs(guarded):
