@@ -43,7 +43,7 @@ int ensure_dynamic_smem(const void* func, size_t bytes);
 
 // rmac_staged.cu: the persistent TMA-staged R-MAC kernel.  CVPCE_OK = launched; kRmacNotApplicable = the caller falls back
 // to the cluster kernel of region_pool.cu; anything else is an error.  Arguments validated by the caller.
-constexpr int kRmacNotApplicable = 1;
+constexpr int kRmacNotApplicable = -1000;  // not a cvpce_status value
 int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int B, const int32_t* regions, const int32_t* n_regions,
                        int per_region_l2, int final_l2, float eps, float* out, int64_t out_stride, void* stream);
 
