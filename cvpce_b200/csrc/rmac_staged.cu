@@ -85,7 +85,7 @@ struct RmacParams {
   float* out;
   long long out_stride;
   int nstages;
-  int off_cm, off_vals, off_desc, off_wscr, off_bar;  // byte offsets into dynamic shared memory (the ring is at 0)
+  int off_cm, off_seg, off_vals, off_desc, off_wscr, off_bar;  // byte offsets into dynamic shared memory (the ring is at 0)
   int wscr_floats;                                    // per consumer warp (NCHW maps: cell maxima)
 };
 
@@ -168,11 +168,11 @@ __device__ __forceinline__ uint4 rm_vneg_inf() {
 // ---------------------------------------------------------------------------------------------------------------------
 template <int DTYPE, int P>
 __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const RmacMap& mp, const unsigned char* ring, uint64_t* full,
-                                                  uint64_t* empty, uint4* cm, float* vals, RmacRing& rg, int tid, int lane) {
+                                                  uint64_t* empty, uint4* cm, uint4* segm, float* vals, RmacRing& rg, int tid, int lane) {
   constexpr int E = (DTYPE == CVPCE_F32) ? 4 : 8;  // channels per 16-byte vector
   const int nst = p.nstages;
   const int C = mp.C, H = mp.H, row_bytes = mp.row_bytes, R = mp.rows_per_chunk, nq = mp.pix_vecs;
-  const int n_regions = mp.n_regions, region_begin = mp.region_begin;
+  const int n_regions = mp.n_regions, region_begin = mp.region_begin, nxs = mp.nxs;
   const int RV = row_bytes >> 4;  // vectors per row
   constexpr int J = kRmacVecsPerThread;
   uint4 acc[P][J];
@@ -199,20 +199,34 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
       }
     }
     rm_cons_sync();
+    // The region stage is shared-memory-bandwidth bound (cycle counters, profiles/r4n): letting every region re-read its columns
+    // of cm moved ~320 KB per row-segment end at the VGG shapes.  Two steps instead: the maximum of every COLUMN SEGMENT once
+    // (each column of cm is read once), then a region = the maximum of its few column segments.
+    if (g < n_groups) {
+      for (int sgi = g; sgi < nxs; sgi += n_groups) {
+        int x = mp.xb[sgi];
+        const int xe = mp.xb[sgi + 1];
+        const uint4* src = cm + x * nq + q;
+        uint4 m0 = rm_vneg_inf<DTYPE>(), m1 = m0;
+        for (; x + 2 <= xe; x += 2, src += 2 * nq) {
+          m0 = rm_vmax<DTYPE>(m0, src[0]);
+          m1 = rm_vmax<DTYPE>(m1, src[nq]);
+        }
+        if (x < xe) m0 = rm_vmax<DTYPE>(m0, src[0]);
+        segm[sgi * nq + q] = rm_vmax<DTYPE>(m0, m1);
+      }
+    }
+    rm_cons_sync();
     if (g < n_groups) {
       for (int r = g; r < n_regions; r += n_groups) {
         const uchar4 sg = p.segs[region_begin + r];
         if (ys < sg.x || ys >= sg.y) continue;
-        const int4 box = p.regions[region_begin + r];
-        const uint4* src = cm + box.y * nq + q;
-        uint4 m0 = rm_vneg_inf<DTYPE>(), m1 = m0;
-        int x = box.y;
-        for (; x + 2 <= box.w; x += 2, src += 2 * nq) {
+        const uint4* src = segm + sg.z * nq + q;
+        uint4 m0 = src[0];
+        for (int sgi = sg.z + 1; sgi < sg.w; ++sgi) {
+          src += nq;
           m0 = rm_vmax<DTYPE>(m0, src[0]);
-          m1 = rm_vmax<DTYPE>(m1, src[nq]);
         }
-        if (x < box.w) m0 = rm_vmax<DTYPE>(m0, src[0]);
-        m0 = rm_vmax<DTYPE>(m0, m1);
         float f[E];
         if (DTYPE == CVPCE_F32) {
           f[0] = __uint_as_float(m0.x); f[1] = __uint_as_float(m0.y); f[2] = __uint_as_float(m0.z); f[3] = __uint_as_float(m0.w);
@@ -437,6 +451,7 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
   for (int i = tid; i < (int)(sizeof(RmacParams) / 4); i += kRmacThreads) reinterpret_cast<int*>(&p)[i] = reinterpret_cast<const int*>(&gp)[i];
   unsigned char* ring = rm_smem;
   uint4* cm = reinterpret_cast<uint4*>(rm_smem + gp.off_cm);
+  uint4* segm = reinterpret_cast<uint4*>(rm_smem + gp.off_seg);
   float* vals = reinterpret_cast<float*>(rm_smem + gp.off_vals);
   float* desc = reinterpret_cast<float*>(rm_smem + gp.off_desc);
   float* wscr_all = reinterpret_cast<float*>(rm_smem + gp.off_wscr);
@@ -508,10 +523,10 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
     for (int m = 0; m < p.n_maps; ++m) {
       const RmacMap& mp = p.maps[m];
       if (mp.nhwc) {
-        if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
-        else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
-        else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
-        else rmac_consume_nhwc<DTYPE, 4>(p, mp, ring, full, empty, cm, vals, rg, tid, lane);
+        if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else rmac_consume_nhwc<DTYPE, 4>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
       } else {
         rmac_consume_nchw<DTYPE>(p, mp, ring, full, empty, wscr_all + warp * p.wscr_floats, vals, rg, warp, lane);
       }
@@ -614,7 +629,7 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
   p.out = out;
   p.out_stride = out_stride;
   int rbeg = 0, col = 0;
-  size_t cm_bytes = 0, vals_floats = 0, wscr_floats = 0;
+  size_t cm_bytes = 0, seg_bytes = 0, vals_floats = 0, wscr_floats = 0;
   const int32_t* rg = regions;
   for (int m = 0; m < n_maps; ++m) {
     const cvpce_feature_map& fm = maps[m];
@@ -664,6 +679,7 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
         pm.n_chunks = fm.H * pm.row_parts;
       }
       cm_bytes = std::max(cm_bytes, (size_t)pm.row_bytes);
+      seg_bytes = std::max(seg_bytes, (size_t)pm.nxs * (size_t)pix_bytes);
     } else {
       pm.plane_bytes = (int)plane_bytes;
       pm.lpr = (int)(pl_row_bytes / 16);
@@ -681,8 +697,8 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
   auto up128 = [](size_t v) { return (v + 127) & ~(size_t)127; };
   wscr_floats = (wscr_floats + 3) & ~(size_t)3;
   const size_t bar_bytes = (kRmacFullBars + kRmacMaxStages) * sizeof(uint64_t);
-  const size_t rest = up128(cm_bytes) + up128(vals_floats * 4) + up128((size_t)col * 4) + up128(wscr_floats * 4 * kRmacConsWarps) + up128(bar_bytes);
-  const size_t budget = 216 * 1024;  // of the 227 KB a CTA may use; the kernel's static shared memory is ~6 KB
+  const size_t rest = up128(cm_bytes) + up128(seg_bytes) + up128(vals_floats * 4) + up128((size_t)col * 4) + up128(wscr_floats * 4 * kRmacConsWarps) + up128(bar_bytes);
+  const size_t budget = 222 * 1024;  // static (4.2 KB) + dynamic shared memory of a CTA may reach 227 KB
   if (rest + 3 * (size_t)kRmacStageBytes > budget) return kRmacNotApplicable;
   int nst = (int)std::min<size_t>(kRmacMaxStages, (budget - rest) / kRmacStageBytes);
   const int forced = tuning("rmac_stages");
@@ -690,6 +706,7 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
   p.nstages = nst;
   size_t off = (size_t)nst * kRmacStageBytes;
   p.off_cm = (int)off;    off += up128(cm_bytes);
+  p.off_seg = (int)off;   off += up128(seg_bytes);
   p.off_vals = (int)off;  off += up128(vals_floats * 4);
   p.off_desc = (int)off;  off += up128((size_t)col * 4);
   p.off_wscr = (int)off;  off += up128(wscr_floats * 4 * kRmacConsWarps);
