@@ -49,8 +49,8 @@ CVPCE_API int cvpce_device_check(void);
 /* Frees lazily created module state (TMA descriptor cache). Safe to call more than once. */
 CVPCE_API int cvpce_shutdown(void);
 /* Development overrides of launch heuristics (A/B measurements, cross-checks of alternative kernels): process-wide named
- * integers, 0 = automatic.  Knobs: "crop_kernel", "crop_band_rows", "sim_split", "mac_cluster"
- * (csrc/common.cu lists their values).  Results never depend on them beyond fp32 summation order; the library reads no
+ * integers, 0 = automatic.  Knobs: "crop_kernel", "crop_band_rows", "sim_split", "sim_plan", "sim_keys", "mac_cluster",
+ * "mac_kernel", "mac_ctas_per_sm", "rmac_kernel", "rmac_stages" (csrc/common.cu lists their values).  Results never depend on them beyond fp32 summation order; the library reads no
  * environment variables.  Unknown names return CVPCE_ERR_INVALID_ARG. */
 CVPCE_API int cvpce_tuning_set(const char* name, int value);
 CVPCE_API int cvpce_tuning_get(const char* name);
