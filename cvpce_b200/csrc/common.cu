@@ -76,7 +76,8 @@ static TuningEntry g_tuning[] = {
     {"mac_cluster", {0}},       // 0: automatic; 2 / 4 / 8: cluster size of the dense channels-last MAC cluster kernel
     {"mac_kernel", {0}},        // 0: automatic (balanced streaming kernel when a workspace is given); 1: always the cluster kernel
     {"mac_ctas_per_sm", {0}},   // 0: automatic (2); CTAs per SM of the balanced streaming MAC kernel
-    {"rmac_kernel", {0}},       // region lists / per-region L2: 0 automatic (staged kernel from B >= SMs/2); 1: always the cluster kernel; 2: staged kernel whenever it applies
+    {"rmac_kernel", {0}},       // region lists / per-region L2: 0 automatic (staged kernel from B >= SMs/2); 1: always the cluster kernel; 2: rmac_staged_kernel whenever it applies; 4: whenever they apply, the warp-specialised kernel where it covers the maps
+    {"rmac_ws", {0}},           // automatic choice between the two staged kernels: 0 warp-specialised where it covers the maps; 1: never
     {"rmac_stages", {0}},       // 0: automatic (as many 16 KB ring stages as fit, <= 8); else an upper limit (>= 2)
 };
 

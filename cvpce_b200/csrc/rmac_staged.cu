@@ -163,16 +163,91 @@ __device__ __forceinline__ uint4 rm_vneg_inf() {
   return make_uint4(w, w, w, w);
 }
 
+// warp-specialised form (rmac_staged_ws_kernel): 16 streaming warps, 8 region warps, the producer warp
+constexpr int kWsStream = kRmacCons;           // streaming threads (= the consumers of the plain kernel)
+constexpr int kWsReduceWarps = 8;
+constexpr int kWsReduce = kWsReduceWarps * 32;  // region / norm threads
+constexpr int kWsThreads = kWsStream + kWsReduce + 32;
+constexpr int kWsBarReady = 2, kWsBarFree = 3, kWsBarReduce = 4;  // named barriers: cm ready (768), cm free (768), region team (256)
+
+template <int NT, int BAR>
+__device__ __forceinline__ void rm_team_sync() { asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NT) : "memory"); }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The region stage of one row segment by a team of NT threads (t = 0 .. NT-1, named barrier BAR): cm = the row of column
+// maxima of row segment `ys`, complete and visible to the team.  It is shared-memory-bandwidth bound (cycle counters,
+// profiles/r4n): letting every region re-read its columns of cm moved ~320 KB per row-segment end at the VGG shapes.  Two
+// steps instead: the maximum of every COLUMN SEGMENT once (each column of cm is read once), then a region = the maximum of
+// its few column segments.  Thread (g, q) = (group, 16-byte channel vector).  With RELEASE_CM the team hands cm back to the
+// streaming warps as soon as the first step is done.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int DTYPE, int NT, int BAR, bool RELEASE_CM>
+__device__ __forceinline__ void rmac_region_stage(const RmacParams& p, const RmacMap& mp, const uint4* cm, uint4* segm, float* vals, int ys, int t,
+                                                  bool release) {
+  constexpr int E = (DTYPE == CVPCE_F32) ? 4 : 8;  // channels per 16-byte vector
+  const int C = mp.C, nq = mp.pix_vecs, nxs = mp.nxs, n_regions = mp.n_regions, region_begin = mp.region_begin;
+  const int n_groups = NT / nq;
+  const int g = t / nq, q = t - g * nq;
+  if (g < n_groups) {
+    for (int sgi = g; sgi < nxs; sgi += n_groups) {
+      int x = mp.xb[sgi];
+      const int xe = mp.xb[sgi + 1];
+      const uint4* src = cm + x * nq + q;
+      uint4 m0 = rm_vneg_inf<DTYPE>(), m1 = m0;
+      for (; x + 2 <= xe; x += 2, src += 2 * nq) {
+        m0 = rm_vmax<DTYPE>(m0, src[0]);
+        m1 = rm_vmax<DTYPE>(m1, src[nq]);
+      }
+      if (x < xe) m0 = rm_vmax<DTYPE>(m0, src[0]);
+      segm[sgi * nq + q] = rm_vmax<DTYPE>(m0, m1);
+    }
+  }
+  rm_team_sync<NT, BAR>();
+  if (RELEASE_CM && release) {
+    __threadfence_block();
+    asm volatile("bar.arrive %0, %1;" ::"n"(kWsBarFree), "n"(kWsStream + kWsReduce) : "memory");
+  }
+  if (g < n_groups) {
+    for (int r = g; r < n_regions; r += n_groups) {
+      const uchar4 sg = p.segs[region_begin + r];
+      if (ys < sg.x || ys >= sg.y) continue;
+      const uint4* src = segm + sg.z * nq + q;
+      uint4 m0 = src[0];
+      for (int sgi = sg.z + 1; sgi < sg.w; ++sgi) {
+        src += nq;
+        m0 = rm_vmax<DTYPE>(m0, src[0]);
+      }
+      float f[E];
+      if (DTYPE == CVPCE_F32) {
+        f[0] = __uint_as_float(m0.x); f[1] = __uint_as_float(m0.y); f[2] = __uint_as_float(m0.z); f[3] = __uint_as_float(m0.w);
+      } else {
+        f[0] = __uint_as_float(m0.x << 16); f[1] = __uint_as_float(m0.x & 0xffff0000u);
+        f[2] = __uint_as_float(m0.y << 16); f[3] = __uint_as_float(m0.y & 0xffff0000u);
+        f[4 % E] = __uint_as_float(m0.z << 16); f[5 % E] = __uint_as_float(m0.z & 0xffff0000u);
+        f[6 % E] = __uint_as_float(m0.w << 16); f[7 % E] = __uint_as_float(m0.w & 0xffff0000u);
+      }
+      float* dst = vals + r * C + q * E;
+#pragma unroll
+      for (int e = 0; e < E; e += 4) {
+        float4 o = make_float4(f[e], f[e + 1], f[e + 2], f[e + 3]);
+        if (ys > sg.x) {
+          const float4 old = *reinterpret_cast<const float4*>(dst + e);
+          o.x = fmaxf(o.x, old.x); o.y = fmaxf(o.y, old.y); o.z = fmaxf(o.z, old.z); o.w = fmaxf(o.w, old.w);
+        }
+        *reinterpret_cast<float4*>(dst + e) = o;
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // channels-last map: region maxima -> vals[r][C].  P = 16 KB parts per row (1: a chunk holds whole rows).
 // ---------------------------------------------------------------------------------------------------------------------
-template <int DTYPE, int P>
+template <int DTYPE, int P, bool WS>  // WS: the caller is a streaming warp of rmac_staged_ws_kernel (the region stage runs elsewhere)
 __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const RmacMap& mp, const unsigned char* ring, uint64_t* full,
                                                   uint64_t* empty, uint4* cm, uint4* segm, float* vals, RmacRing& rg, int tid, int lane) {
-  constexpr int E = (DTYPE == CVPCE_F32) ? 4 : 8;  // channels per 16-byte vector
   const int nst = p.nstages;
-  const int C = mp.C, H = mp.H, row_bytes = mp.row_bytes, R = mp.rows_per_chunk, nq = mp.pix_vecs;
-  const int n_regions = mp.n_regions, region_begin = mp.region_begin, nxs = mp.nxs;
+  const int H = mp.H, row_bytes = mp.row_bytes, R = mp.rows_per_chunk;
   const int RV = row_bytes >> 4;  // vectors per row
   constexpr int J = kRmacVecsPerThread;
   uint4 acc[P][J];
@@ -180,15 +255,13 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
   for (int pc = 0; pc < P; ++pc)
 #pragma unroll
     for (int j = 0; j < J; ++j) acc[pc][j] = rm_vneg_inf<DTYPE>();
-  // the region stage: thread (g, q) = (region group, channel vector)
-  const int n_groups = kRmacCons / nq;
-  const int g = tid / nq, q = tid - g * nq;
   int y = 0, ys = 0, ynext = mp.yb[1];
 
   // the row segment ends: its row of column maxima goes to shared memory, every region that contains it is updated
   auto row_segment_end = [&]() {
     const long long tr0 = RM_CLOCK();
-    rm_cons_sync();  // the previous row segment's regions are done with cm
+    if (WS) asm volatile("bar.sync %0, %1;" ::"n"(kWsBarFree), "n"(kWsStream + kWsReduce) : "memory");  // the region warps are done with cm
+    else rm_cons_sync();  // the previous row segment's regions are done with cm
 #pragma unroll
     for (int pc = 0; pc < P; ++pc) {
 #pragma unroll
@@ -198,55 +271,12 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
         acc[pc][j] = rm_vneg_inf<DTYPE>();
       }
     }
-    rm_cons_sync();
-    // The region stage is shared-memory-bandwidth bound (cycle counters, profiles/r4n): letting every region re-read its columns
-    // of cm moved ~320 KB per row-segment end at the VGG shapes.  Two steps instead: the maximum of every COLUMN SEGMENT once
-    // (each column of cm is read once), then a region = the maximum of its few column segments.
-    if (g < n_groups) {
-      for (int sgi = g; sgi < nxs; sgi += n_groups) {
-        int x = mp.xb[sgi];
-        const int xe = mp.xb[sgi + 1];
-        const uint4* src = cm + x * nq + q;
-        uint4 m0 = rm_vneg_inf<DTYPE>(), m1 = m0;
-        for (; x + 2 <= xe; x += 2, src += 2 * nq) {
-          m0 = rm_vmax<DTYPE>(m0, src[0]);
-          m1 = rm_vmax<DTYPE>(m1, src[nq]);
-        }
-        if (x < xe) m0 = rm_vmax<DTYPE>(m0, src[0]);
-        segm[sgi * nq + q] = rm_vmax<DTYPE>(m0, m1);
-      }
-    }
-    rm_cons_sync();
-    if (g < n_groups) {
-      for (int r = g; r < n_regions; r += n_groups) {
-        const uchar4 sg = p.segs[region_begin + r];
-        if (ys < sg.x || ys >= sg.y) continue;
-        const uint4* src = segm + sg.z * nq + q;
-        uint4 m0 = src[0];
-        for (int sgi = sg.z + 1; sgi < sg.w; ++sgi) {
-          src += nq;
-          m0 = rm_vmax<DTYPE>(m0, src[0]);
-        }
-        float f[E];
-        if (DTYPE == CVPCE_F32) {
-          f[0] = __uint_as_float(m0.x); f[1] = __uint_as_float(m0.y); f[2] = __uint_as_float(m0.z); f[3] = __uint_as_float(m0.w);
-        } else {
-          f[0] = __uint_as_float(m0.x << 16); f[1] = __uint_as_float(m0.x & 0xffff0000u);
-          f[2] = __uint_as_float(m0.y << 16); f[3] = __uint_as_float(m0.y & 0xffff0000u);
-          f[4 % E] = __uint_as_float(m0.z << 16); f[5 % E] = __uint_as_float(m0.z & 0xffff0000u);
-          f[6 % E] = __uint_as_float(m0.w << 16); f[7 % E] = __uint_as_float(m0.w & 0xffff0000u);
-        }
-        float* dst = vals + r * C + q * E;
-#pragma unroll
-        for (int e = 0; e < E; e += 4) {
-          float4 o = make_float4(f[e], f[e + 1], f[e + 2], f[e + 3]);
-          if (ys > sg.x) {
-            const float4 old = *reinterpret_cast<const float4*>(dst + e);
-            o.x = fmaxf(o.x, old.x); o.y = fmaxf(o.y, old.y); o.z = fmaxf(o.z, old.z); o.w = fmaxf(o.w, old.w);
-          }
-          *reinterpret_cast<float4*>(dst + e) = o;
-        }
-      }
+    if (WS) {  // hand the row of column maxima to the region warps and go on streaming
+      __threadfence_block();
+      asm volatile("bar.arrive %0, %1;" ::"n"(kWsBarReady), "n"(kWsStream + kWsReduce) : "memory");
+    } else {
+      rm_cons_sync();
+      rmac_region_stage<DTYPE, kRmacCons, 1, false>(p, mp, cm, segm, vals, ys, tid, false);
     }
     ++ys;
     ynext = mp.yb[ys + 1];
@@ -523,10 +553,10 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
     for (int m = 0; m < p.n_maps; ++m) {
       const RmacMap& mp = p.maps[m];
       if (mp.nhwc) {
-        if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
-        else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
-        else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
-        else rmac_consume_nhwc<DTYPE, 4>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1, false>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2, false>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3, false>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+        else rmac_consume_nhwc<DTYPE, 4, false>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
       } else {
         rmac_consume_nchw<DTYPE>(p, mp, ring, full, empty, wscr_all + warp * p.wscr_floats, vals, rg, warp, lane);
       }
@@ -588,6 +618,166 @@ __global__ void __launch_bounds__(kRmacThreads, 1) rmac_staged_kernel(const __gr
   if (tid == 0) RM_PROF_ADD(5, RM_CLOCK() - tc0);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Warp-specialised form for channels-last maps: rmac_staged_ws_kernel.  In rmac_staged_kernel the 16 consumer warps stop
+// streaming 12 times per image for the region stage and twice for the norms (~25 us of an ~80 us image, during which only the
+// ring's 112 KB keep the loads going).  Here the 16 STREAMING warps never stop: at the end of a row segment they drop their row
+// of column maxima into cm and go on with the next rows; 8 REGION warps (256 threads) pick cm up (named barriers: "ready" /
+// "free", bar.arrive on the giving side, bar.sync on the taking side), reduce it to column-segment maxima -- cm is free again
+// after that first step --, update the regions, and do the per-map and per-image norms and the store while the next image is
+// already streaming.  vals, segm, desc belong to the region warps alone.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int DTYPE>
+__device__ __forceinline__ void rmac_ws_reducer(const RmacParams& p, const uint4* cm, uint4* segm, float* vals, float* desc,
+                                                float (*s_part)[kWsReduceWarps], float* s_denom, float* s_wsum, int t) {
+  const int lane = t & 31, warp = t >> 5;
+  asm volatile("bar.arrive %0, %1;" ::"n"(kWsBarFree), "n"(kWsStream + kWsReduce) : "memory");  // cm starts out free
+  for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
+    const bool last_image = n + (int)gridDim.x >= p.B;
+    float sq = 0.f;
+    for (int m = 0; m < p.n_maps; ++m) {
+      const RmacMap& mp = p.maps[m];
+      const int nys = mp.nys;
+      for (int ys = 0; ys < nys; ++ys) {
+        asm volatile("bar.sync %0, %1;" ::"n"(kWsBarReady), "n"(kWsStream + kWsReduce) : "memory");  // the row of column maxima is in cm
+        // the very last hand-back has no taker: it is not given
+        const bool release = !(last_image && m == p.n_maps - 1 && ys == nys - 1);
+        rmac_region_stage<DTYPE, kWsReduce, kWsBarReduce, true>(p, mp, cm, segm, vals, ys, t, release);
+        rm_team_sync<kWsReduce, kWsBarReduce>();  // segm is rewritten by the next row segment; vals complete after the last one
+      }
+      const int C = mp.C, n_regions = mp.n_regions;
+      if (p.per_region_l2) {
+        for (int r = 0; r < n_regions; ++r) {
+          float ssum = 0.f;
+          for (int c = t; c < C; c += kWsReduce) {
+            const float v = vals[r * C + c];
+            ssum = fmaf(v, v, ssum);
+          }
+          ssum = warp_sum(ssum);
+          if (lane == 0) s_part[r][warp] = ssum;
+        }
+        rm_team_sync<kWsReduce, kWsBarReduce>();
+        if (t < n_regions) {
+          float tot = 0.f;
+#pragma unroll
+          for (int w = 0; w < kWsReduceWarps; ++w) tot += s_part[t][w];
+          s_denom[t] = fmaxf(sqrtf(tot), p.eps);
+        }
+        rm_team_sync<kWsReduce, kWsBarReduce>();
+      }
+      for (int c = t; c < C; c += kWsReduce) {
+        float d = 0.f;
+        for (int r = 0; r < n_regions; ++r) {
+          float v = vals[r * C + c];
+          if (p.per_region_l2) v = v / s_denom[r];
+          d = (r == 0) ? v : d + v;
+        }
+        desc[mp.out_offset + c] = d;
+        sq = fmaf(d, d, sq);
+      }
+      rm_team_sync<kWsReduce, kWsBarReduce>();  // vals and s_denom are reused by the next map
+    }
+    float denom = 1.f;
+    if (p.final_l2) {
+      sq = warp_sum(sq);
+      if (lane == 0) s_wsum[warp] = sq;
+      rm_team_sync<kWsReduce, kWsBarReduce>();
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < kWsReduceWarps; ++w) tot += s_wsum[w];
+      denom = fmaxf(sqrtf(tot), p.eps);
+    }
+    const RmacMap& last = p.maps[p.n_maps - 1];
+    const int D = last.out_offset + last.C;
+    float* orow = p.out + (long long)n * p.out_stride;
+    for (int c = t; c < D; c += kWsReduce) orow[c] = p.final_l2 ? desc[c] / denom : desc[c];
+    rm_team_sync<kWsReduce, kWsBarReduce>();  // desc / s_wsum are reused by the next image
+  }
+}
+
+template <int DTYPE>
+__global__ void __launch_bounds__(kWsThreads, 1) rmac_staged_ws_kernel(const __grid_constant__ RmacParams gp) {
+  extern __shared__ __align__(128) unsigned char rm_smem[];
+  __shared__ __align__(16) RmacParams p;
+  __shared__ float s_part[kRmacMaxRegions][kWsReduceWarps];
+  __shared__ float s_denom[kRmacMaxRegions];
+  __shared__ float s_wsum[kWsReduceWarps];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < (int)(sizeof(RmacParams) / 4); i += kWsThreads) reinterpret_cast<int*>(&p)[i] = reinterpret_cast<const int*>(&gp)[i];
+  unsigned char* ring = rm_smem;
+  uint4* cm = reinterpret_cast<uint4*>(rm_smem + gp.off_cm);
+  uint4* segm = reinterpret_cast<uint4*>(rm_smem + gp.off_seg);
+  float* vals = reinterpret_cast<float*>(rm_smem + gp.off_vals);
+  float* desc = reinterpret_cast<float*>(rm_smem + gp.off_desc);
+  uint64_t* full = reinterpret_cast<uint64_t*>(rm_smem + gp.off_bar);
+  uint64_t* empty = full + kRmacFullBars;
+  const int nst = gp.nstages;
+  if (tid == 0) {
+    for (int s = 0; s < kRmacFullBars; ++s) rm_mbar_init(&full[s], 1);
+    for (int s = 0; s < nst; ++s) rm_mbar_init(&empty[s], kRmacConsWarps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == kRmacConsWarps + kWsReduceWarps) {
+    // ---- producer (channels-last maps only) ---------------------------------------------------------------------------------
+    if (lane == 0) {
+      uint64_t policy;
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+      RmacRing rg = {0u, 0};
+      uint32_t rev = 0;
+      for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
+        for (int m = 0; m < p.n_maps; ++m) {
+          const RmacMap& mp = p.maps[m];
+          const unsigned char* src = reinterpret_cast<const unsigned char*>(mp.data) + (long long)n * mp.image_bytes;
+          const int n_chunks = mp.n_chunks, H = mp.H, P = mp.row_parts, R = mp.rows_per_chunk, row_bytes = mp.row_bytes;
+          int row = 0, part = 0;
+          for (int k = 0; k < n_chunks; ++k) {
+            long long off;
+            uint32_t bytes;
+            if (P == 1) {  // whole rows
+              off = (long long)row * row_bytes;
+              const int nr = min(R, H - row);
+              bytes = (uint32_t)nr * (uint32_t)row_bytes;
+              row += nr;
+            } else {  // one part of a row
+              off = (long long)row * row_bytes + (long long)part * kRmacStageBytes;
+              bytes = (uint32_t)min(kRmacStageBytes, row_bytes - part * kRmacStageBytes);
+              if (++part == P) {
+                part = 0;
+                ++row;
+              }
+            }
+            rm_mbar_wait_relaxed(&empty[rg.st], (rev & 1) ^ 1);
+            rm_mbar_expect_tx(&full[rg.bar()], bytes);
+            rm_bulk_load(ring + (size_t)rg.st * kRmacStageBytes, src + off, bytes, &full[rg.bar()], policy);
+            rg.advance(nst);
+            if (rg.st == 0) ++rev;
+          }
+        }
+      }
+    }
+    return;
+  }
+  if (warp >= kRmacConsWarps) {
+    // ---- region warps ----------------------------------------------------------------------------------------------------------
+    rmac_ws_reducer<DTYPE>(p, cm, segm, vals, desc, s_part, s_denom, s_wsum, tid - kWsStream);
+    return;
+  }
+  // ---- streaming warps ---------------------------------------------------------------------------------------------------------
+  RmacRing rg = {0u, 0};
+  for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
+    for (int m = 0; m < p.n_maps; ++m) {
+      const RmacMap& mp = p.maps[m];
+      if (mp.row_parts == 1) rmac_consume_nhwc<DTYPE, 1, true>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+      else if (mp.row_parts == 2) rmac_consume_nhwc<DTYPE, 2, true>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+      else if (mp.row_parts == 3) rmac_consume_nhwc<DTYPE, 3, true>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+      else rmac_consume_nhwc<DTYPE, 4, true>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
+    }
+  }
+}
+
 // Elementary segments of [0, dim) between the distinct boundaries of the intervals; returns the count (0: too many).
 static int rmac_segments(const int* lo, const int* hi, int n, int dim, unsigned char* b) {
   int pts[2 * CVPCE_POOL_MAX_REGIONS + 2];
@@ -614,7 +804,8 @@ static int rmac_seg_index(const unsigned char* b, int ns, int v) {
 // back to the cluster kernel) or an error code.  Arguments are already validated by region_pool_impl.
 int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int B, const int32_t* regions, const int32_t* n_regions,
                        int per_region_l2, int final_l2, float eps, float* out, int64_t out_stride, void* stream) {
-  const int mode = tuning("rmac_kernel");  // 0: automatic; 1: never; 2: whenever applicable
+  const int mode = tuning("rmac_kernel");  // 0: automatic; 1: cluster kernel; 2: rmac_staged_kernel whenever applicable;
+                                           // 4: whenever applicable, the warp-specialised kernel where it covers the maps
   if (mode == 1 || !(dtype == CVPCE_F32 || dtype == CVPCE_BF16) || B <= 0) return kRmacNotApplicable;
   // One CTA per image: below about half the SMs the cluster kernel's 8 CTAs per image fill the GPU better.
   if (mode == 0 && B < sm_count() / 2) return kRmacNotApplicable;
@@ -712,12 +903,21 @@ int rmac_staged_launch(const cvpce_feature_map* maps, int n_maps, int dtype, int
   p.off_wscr = (int)off;  off += up128(wscr_floats * 4 * kRmacConsWarps);
   p.off_bar = (int)off;   off += up128(bar_bytes);
   p.wscr_floats = (int)wscr_floats;
-  auto kern = dtype == CVPCE_F32 ? rmac_staged_kernel<CVPCE_F32> : rmac_staged_kernel<CVPCE_BF16>;
+  // channels-last only, pixels of at most 256 vectors (one region-team thread per vector): the warp-specialised kernel
+  bool ws_ok = true;
+  for (int m = 0; m < n_maps; ++m) ws_ok = ws_ok && p.maps[m].nhwc && p.maps[m].pix_vecs <= kWsReduce;
+  // measured (tools/kbench.py rmac, same box): it wins from about 1.2 MB per image (VGG relu4_3 + relu5_3: 0.1475 -> 0.1413 ms at
+  // B = 256 f32, 0.098 -> 0.092 bf16) and loses a little below (two 16 x 16 x 512 f32 maps: 0.092 -> 0.096)
+  long long bytes_per_image = 0;
+  for (int m = 0; m < n_maps; ++m) bytes_per_image += (long long)maps[m].C * maps[m].H * maps[m].W * esz;
+  const bool use_ws = ws_ok && (mode == 4 || (mode == 0 && tuning("rmac_ws") != 1 && bytes_per_image >= 1200 * 1024));
+  auto kern = use_ws ? (dtype == CVPCE_F32 ? rmac_staged_ws_kernel<CVPCE_F32> : rmac_staged_ws_kernel<CVPCE_BF16>)
+                     : (dtype == CVPCE_F32 ? rmac_staged_kernel<CVPCE_F32> : rmac_staged_kernel<CVPCE_BF16>);
   if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), off)) return rc;
   // equal image counts per CTA: a CTA that alone carries one image more than the others would double the run time
   const int per_cta = (B + sm_count() - 1) / sm_count();
   const int grid = (B + per_cta - 1) / per_cta;
-  kern<<<grid, kRmacThreads, off, (cudaStream_t)stream>>>(p);
+  kern<<<grid, use_ws ? kWsThreads : kRmacThreads, off, (cudaStream_t)stream>>>(p);
   CVPCE_LAUNCH_OK("rmac_staged_kernel");
   return CVPCE_OK;
 }

@@ -292,10 +292,16 @@ def test_rmac_vgg_shapes_layouts_dtypes(ops, hw):
 
 
 def _rmac_both_kernels(ops, feats, **kw):
-    """The same call through the persistent TMA-staged kernel (forced) and through the cluster kernel."""
+    """The same call through the persistent TMA-staged kernel (forced), its warp-specialised form (forced) and the cluster kernel."""
     from cvpce_b200 import _lib
     with _lib.tuning(rmac_kernel=2):
         staged = ops.region_pool_embed(feats, **kw).cpu().numpy()
+    with _lib.tuning(rmac_kernel=4):  # channels-last only calls: the warp-specialised kernel (16 streaming + 8 region warps); else as 2
+        ws = ops.region_pool_embed(feats, **kw).cpu().numpy()
+    # the same maxima; the norms sum the squares over 8 instead of 16 warps
+    np.testing.assert_allclose(ws, staged, rtol=2e-6, atol=1e-7)
+    if not kw.get("per_region_l2", False) and not kw.get("final_l2", True):
+        assert np.array_equal(ws, staged)
     with _lib.tuning(rmac_kernel=1):
         cluster = ops.region_pool_embed(feats, **kw).cpu().numpy()
     return staged, cluster
@@ -358,17 +364,24 @@ def test_rmac_staged_kernel_many_images_per_cta_and_odd_maps(ops):
         np.testing.assert_allclose(staged, want, rtol=1e-5, atol=1e-7)
         np.testing.assert_allclose(staged, cluster, rtol=1e-5, atol=1e-7)
         auto = ops.region_pool_embed(maps, regions=regions, per_region_l2=True).cpu().numpy()
-        assert np.array_equal(auto, staged)  # B >= SMs/2: the automatic choice is the staged kernel, which is deterministic
+        again = ops.region_pool_embed(maps, regions=regions, per_region_l2=True).cpu().numpy()
+        assert np.array_equal(auto, again)  # B >= SMs/2: the automatic choice is one of the staged kernels, both deterministic
+        np.testing.assert_allclose(auto, staged, rtol=2e-6, atol=1e-7)
         wide = torch.full((B, 600), -7.0, device="cuda")
         with _lib.tuning(rmac_kernel=2):
             ops.region_pool_embed(maps, regions=regions, per_region_l2=True, out=wide)
         assert np.array_equal(wide[:, :512].cpu().numpy(), staged) and bool((wide[:, 512:] == -7.0).all())
     # fewer ring stages than chunks per image
     base, _ = _rmac_both_kernels(ops, nhwc, regions=regions, per_region_l2=True)
+    with _lib.tuning(rmac_kernel=4):
+        base_ws = ops.region_pool_embed(nhwc, regions=regions, per_region_l2=True).cpu().numpy()
     for stages in (3, 4, 5):
         with _lib.tuning(rmac_kernel=2, rmac_stages=stages):
             out = ops.region_pool_embed(nhwc, regions=regions, per_region_l2=True).cpu().numpy()
         assert np.array_equal(out, base)
+        with _lib.tuning(rmac_kernel=4, rmac_stages=stages):
+            out = ops.region_pool_embed(nhwc, regions=regions, per_region_l2=True).cpu().numpy()
+        assert np.array_equal(out, base_ws)
 
 
 def test_l2norm_rows(ops):

@@ -203,12 +203,14 @@ def bench_rmac(args):
                 nb = f4.element_size() * (f4.numel() + f5.numel()) + 4.0 * 1024 * B
                 regs = [ops.rmac_regions(32, 32, 3), ops.rmac_regions(16, 16, 3)]
                 name = "R-MAC L=3 B=%d %s %s" % (B, "nhwc" if cl else "nchw", "f32" if dt == torch.float32 else "bf16")
-                for kern, stages in ((1, 0), (2, 0), (2, 4)):
+                for kern, stages in ((1, 0), (2, 0), (2, 4), (4, 0)):
                     if stages and not (B in (128, 256) and dt == torch.float32):
+                        continue
+                    if kern == 4 and not cl:
                         continue
                     with _lib.tuning(rmac_kernel=kern, rmac_stages=stages):
                         ms, best = timeit(lambda: ops.region_pool_embed([f4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
-                    report(name + (" cluster kernel" if kern == 1 else " staged kernel" + (" %d stages" % stages if stages else "")), ms, best, nb)
+                    report(name + (" cluster kernel" if kern == 1 else (" staged kernel, warp-specialised" if kern == 4 else " staged kernel" + (" %d stages" % stages if stages else ""))), ms, best, nb)
                 del f4, f5
     # the fast trunk's hand-off: pool4(relu4_3) and relu5_3, both 16 x 16, channels-last f32
     for B in (128, 256):
@@ -217,10 +219,10 @@ def bench_rmac(args):
         out = torch.empty((B, 1024), device=dev)
         nb = 4.0 * (p4.numel() + f5.numel()) + 4.0 * 1024 * B
         regs = [ops.rmac_regions(16, 16, 3), ops.rmac_regions(16, 16, 3)]
-        for kern in (1, 2):
+        for kern in (1, 2, 4):
             with _lib.tuning(rmac_kernel=kern):
                 ms, best = timeit(lambda: ops.region_pool_embed([p4, f5], regions=regs, per_region_l2=True, out=out), args.iters)
-            report("R-MAC L=3 B=%d nhwc f32, two 16x16 maps (fast-trunk hand-off) %s" % (B, "cluster kernel" if kern == 1 else "staged kernel"), ms, best, nb)
+            report("R-MAC L=3 B=%d nhwc f32, two 16x16 maps (fast-trunk hand-off) %s" % (B, {1: "cluster kernel", 2: "staged kernel", 4: "staged kernel, warp-specialised"}[kern]), ms, best, nb)
 
 
 def bench_prep(args):
