@@ -320,6 +320,7 @@ __device__ __forceinline__ void rmac_consume_nhwc(const RmacParams& p, const Rma
         const long long tw0 = RM_CLOCK();
         rm_mbar_wait(&full[rg.bar()], rg.parity());
         if (tid == 0) RM_PROF_ADD(2, RM_CLOCK() - tw0);
+        if (tid == 0 && rg.it == 0) RM_PROF_ADD(15, RM_CLOCK() - tw0);  // the wait for the very first chunk
         const uint4* buf = reinterpret_cast<const uint4*>(ring + (size_t)rg.st * kRmacStageBytes);
         const int nvec = min(kRmacStageVecs, RV - pc * kRmacStageVecs);
 #pragma unroll
@@ -647,14 +648,29 @@ __device__ __forceinline__ void rmac_ws_reducer(const RmacParams& p, const uint4
       }
       const int C = mp.C, n_regions = mp.n_regions;
       if (p.per_region_l2) {
-        for (int r = 0; r < n_regions; ++r) {
-          float ssum = 0.f;
-          for (int c = t; c < C; c += kWsReduce) {
-            const float v = vals[r * C + c];
-            ssum = fmaf(v, v, ssum);
+        // this is on the critical path of the hand-off (and the tail of the launch): eight regions at a time, so that their
+        // shuffle reductions overlap instead of forming 14 chains of five dependent shuffles
+        for (int r0 = 0; r0 < n_regions; r0 += 8) {
+          float ssum[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            ssum[j] = 0.f;
+            if (r0 + j < n_regions)
+              for (int c = t; c < C; c += kWsReduce) {
+                const float v = vals[(r0 + j) * C + c];
+                ssum[j] = fmaf(v, v, ssum[j]);
+              }
           }
-          ssum = warp_sum(ssum);
-          if (lane == 0) s_part[r][warp] = ssum;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ssum[j] += __shfl_xor_sync(0xffffffffu, ssum[j], o);
+          }
+          if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (r0 + j < n_regions) s_part[r0 + j][warp] = ssum[j];
+          }
         }
         rm_team_sync<kWsReduce, kWsBarReduce>();
         if (t < n_regions) {
@@ -667,7 +683,21 @@ __device__ __forceinline__ void rmac_ws_reducer(const RmacParams& p, const uint4
       }
       for (int c = t; c < C; c += kWsReduce) {
         float d = 0.f;
-        for (int r = 0; r < n_regions; ++r) {
+        int r = 0;
+        for (; r + 4 <= n_regions; r += 4) {  // four independent quotients, summed in region order
+          float v0 = vals[r * C + c], v1 = vals[(r + 1) * C + c], v2 = vals[(r + 2) * C + c], v3 = vals[(r + 3) * C + c];
+          if (p.per_region_l2) {
+            v0 = v0 / s_denom[r];
+            v1 = v1 / s_denom[r + 1];
+            v2 = v2 / s_denom[r + 2];
+            v3 = v3 / s_denom[r + 3];
+          }
+          d = (r == 0) ? v0 : d + v0;
+          d += v1;
+          d += v2;
+          d += v3;
+        }
+        for (; r < n_regions; ++r) {
           float v = vals[r * C + c];
           if (p.per_region_l2) v = v / s_denom[r];
           d = (r == 0) ? v : d + v;
@@ -703,6 +733,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) rmac_staged_ws_kernel(const __g
   __shared__ float s_denom[kRmacMaxRegions];
   __shared__ float s_wsum[kWsReduceWarps];
 
+  const long long t_entry = RM_CLOCK();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < (int)(sizeof(RmacParams) / 4); i += kWsThreads) reinterpret_cast<int*>(&p)[i] = reinterpret_cast<const int*>(&gp)[i];
   unsigned char* ring = rm_smem;
@@ -763,10 +794,12 @@ __global__ void __launch_bounds__(kWsThreads, 1) rmac_staged_ws_kernel(const __g
   if (warp >= kRmacConsWarps) {
     // ---- region warps ----------------------------------------------------------------------------------------------------------
     rmac_ws_reducer<DTYPE>(p, cm, segm, vals, desc, s_part, s_denom, s_wsum, tid - kWsStream);
+    if (tid == kWsStream) RM_PROF_ADD(14, RM_CLOCK() - t_entry);  // entry -> the region warps are done (the CTA's work is complete)
     return;
   }
   // ---- streaming warps ---------------------------------------------------------------------------------------------------------
   RmacRing rg = {0u, 0};
+  if (tid == 0) RM_PROF_ADD(12, RM_CLOCK() - t_entry);  // prologue (parameter copy, barrier init, CTA barrier)
   for (int n = blockIdx.x; n < p.B; n += gridDim.x) {
     for (int m = 0; m < p.n_maps; ++m) {
       const RmacMap& mp = p.maps[m];
@@ -776,6 +809,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) rmac_staged_ws_kernel(const __g
       else rmac_consume_nhwc<DTYPE, 4, true>(p, mp, ring, full, empty, cm, segm, vals, rg, tid, lane);
     }
   }
+  if (tid == 0) RM_PROF_ADD(13, RM_CLOCK() - t_entry);  // entry -> the streaming warps are done
 }
 
 // Elementary segments of [0, dim) between the distinct boundaries of the intervals; returns the count (0: too many).
