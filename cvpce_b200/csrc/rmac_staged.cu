@@ -55,7 +55,7 @@ __device__ long long g_rmac_prof[16];
 #define RM_PROF_ADD(k, v) do { if (blockIdx.x == 0) g_rmac_prof[k] += (v); } while (0)
 #define RM_CLOCK() clock64()
 #else
-#define RM_PROF_ADD(k, v) do { } while (0)
+#define RM_PROF_ADD(k, v) do { (void)(v); } while (0)
 #define RM_CLOCK() 0ll
 #endif
 
