@@ -28,6 +28,10 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# crops per cuDNN call of the torch trunk (and per pooling launch).  Measured on one box, alternating runs (profiles/r4wx_trunk_batch_sweep_in_step.jsonl):
+# 256 -> 14.32-14.51k crops/s with the MAC launch at 0.70 of HBM; 512 -> 14.49-14.71k, 0.80; 800 -> 14.64-14.69k, 0.855;
+# 1600 -> 14.71k, 0.91.  800 = the crops of one upload group of the end-to-end leg (4 shelves x 200) and 6400 / 8.
+TRUNK_BATCH = 800
 METRIC = "proposal crops classified/sec"
 UNIT = "crops/s"
 
@@ -50,7 +54,7 @@ def parse():
     ap.add_argument("--channels-last", action="store_true")
     ap.add_argument("--plain-trunk", action="store_true", help="call the torch trunk module by module in NCHW (the reference's way) "
                     "instead of channels-last + torch.cudnn_convolution_relu")
-    ap.add_argument("--trunk-batch", type=int, default=256)
+    ap.add_argument("--trunk-batch", type=int, default=TRUNK_BATCH)
     ap.add_argument("--streams", type=int, default=1, help="CUDA streams the trunk batches alternate between")
     ap.add_argument("--cudnn-benchmark", action="store_true")
     ap.add_argument("--strict-fp32", action="store_true", help="torch.backends.cudnn.allow_tf32 = False for the torch trunk (the default "

@@ -100,7 +100,7 @@ def test_crop_identity_and_constant_at_shelf_size(ops):
     assert float(many.min()) >= 0.0 and float(many.max()) <= 1.0
 
 
-@pytest.mark.parametrize("B", [256, 130])   # the trunk batch of the step (clusters of 2) and a ragged last batch (clusters of 4)
+@pytest.mark.parametrize("B", [800, 256, 130])   # the trunk batch of the bench step, a smaller one (clusters of 2) and a ragged last batch (clusters of 4)
 def test_mac_exact_maxima_at_trunk_batch_size(ops, B):
     g = torch.Generator(device="cuda").manual_seed(3)
     for cl in (False, True):

@@ -1,7 +1,7 @@
 """Gate for the numeric mode bench.py's headline runs in.
 
 bench.py's default line times HotPath with the FAST trunk (channels-last + torch.cudnn_convolution_relu + the library's
-max-pool), 4-channel crops (CVPCE_NHWC4), trunk batch 256, S = 256, the tcgen05 search with exact fp32 re-score and --
+max-pool), 4-channel crops (CVPCE_NHWC4), bench.py's trunk batch (bench.TRUNK_BATCH), S = 256, the tcgen05 search with exact fp32 re-score and --
 torch's GPU default -- TF32 convolutions.  Every other parity test switches TF32 off.  Here the step is built exactly as
 bench.py:run_ours_shelves builds it and compared with the reference's torch CPU path in strict fp32
 (oracle/torch_port.py: torchvision nms, python crop loop + antialiased resize, VGG16 fp32, amax / cat / norm):
@@ -23,6 +23,7 @@ import numpy as np
 import pytest
 import torch
 
+import bench
 from cvpce_b200 import synth
 
 pytestmark = pytest.mark.gpu
@@ -109,7 +110,7 @@ def test_headline_numeric_mode_against_fp32_cpu_path(cuda):
             torch.manual_seed(synth.WEIGHT_SEED)                         # bench.py:build_encoder
             enc = classification.macvgg_embedder("vgg16", pretrained=False).eval().requires_grad_(False).to(dev)
             enc.enable_fast_trunk()
-            hp = pipeline.HotPath(enc, gallery, k=k, trunk_batch=256, trunk_dtype=torch.float32, channels_last=True, n_streams=1, pad_channel=True)
+            hp = pipeline.HotPath(enc, gallery, k=k, trunk_batch=bench.TRUNK_BATCH, trunk_dtype=torch.float32, channels_last=True, n_streams=1, pad_channel=True)
             out = hp.step(imgs_d, torch.from_numpy(boxes).to(dev), torch.from_numpy(scores).to(dev), torch.from_numpy(seg).to(dev), max(sizes))
             torch.cuda.synchronize()
             results[mode] = _compare(out, want_boxes, emb_cpu, gallery.cpu(), k, emb_bar, top1_bar)
@@ -118,7 +119,7 @@ def test_headline_numeric_mode_against_fp32_cpu_path(cuda):
         torch.backends.cudnn.allow_tf32 = saved
     os.makedirs("gpurun_out", exist_ok=True)
     with open(os.path.join("gpurun_out", "headline_mode_check.json"), "w") as f:
-        json.dump({"config": "HotPath as bench.py builds it: fast trunk, NHWC4 crops, trunk batch 256, S=256, tcgen05 + exact re-score, "
-                             "%d shelves x ~%d products, gallery %d x 1024, top-%d; reference = oracle/torch_port.py, strict fp32 on the CPU" % (n_shelves, products, G, k),
+        json.dump({"config": "HotPath as bench.py builds it: fast trunk, NHWC4 crops, trunk batch %d, S=256, tcgen05 + exact re-score, "
+                             "%d shelves x ~%d products, gallery %d x 1024, top-%d; reference = oracle/torch_port.py, strict fp32 on the CPU" % (bench.TRUNK_BATCH, n_shelves, products, G, k),
                    "bars": {"emb_rel_norm_tf32": EMB_BAR_TF32, "emb_rel_norm_fp32": EMB_BAR_FP32, "top1_tf32": TOP1_BAR_TF32, "top1_fp32": TOP1_BAR_FP32},
                    "results": results}, f, indent=1)
