@@ -24,6 +24,9 @@
 //  * all channels of an image are in one CTA, so the per-region L2 norms and the final L2 norm are block reductions (no
 //    cluster, no workspace, no second launch).
 // Every feature value is read from HBM exactly once.
+// Two kernels share the code: rmac_staged_kernel (16 consumer warps do everything; any mix of layouts) and
+// rmac_staged_ws_kernel (channels-last only: 16 streaming warps that never stop + 8 region warps; the automatic choice from
+// 1.2 MB per image).  DESIGN.md section 4.3 has the measurements, including the variants that were slower.
 #include "common.cuh"
 #include <cuda_bf16.h>
 #include <math.h>
