@@ -168,7 +168,7 @@ CVPCE_API int cvpce_crop_resize(const int64_t* image_table, int n_images, const 
  *      (NCHW-contiguous and channels-last are the fast cases), dtype f32 or bf16.
  *      Measured fractions of HBM bandwidth on B200 (two 512-channel maps, 128-256 images): MAC channels-last 0.75-0.87,
  *      MAC NCHW 0.74-0.80.  Region lists / per-region L2 (R-MAC, 3 levels) on dense maps of at least SMs/2 images run a
- *      persistent TMA-staged kernel (csrc/rmac_staged.cu: cp.async.bulk ring, one CTA per image): channels-last f32 0.64-0.73
+ *      persistent TMA-staged kernel (csrc/rmac_staged.cu: cp.async.bulk ring, one CTA per image): channels-last f32 0.64-0.84 (128-800 images)
  *      (the cluster kernel it replaces there: 0.48-0.51), channels-last bf16 0.47-0.56 (0.17).  R-MAC on NCHW maps is SUPPORTED
  *      BUT NOT FAST (0.27 f32 / 0.15 bf16 staged, 0.17 / 0.06 before): an extension mode on a legacy layout -- hand the maps
  *      over channels-last (what the fast trunk produces) when R-MAC throughput matters.  Smaller batches, strided maps, maps
